@@ -1,0 +1,83 @@
+// Shared helpers for the sm_100a kernels of the BOP pose-error hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/bop_b200.h"
+
+// ---- error plumbing (api.cu owns the storage) -----------------------------------
+int bop_set_error_cuda(cudaError_t e, const char* what, const char* file, int line);
+int bop_set_error_msg(int code, const char* msg);
+void bop_count_launch(int n = 1);
+
+#define BOP_CUDA(x)                                                        \
+  do {                                                                     \
+    cudaError_t _e = (x);                                                  \
+    if (_e != cudaSuccess) return bop_set_error_cuda(_e, #x, __FILE__, __LINE__); \
+  } while (0)
+
+#define BOP_LAUNCH_CHECK()                                                 \
+  do {                                                                     \
+    cudaError_t _e = cudaGetLastError();                                   \
+    if (_e != cudaSuccess) return bop_set_error_cuda(_e, "kernel launch", __FILE__, __LINE__); \
+    bop_count_launch();                                                    \
+  } while (0)
+
+#define BOP_REQUIRE(cond, msg)                                             \
+  do {                                                                     \
+    if (!(cond)) return bop_set_error_msg(-1, msg);                        \
+  } while (0)
+
+// ---- device helpers -----------------------------------------------------------
+#define BOP_FULL_MASK 0xffffffffu
+#define BOP_INF_BITS_F32 0x7f800000u
+#define BOP_INF_BITS_F64 0x7ff0000000000000ull
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(BOP_FULL_MASK, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(BOP_FULL_MASK, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_sum(int v) {
+  return __reduce_add_sync(BOP_FULL_MASK, v);
+}
+
+// Streaming 128-bit load that does not allocate in L1 (depth images are read once).
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ld_stream_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];"
+               : "=r"(r.x), "=r"(r.y)
+               : "l"(p));
+  return r;
+}
+
+// 3x3 helpers on row-major doubles.
+__device__ __forceinline__ void mat3_mul(const double* A, const double* B, double* C) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      C[i * 3 + j] = A[i * 3 + 0] * B[0 * 3 + j] + A[i * 3 + 1] * B[1 * 3 + j] +
+                     A[i * 3 + 2] * B[2 * 3 + j];
+}
+__device__ __forceinline__ void mat3_vec(const double* A, const double* v, double* o) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) o[i] = A[i * 3 + 0] * v[0] + A[i * 3 + 1] * v[1] + A[i * 3 + 2] * v[2];
+}
+
+// Internal launchers shared between api.cu and the kernel translation units.
+int bop_launch_re_te(const double* pe, const double* pg, int n, double* re, double* te,
+                     cudaStream_t s);

@@ -1,0 +1,206 @@
+/*
+ * bop_b200.h -- C ABI of the B200-native BOP pose-error hot path.
+ *
+ * Every entry point replaces one Python-level call of the reference
+ * (gist-ailab/bop_toolkit); the reference file:line each one stands in for is
+ * cited beside it.  All paths are relative to the reference repository root.
+ *
+ * Conventions
+ *   - Plain C types only: pointers, sizes, POD structs.  No torch/pybind types.
+ *   - `*_dev` functions take DEVICE pointers and enqueue work on `stream`
+ *     (a cudaStream_t passed as void*; NULL = legacy default stream).  They never
+ *     synchronise the device.
+ *   - `*_host` functions take HOST pointers, stage them through the device on an
+ *     internal stream, run the same kernels and return after the results are back
+ *     in host memory.
+ *   - Return value: 0 on success, non-zero on failure; bop_last_error() then
+ *     returns a human-readable message (thread-local).
+ *   - Poses are `double[12]`: R row-major (9 values) followed by t (3 values, mm),
+ *     exactly the (R, t) pairs the reference passes to pose_error.* .
+ *   - Units: millimetres and pixels, OpenCV camera frame (docs/bop_datasets_format.md).
+ *   - There is NO CPU fallback: every compute entry point fails if no CUDA device
+ *     is usable.
+ */
+#ifndef BOP_B200_H_
+#define BOP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BOP_B200_ABI_VERSION 1
+#define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
+#define BOP_MAX_SYMS_PER_CTA 32
+
+/* Cost types of pose_error.vsd (bop_toolkit_lib/pose_error.py:79-88). */
+#define BOP_COST_STEP 0
+#define BOP_COST_TLINEAR 1
+/* Visibility modes of visibility._estimate_visib_mask (bop_toolkit_lib/visibility.py:29-37). */
+#define BOP_VISIB_BOP19 0
+#define BOP_VISIB_BOP18 1
+/* Depth image element types accepted by the VSD entry points. */
+#define BOP_DEPTH_F32 0      /* float32 millimetres (what inout.load_depth returns, inout.py:39-46) */
+#define BOP_DEPTH_U16 1      /* raw uint16 PNG samples; multiplied by depth_scale[im] in float32
+                                (scripts/eval_calc_errors.py:239-243) */
+
+/*
+ * One object model resident in device memory.
+ * Mirrors what the reference keeps per obj_id: models[obj_id]['pts'] (inout.load_ply,
+ * inout.py:401-583), the renderer's vertex/index buffers (renderer_vispy.py:299-420),
+ * models_sym[obj_id] (misc.get_symmetry_transformations, misc.py:43-90) and
+ * models_info[obj_id]['diameter'].
+ */
+typedef struct bop_model_dev {
+  const void*    pts;       /* [n_pts][3] float64 if pts_f64 else float32                     */
+  const float*   verts4;    /* [n_pts][4] float32 (x,y,z,0): rasteriser vertices, ADI targets */
+  const int32_t* faces4;    /* [n_faces][4] int32 (i0,i1,i2,0); may be NULL if n_faces == 0   */
+  const double*  syms;      /* [n_syms][12] R row-major then t; may be NULL if n_syms == 0    */
+  double         diameter;  /* models_info[obj_id]['diameter'] (mm)                          */
+  int32_t        n_pts;
+  int32_t        n_faces;
+  int32_t        n_syms;
+  int32_t        pts_f64;
+} bop_model_dev;
+
+/* Parameters of pose_error.vsd (bop_toolkit_lib/pose_error.py:17-18). */
+typedef struct bop_vsd_params {
+  double  taus[BOP_MAX_TAUS];
+  double  delta;
+  int32_t n_taus;
+  int32_t normalized_by_diameter;
+  int32_t cost_type;        /* BOP_COST_*  */
+  int32_t visib_mode;       /* BOP_VISIB_* */
+  int32_t height;
+  int32_t width;
+  int32_t gate;             /* 1: apply the driver's sphere-projection gate
+                               (scripts/eval_calc_errors.py:296-313) -> [1.0]*n_taus   */
+  int32_t depth_dtype;      /* BOP_DEPTH_* */
+} bop_vsd_params;
+
+/* ---- library / device ---------------------------------------------------- */
+int         bop_abi_version(void);
+const char* bop_last_error(void);
+/* Number of usable CUDA devices (0 if none); never fails. */
+int         bop_device_count(void);
+/* Number of kernels launched by this library in the calling process so far. */
+uint64_t    bop_kernel_launch_count(void);
+
+/* ---- K5: re / te ----------------------------------------------------------
+ * pose_error.re (pose_error.py:187-202), pose_error.te (pose_error.py:205-214).
+ * re_out / te_out: [n_pairs] float64; either may be NULL.                      */
+int bop_re_te_dev(const double* pose_est, const double* pose_gt, int n_pairs,
+                  double* re_out, double* te_out, void* stream);
+int bop_re_te_host(const double* pose_est, const double* pose_gt, int n_pairs,
+                   double* re_out, double* te_out);
+
+/* ---- K3: per-vertex errors -------------------------------------------------
+ * pose_error.mssd (pose_error.py:96-118), mspd (:121-144), add (:147-161),
+ * proj (:217-232).  models: device table; obj_idx: [n_pairs] row of `models` per
+ * pair.  gate != 0 applies `||t_e - t_g|| < diameter` else +inf
+ * (scripts/eval_calc_errors.py:305-309,321-322,334-339); mspd/proj are never gated.
+ * K (mspd/proj): [n_pairs][9] row-major 3x3 intrinsics per pair.
+ * out: [n_pairs] float64.                                                      */
+int bop_mssd_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                 const double* pose_est, const double* pose_gt, int n_pairs,
+                 int max_syms, int gate, double* out, void* stream);
+int bop_mspd_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                 const double* pose_est, const double* pose_gt, const double* K,
+                 int n_pairs, int max_syms, double* out, void* stream);
+int bop_add_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                const double* pose_est, const double* pose_gt, int n_pairs,
+                int max_pts, int gate, double* out, void* stream);
+int bop_proj_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                 const double* pose_est, const double* pose_gt, const double* K,
+                 int n_pairs, int max_pts, double* out, void* stream);
+
+/* ---- K4: ADI ----------------------------------------------------------------
+ * pose_error.adi (pose_error.py:164-184): mean over GT-posed points of the
+ * distance to the nearest EST-posed point; exact brute-force NN replaces
+ * scipy.spatial.cKDTree.  out: [n_pairs] float64.                              */
+int bop_adi_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                const double* pose_est, const double* pose_gt, int n_pairs,
+                int max_pts, int gate, double* out, void* stream);
+
+/* ---- K1: depth rasteriser ---------------------------------------------------
+ * Renderer.render_object in 'depth' mode (renderer.py:62-74;
+ * renderer_vispy.py:433-466,509-538; shaders :123-146).  One image per pose:
+ * depth_out[b] is H x W float32, nearest-surface camera Z in mm at the pixel
+ * centre (c+0.5, r+0.5), 0 = background.  cam: [n][4] float64 fx,fy,cx,cy.
+ * workspace: bop_render_workspace_bytes(n) bytes of device memory.             */
+size_t bop_render_workspace_bytes(int n);
+int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                         const double* pose, const double* cam, int n,
+                         int height, int width, float* depth_out,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K2: fused depth->dist + visibility + per-tau cost ---------------------
+ * pose_error.vsd after the two render calls (pose_error.py:48-91), i.e.
+ * misc.depth_im_to_dist_im_fast (misc.py:143-163) x3,
+ * visibility.estimate_visib_mask_gt/_est (visibility.py:45-75) and the tau sweep,
+ * for pre-rendered depth images.  depth_est/depth_gt: [n_pairs][H][W] float32.
+ * depth_test: [n_im][H][W] (prm->depth_dtype); im_idx: [n_pairs]; K: [n_im][9];
+ * depth_scale: [n_im] float32 or NULL; diameters: [n_pairs] float64.
+ * errors_out: [n_pairs][n_taus] float64.  counts_out (optional, may be NULL):
+ * [n_pairs][2+n_taus] int64 = union, inter, per-tau cost counts (step cost).  */
+size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width);
+int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
+                           const int32_t* im_idx, const double* K,
+                           const float* depth_est, const float* depth_gt,
+                           const double* diameters, int n_pairs,
+                           const bop_vsd_params* prm, double* errors_out,
+                           int64_t* counts_out, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* ---- K1+K2 fused: pose_error.vsd for a batch of pose pairs -----------------
+ * pose_error.vsd (pose_error.py:17-93) with the library's own rasteriser: both
+ * poses are rendered into shared-memory z-tiles over the union ROI and consumed
+ * by the pixel pass without ever being written to HBM.
+ * errors_out: [n_pairs][n_taus] float64; counts_out optional as above.        */
+int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                const double* pose_est, const double* pose_gt,
+                const void* depth_test, const float* depth_scale,
+                const int32_t* im_idx, const double* K, int n_pairs,
+                const bop_vsd_params* prm, double* errors_out,
+                int64_t* counts_out, void* workspace, size_t workspace_bytes,
+                void* stream);
+
+/* ---- host-buffer convenience layer -----------------------------------------
+ * Upload a model (host arrays, float64 pts as pose_error.* receives them) and get a
+ * filled descriptor whose pointers are device memory owned by the library until
+ * bop_model_free.  `desc_dev_out` receives a device copy of the descriptor that can
+ * be used as a 1-row `models` table.                                           */
+int bop_model_upload(const double* pts, int n_pts, const int32_t* faces, int n_faces,
+                     const double* syms, int n_syms, double diameter,
+                     bop_model_dev* desc_host_out, bop_model_dev** desc_dev_out);
+int bop_model_free(bop_model_dev* desc_host, bop_model_dev* desc_dev);
+
+/* Single-model batches with host buffers (what a ctypes binding of
+ * pose_error.mssd/mspd/add/adi would call). */
+int bop_mssd_host(const bop_model_dev* model_dev, int n_syms, const double* pose_est,
+                  const double* pose_gt, int n_pairs, int gate, double* out);
+int bop_mspd_host(const bop_model_dev* model_dev, int n_syms, const double* pose_est,
+                  const double* pose_gt, const double* K, int n_pairs, double* out);
+int bop_add_host(const bop_model_dev* model_dev, int n_pts, const double* pose_est,
+                 const double* pose_gt, int n_pairs, int gate, double* out);
+int bop_adi_host(const bop_model_dev* model_dev, int n_pts, const double* pose_est,
+                 const double* pose_gt, int n_pairs, int gate, double* out);
+int bop_render_depth_host(const bop_model_dev* model_dev, const double* pose,
+                          const double* cam, int n, int height, int width,
+                          float* depth_out);
+int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_est,
+                 const double* pose_gt, const void* depth_test,
+                 const float* depth_scale, const int32_t* im_idx, const double* K,
+                 int n_im, int n_pairs, const bop_vsd_params* prm, double* errors_out);
+
+/* Tunables of the fused VSD kernel (persist per process; used for on-GPU tuning).
+ * tile_px: z-tile capacity in pixels per pose (shared memory = 8*tile_px bytes);
+ * threads: CTA size; ctas_per_sm: persistent CTAs per SM.  0 keeps the current value. */
+int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_px);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* BOP_B200_H_ */
