@@ -1,0 +1,122 @@
+"""ctypes binding of libbop_b200.so (the C ABI declared in include/bop_b200.h).
+
+There is no CPU fallback: if the shared library is missing this module raises, and every
+compute entry point fails when no CUDA device is usable.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, 'csrc')
+SO_PATH = os.path.join(CSRC, 'libbop_b200.so')
+SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu']
+HEADERS = ['common.cuh', 'raster.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
+
+BOP_MAX_TAUS = 16
+COST_TYPES = {'step': 0, 'tlinear': 1}
+VISIB_MODES = {'bop19': 0, 'bop18': 1}
+DEPTH_F32, DEPTH_U16 = 0, 1
+
+
+class ModelDev(ctypes.Structure):
+  """struct bop_model_dev (include/bop_b200.h)."""
+  _fields_ = [
+    ('pts', ctypes.c_void_p), ('verts4', ctypes.c_void_p), ('faces4', ctypes.c_void_p),
+    ('syms', ctypes.c_void_p), ('diameter', ctypes.c_double), ('n_pts', ctypes.c_int32),
+    ('n_faces', ctypes.c_int32), ('n_syms', ctypes.c_int32), ('pts_f64', ctypes.c_int32)]
+
+
+class VsdParams(ctypes.Structure):
+  """struct bop_vsd_params (include/bop_b200.h)."""
+  _fields_ = [
+    ('taus', ctypes.c_double * BOP_MAX_TAUS), ('delta', ctypes.c_double),
+    ('n_taus', ctypes.c_int32), ('normalized_by_diameter', ctypes.c_int32),
+    ('cost_type', ctypes.c_int32), ('visib_mode', ctypes.c_int32), ('height', ctypes.c_int32),
+    ('width', ctypes.c_int32), ('gate', ctypes.c_int32), ('depth_dtype', ctypes.c_int32)]
+
+
+def build(force=False, verbose=False):
+  """Compiles the CUDA sources for sm_100a into csrc/libbop_b200.so (in-tree)."""
+  srcs = [os.path.join(CSRC, s) for s in SOURCES]
+  deps = srcs + [os.path.join(CSRC, h) for h in HEADERS]
+  if not force and os.path.exists(SO_PATH):
+    so_m = os.path.getmtime(SO_PATH)
+    if all(os.path.getmtime(d) <= so_m for d in deps):
+      return SO_PATH
+  cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
+         '-Xcompiler', '-fPIC', '-shared', '-o', SO_PATH] + srcs
+  if verbose:
+    cmd.insert(1, '-Xptxas=-v')
+  subprocess.check_call(cmd, cwd=CSRC)
+  return SO_PATH
+
+
+_P = ctypes.c_void_p
+_I = ctypes.c_int
+_SIGNATURES = {
+  'bop_abi_version': (_I, []),
+  'bop_last_error': (ctypes.c_char_p, []),
+  'bop_device_count': (_I, []),
+  'bop_kernel_launch_count': (ctypes.c_uint64, []),
+  'bop_re_te_dev': (_I, [_P, _P, _I, _P, _P, _P]),
+  'bop_re_te_host': (_I, [_P, _P, _I, _P, _P]),
+  'bop_mssd_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
+  'bop_mspd_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P]),
+  'bop_add_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
+  'bop_proj_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P]),
+  'bop_adi_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
+  'bop_render_workspace_bytes': (ctypes.c_size_t, [_I]),
+  'bop_render_depth_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, ctypes.c_size_t, _P]),
+  'bop_vsd_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I]),
+  'bop_vsd_from_depth_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P,
+                                   ctypes.c_size_t, _P]),
+  'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, ctypes.c_size_t,
+                       _P]),
+  'bop_model_upload': (_I, [_P, _I, _P, _I, _P, _I, ctypes.c_double, _P, _P]),
+  'bop_model_free': (_I, [_P, _P]),
+  'bop_mssd_host': (_I, [_P, _I, _P, _P, _I, _I, _P]),
+  'bop_mspd_host': (_I, [_P, _I, _P, _P, _P, _I, _P]),
+  'bop_add_host': (_I, [_P, _I, _P, _P, _I, _I, _P]),
+  'bop_adi_host': (_I, [_P, _I, _P, _P, _I, _I, _P]),
+  'bop_render_depth_host': (_I, [_P, _P, _P, _I, _I, _I, _P]),
+  'bop_vsd_host': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P]),
+  'bop_vsd_set_tuning': (_I, [_I, _I, _I, _I]),
+}
+EXPORTED_SYMBOLS = sorted(_SIGNATURES)
+
+_lib = None
+
+
+def lib():
+  """Returns the loaded library; raises ImportError if it has not been built."""
+  global _lib
+  if _lib is None:
+    if not os.path.exists(SO_PATH):
+      raise ImportError(
+        'bop_toolkit_b200: %s is missing. Build it with `python -c "import __graft_entry__ as g; '
+        'g.build()"` (needs nvcc). There is no CPU fallback.' % SO_PATH)
+    l = ctypes.CDLL(SO_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+      fn = getattr(l, name)
+      fn.restype = res
+      fn.argtypes = args
+    _lib = l
+  return _lib
+
+
+class BopCudaError(RuntimeError):
+  pass
+
+
+def check(rc):
+  if rc != 0:
+    msg = lib().bop_last_error().decode('utf-8', 'replace')
+    if msg in ('Unknown pixel matching cost.', 'Unknown visibility mode.'):
+      raise ValueError(msg)  # same exception types as the reference (pose_error.py:88)
+    raise BopCudaError('libbop_b200 call failed (rc=%d): %s' % (rc, msg))
+
+
+def require_cuda():
+  if lib().bop_device_count() <= 0:
+    raise BopCudaError('bop_toolkit_b200 needs a CUDA device (sm_100a); there is no CPU fallback.')

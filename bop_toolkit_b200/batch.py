@@ -1,0 +1,423 @@
+"""Batched pose-error API: whole shards of pose pairs per call, on one B200.
+
+This is the fast path the drop-in facade (pose_error.py) and the driver (eval_calc_errors.py)
+sit on.  torch is used for device memory, streams and pinned staging only; all arithmetic runs
+in the hand-written sm_100a kernels behind the C ABI (include/bop_b200.h).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _dev(device):
+  return torch.device(device if device is not None else 'cuda:0')
+
+
+def _stream_ptr():
+  return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def to_device(x, dtype, device, shape=None):
+  """numpy / torch / list -> contiguous device tensor of `dtype` (non-blocking when pinned)."""
+  if isinstance(x, torch.Tensor):
+    t = x
+  else:
+    t = torch.from_numpy(np.ascontiguousarray(x))
+  if t.dtype != dtype:
+    t = t.to(dtype)
+  if t.device != device:
+    t = t.to(device, non_blocking=True)
+  t = t.contiguous()
+  if shape is not None:
+    t = t.reshape(shape)
+  return t
+
+
+def pack_poses(Rs, ts):
+  """(R 3x3, t 3x1|3,) pairs -> [P,12] float64 array (R row-major then t)."""
+  Rs = np.asarray(Rs, dtype=np.float64).reshape(-1, 9)
+  ts = np.asarray(ts, dtype=np.float64).reshape(-1, 3)
+  return np.ascontiguousarray(np.hstack([Rs, ts]))
+
+
+def pack_syms(syms):
+  """List of {'R','t'} dicts (misc.get_symmetry_transformations) -> [S,12] float64."""
+  out = np.empty((len(syms), 12), dtype=np.float64)
+  for i, s in enumerate(syms):
+    out[i, :9] = np.asarray(s['R'], dtype=np.float64).reshape(9)
+    out[i, 9:] = np.asarray(s['t'], dtype=np.float64).reshape(3)
+  return out
+
+
+class ModelSet(object):
+  """Object models resident in HBM: the device-side counterpart of the reference's
+  `models[obj_id]` (inout.load_ply), `models_sym[obj_id]` (misc.get_symmetry_transformations),
+  `models_info[obj_id]['diameter']` and the renderer's vertex/index buffers
+  (scripts/eval_calc_errors.py:157-191).  Replicated per GPU (a 5k-vertex model is ~0.3 MB)."""
+
+  def __init__(self, device=None):
+    _lib.require_cuda()
+    self.device = _dev(device)
+    self._rows = []      # ModelDev structs
+    self._keep = []      # tensors kept alive
+    self._index = {}     # obj_id -> row
+    self._table = None
+    self.max_pts = 1
+    self.max_syms = 1
+    self.info = {}       # obj_id -> dict(n_pts, n_faces, n_syms, diameter)
+
+  def add(self, obj_id, pts, faces=None, syms=None, diameter=0.0):
+    """pts: Nx3 float64 as pose_error.* receives them; faces: Fx3 ints (needed for VSD /
+    rendering); syms: list of {'R','t'} or [S,12]; diameter: models_info 'diameter'."""
+    pts = np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 3))
+    n = pts.shape[0]
+    if n == 0:
+      raise ValueError('model without points')
+    p32 = pts.astype(np.float32)
+    f32_exact = bool(np.array_equal(p32.astype(np.float64), pts))
+    with torch.cuda.device(self.device):
+      if f32_exact:
+        d_pts = torch.from_numpy(p32).to(self.device)
+      else:
+        d_pts = torch.from_numpy(pts).to(self.device)
+      v4 = np.zeros((n, 4), dtype=np.float32)
+      v4[:, :3] = p32
+      d_v4 = torch.from_numpy(v4).to(self.device)
+      row = _lib.ModelDev()
+      row.pts = d_pts.data_ptr()
+      row.verts4 = d_v4.data_ptr()
+      row.pts_f64 = 0 if f32_exact else 1
+      row.n_pts = n
+      row.diameter = float(diameter)
+      keep = [d_pts, d_v4]
+      nf = 0
+      if faces is not None and len(faces):
+        faces = np.asarray(faces).astype(np.int64).reshape(-1, 3)
+        if faces.min() < 0 or faces.max() >= n:
+          raise ValueError('face index out of range')
+        nf = faces.shape[0]
+        f4 = np.zeros((nf, 4), dtype=np.int32)
+        f4[:, :3] = faces
+        d_f4 = torch.from_numpy(f4).to(self.device)
+        row.faces4 = d_f4.data_ptr()
+        row.n_faces = nf
+        keep.append(d_f4)
+      ns = 0
+      if syms is not None and len(syms):
+        s = pack_syms(syms) if isinstance(syms, (list, tuple)) else \
+          np.ascontiguousarray(np.asarray(syms, dtype=np.float64).reshape(-1, 12))
+        ns = s.shape[0]
+        d_s = torch.from_numpy(s).to(self.device)
+        row.syms = d_s.data_ptr()
+        row.n_syms = ns
+        keep.append(d_s)
+    if obj_id in self._index:
+      self._rows[self._index[obj_id]] = row
+    else:
+      self._index[obj_id] = len(self._rows)
+      self._rows.append(row)
+    self._keep.append(keep)
+    self.max_pts = max(self.max_pts, n)
+    self.max_syms = max(self.max_syms, ns)
+    self.info[obj_id] = dict(n_pts=n, n_faces=nf, n_syms=ns, diameter=float(diameter))
+    self._table = None
+    return self._index[obj_id]
+
+  def index_of(self, obj_id):
+    return self._index[obj_id]
+
+  def indices(self, obj_ids):
+    return np.fromiter((self._index[o] for o in obj_ids), dtype=np.int32, count=len(obj_ids))
+
+  def __contains__(self, obj_id):
+    return obj_id in self._index
+
+  @property
+  def table(self):
+    """Device copy of the bop_model_dev table."""
+    if self._table is None:
+      buf = b''.join(bytes(r) for r in self._rows)
+      host = torch.frombuffer(bytearray(buf), dtype=torch.uint8)
+      self._table = host.to(self.device)
+    return self._table
+
+
+class Workspace(object):
+  """Grow-only device scratch buffer (256-byte aligned by the caching allocator)."""
+
+  def __init__(self, device):
+    self.device = device
+    self.buf = None
+
+  def get(self, nbytes):
+    if self.buf is None or self.buf.numel() < nbytes:
+      self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+    return self.buf
+
+
+_workspaces = {}
+
+
+def _workspace(device, nbytes):
+  key = (device.type, device.index)
+  ws = _workspaces.get(key)
+  if ws is None:
+    ws = _workspaces[key] = Workspace(device)
+  return ws.get(nbytes)
+
+
+def _obj_idx(models, obj, n):
+  if isinstance(obj, (int, np.integer)):
+    return torch.full((n,), int(obj), dtype=torch.int32, device=models.device)
+  return to_device(obj, torch.int32, models.device, (n,))
+
+
+def _poses(models, pe, pg):
+  pe = to_device(pe, torch.float64, models.device)
+  pg = to_device(pg, torch.float64, models.device)
+  if pe.numel() % 12 or pe.shape != pg.shape:
+    raise ValueError('poses must be [P,12] (R row-major, then t)')
+  return pe, pg, pe.numel() // 12
+
+
+def re_te_batch(pose_est, pose_gt, device=None):
+  """pose_error.re / te for P pairs -> (re[P] deg, te[P] mm) device tensors."""
+  _lib.require_cuda()
+  dev = _dev(device)
+  pe = to_device(pose_est, torch.float64, dev)
+  pg = to_device(pose_gt, torch.float64, dev)
+  n = pe.numel() // 12
+  re = torch.empty(n, dtype=torch.float64, device=dev)
+  te = torch.empty(n, dtype=torch.float64, device=dev)
+  with torch.cuda.device(dev):
+    _lib.check(_lib.lib().bop_re_te_dev(pe.data_ptr(), pg.data_ptr(), n, re.data_ptr(),
+                                        te.data_ptr(), _stream_ptr()))
+  return re, te
+
+
+def _points_call(fn_name, models, obj, pose_est, pose_gt, K, max_n, gate):
+  pe, pg, n = _poses(models, pose_est, pose_gt)
+  oi = _obj_idx(models, obj, n)
+  out = torch.empty(n, dtype=torch.float64, device=models.device)
+  fn = getattr(_lib.lib(), fn_name)
+  with torch.cuda.device(models.device):
+    if K is not None:
+      Kd = to_device(K, torch.float64, models.device)
+      if Kd.numel() == 9:
+        Kd = Kd.reshape(1, 9).expand(n, 9).contiguous()
+      if Kd.numel() != 9 * n:
+        raise ValueError('K must be [P,9] or a single 3x3')
+      rc = fn(models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), Kd.data_ptr(),
+              n, int(max_n), out.data_ptr(), _stream_ptr())
+    else:
+      rc = fn(models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), n,
+              int(max_n), int(bool(gate)), out.data_ptr(), _stream_ptr())
+  _lib.check(rc)
+  return out
+
+
+def mssd_batch(models, obj, pose_est, pose_gt, gate=False):
+  """pose_error.mssd for P pairs; gate=True applies the driver's sphere gate (-> inf)."""
+  return _points_call('bop_mssd_dev', models, obj, pose_est, pose_gt, None, models.max_syms, gate)
+
+
+def mspd_batch(models, obj, pose_est, pose_gt, K):
+  """pose_error.mspd for P pairs; K: [P,9] per pair or one 3x3."""
+  return _points_call('bop_mspd_dev', models, obj, pose_est, pose_gt, K, models.max_syms, False)
+
+
+def add_batch(models, obj, pose_est, pose_gt, gate=False):
+  return _points_call('bop_add_dev', models, obj, pose_est, pose_gt, None, models.max_pts, gate)
+
+
+def adi_batch(models, obj, pose_est, pose_gt, gate=False):
+  return _points_call('bop_adi_dev', models, obj, pose_est, pose_gt, None, models.max_pts, gate)
+
+
+def proj_batch(models, obj, pose_est, pose_gt, K):
+  return _points_call('bop_proj_dev', models, obj, pose_est, pose_gt, K, models.max_pts, False)
+
+
+def make_vsd_params(height, width, delta, taus, normalized_by_diameter=True, cost_type='step',
+                    visib_mode='bop19', gate=False, depth_dtype=_lib.DEPTH_F32):
+  if cost_type not in _lib.COST_TYPES:
+    raise ValueError('Unknown pixel matching cost.')  # pose_error.py:88
+  if visib_mode not in _lib.VISIB_MODES:
+    raise ValueError('Unknown visibility mode.')      # visibility.py:40
+  taus = [float(t) for t in taus]
+  if not 1 <= len(taus) <= _lib.BOP_MAX_TAUS:
+    raise ValueError('between 1 and %d taus per launch' % _lib.BOP_MAX_TAUS)
+  p = _lib.VsdParams()
+  for i, t in enumerate(taus):
+    p.taus[i] = t
+  p.delta = float(delta)
+  p.n_taus = len(taus)
+  p.normalized_by_diameter = int(bool(normalized_by_diameter))
+  p.cost_type = _lib.COST_TYPES[cost_type]
+  p.visib_mode = _lib.VISIB_MODES[visib_mode]
+  p.height, p.width = int(height), int(width)
+  p.gate = int(bool(gate))
+  p.depth_dtype = depth_dtype
+  return p
+
+
+def _depth_input(depth_test, device):
+  if isinstance(depth_test, np.ndarray):
+    depth_test = torch.from_numpy(np.ascontiguousarray(depth_test))
+  if depth_test.dtype == torch.uint16 or depth_test.dtype == torch.int16:
+    dd, code = depth_test.view(torch.int16), _lib.DEPTH_U16
+  else:
+    dd, code = depth_test.to(torch.float32), _lib.DEPTH_F32
+  if dd.dim() == 2:
+    dd = dd.unsqueeze(0)
+  if dd.device != device:
+    dd = dd.to(device, non_blocking=True)
+  return dd.contiguous(), code
+
+
+def _tau_chunks(taus):
+  taus = list(taus)
+  return [taus[i:i + _lib.BOP_MAX_TAUS] for i in range(0, len(taus), _lib.BOP_MAX_TAUS)]
+
+
+def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus,
+              normalized_by_diameter=True, cost_type='step', visib_mode='bop19', gate=False,
+              depth_scale=None, return_counts=False, diameter_override=None):
+  """pose_error.vsd for P pairs with the fused raster + pixel-pass kernel.
+
+  depth_test: [n_im,H,W] float32 mm (or uint16 raw + depth_scale[n_im]); im_idx: [P] image of
+  each pair (None = pair i uses image i); K: [n_im,9].  Returns errors [P,len(taus)] float64
+  (device tensor) and, if return_counts, int64 [P,2+T] = union, inter, step-cost counts.
+  """
+  pe, pg, n = _poses(models, pose_est, pose_gt)
+  dev = models.device
+  oi = _obj_idx(models, obj, n)
+  dd, code = _depth_input(depth_test, dev)
+  n_im, H, W = dd.shape
+  Kd = to_device(K, torch.float64, dev).reshape(-1, 9)
+  if Kd.shape[0] != n_im:
+    if Kd.shape[0] == 1:
+      Kd = Kd.expand(n_im, 9).contiguous()
+    else:
+      raise ValueError('K must be [n_im,9]')
+  if im_idx is None:
+    if n_im == 1:
+      ii = torch.zeros(n, dtype=torch.int32, device=dev)
+    else:
+      ii = torch.arange(n, dtype=torch.int32, device=dev)
+  else:
+    ii = to_device(im_idx, torch.int32, dev, (n,))
+  sc = None
+  if code == _lib.DEPTH_U16:
+    if depth_scale is None:
+      depth_scale = np.ones(n_im, dtype=np.float32)
+    sc = to_device(depth_scale, torch.float32, dev, (n_im,))
+  diam = None
+  if diameter_override is not None:
+    if isinstance(diameter_override, torch.Tensor):
+      diam = to_device(diameter_override, torch.float64, dev, (n,))
+    else:
+      diam = to_device(np.ascontiguousarray(np.broadcast_to(
+        np.asarray(diameter_override, dtype=np.float64), (n,))), torch.float64, dev, (n,))
+  outs, cnts = [], []
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W)
+  ws = _workspace(dev, wsb)
+  with torch.cuda.device(dev):
+    for chunk in _tau_chunks(taus):
+      prm = make_vsd_params(H, W, delta, chunk, normalized_by_diameter, cost_type, visib_mode,
+                            gate, code)
+      err = torch.empty((n, len(chunk)), dtype=torch.float64, device=dev)
+      cnt = torch.empty((n, 2 + len(chunk)), dtype=torch.int64, device=dev) if return_counts else None
+      rc = _lib.lib().bop_vsd_dev(
+        models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
+        sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
+        diam.data_ptr() if diam is not None else None, n,
+        ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
+        ws.data_ptr(), wsb, _stream_ptr())
+      _lib.check(rc)
+      outs.append(err)
+      cnts.append(cnt)
+  err = outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
+  if return_counts:
+    cnt = cnts[0] if len(cnts) == 1 else torch.cat([cnts[0]] + [c[:, 2:] for c in cnts[1:]], dim=1)
+    return err, cnt
+  return err
+
+
+def vsd_from_depth_batch(depth_est, depth_gt, depth_test, im_idx, K, diameters, delta, taus,
+                         normalized_by_diameter=True, cost_type='step', visib_mode='bop19',
+                         depth_scale=None, return_counts=False, device=None):
+  """K2 alone: pose_error.vsd lines 48-91 on pre-rendered depth images [P,H,W] float32."""
+  _lib.require_cuda()
+  dev = _dev(device if device is not None else
+             (depth_est.device if isinstance(depth_est, torch.Tensor) and depth_est.is_cuda else None))
+  de = to_device(depth_est, torch.float32, dev)
+  dg = to_device(depth_gt, torch.float32, dev)
+  if de.dim() == 2:
+    de, dg = de.unsqueeze(0), dg.unsqueeze(0)
+  n, H, W = de.shape
+  dd, code = _depth_input(depth_test, dev)
+  n_im = dd.shape[0]
+  Kd = to_device(K, torch.float64, dev).reshape(-1, 9)
+  if Kd.shape[0] == 1 and n_im > 1:
+    Kd = Kd.expand(n_im, 9).contiguous()
+  if im_idx is None:
+    ii = torch.zeros(n, dtype=torch.int32, device=dev) if n_im == 1 else \
+      torch.arange(n, dtype=torch.int32, device=dev)
+  else:
+    ii = to_device(im_idx, torch.int32, dev, (n,))
+  diam = to_device(np.broadcast_to(np.asarray(diameters, dtype=np.float64), (n,)) if not
+                   isinstance(diameters, torch.Tensor) else diameters, torch.float64, dev, (n,))
+  sc = None
+  if code == _lib.DEPTH_U16:
+    sc = to_device(depth_scale if depth_scale is not None else np.ones(n_im, np.float32),
+                   torch.float32, dev, (n_im,))
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W)
+  ws = _workspace(dev, wsb)
+  outs, cnts = [], []
+  with torch.cuda.device(dev):
+    for chunk in _tau_chunks(taus):
+      prm = make_vsd_params(H, W, delta, chunk, normalized_by_diameter, cost_type, visib_mode,
+                            False, code)
+      err = torch.empty((n, len(chunk)), dtype=torch.float64, device=dev)
+      cnt = torch.empty((n, 2 + len(chunk)), dtype=torch.int64, device=dev) if return_counts else None
+      rc = _lib.lib().bop_vsd_from_depth_dev(
+        dd.data_ptr(), sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
+        de.data_ptr(), dg.data_ptr(), diam.data_ptr(), n, ctypes.byref(prm), err.data_ptr(),
+        cnt.data_ptr() if cnt is not None else None, ws.data_ptr(), wsb, _stream_ptr())
+      _lib.check(rc)
+      outs.append(err)
+      cnts.append(cnt)
+  err = outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
+  if return_counts:
+    cnt = cnts[0] if len(cnts) == 1 else torch.cat([cnts[0]] + [c[:, 2:] for c in cnts[1:]], dim=1)
+    return err, cnt
+  return err
+
+
+def render_batch(models, obj, poses, cams, height, width):
+  """Renderer.render_object ('depth' mode) for B poses -> [B,H,W] float32 device tensor.
+  cams: [B,4] or [4] = fx, fy, cx, cy."""
+  dev = models.device
+  p = to_device(poses, torch.float64, dev)
+  n = p.numel() // 12
+  oi = _obj_idx(models, obj, n)
+  c = to_device(cams, torch.float64, dev)
+  if c.numel() == 4:
+    c = c.reshape(1, 4).expand(n, 4).contiguous()
+  out = torch.empty((n, int(height), int(width)), dtype=torch.float32, device=dev)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, int(height), int(width))
+  ws = _workspace(dev, wsb)
+  with torch.cuda.device(dev):
+    rc = _lib.lib().bop_render_depth_dev(models.table.data_ptr(), oi.data_ptr(), p.data_ptr(),
+                                         c.data_ptr(), n, int(height), int(width), out.data_ptr(),
+                                         ws.data_ptr(), wsb, _stream_ptr())
+  _lib.check(rc)
+  return out
+
+
+def kernel_launch_count():
+  return int(_lib.lib().bop_kernel_launch_count())

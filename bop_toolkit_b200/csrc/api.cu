@@ -115,3 +115,142 @@ extern "C" int bop_model_free(bop_model_dev* desc_host, bop_model_dev* desc_dev)
   if (desc_dev) cudaFree(desc_dev);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------
+// Host-buffer layer.  Simple synchronous staging: cudaMalloc + cudaMemcpy around the `_dev`
+// entry points, on the legacy default stream.  (The Python package stages through torch's
+// caching allocator and pinned memory instead; this layer is for bindings without torch.)
+// ---------------------------------------------------------------------------------
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  int alloc(size_t bytes) {
+    BOP_CUDA(cudaMalloc(&p, bytes ? bytes : 1));
+    return 0;
+  }
+  int upload(const void* h, size_t bytes) {
+    if (int rc = alloc(bytes)) return rc;
+    if (bytes) BOP_CUDA(cudaMemcpy(p, h, bytes, cudaMemcpyHostToDevice));
+    return 0;
+  }
+  template <typename T> T* as() { return (T*)p; }
+};
+
+int download(void* h, const void* d, size_t bytes) {
+  BOP_CUDA(cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int zeros_i32(DevBuf& b, int n) {
+  if (int rc = b.alloc(sizeof(int32_t) * (size_t)n)) return rc;
+  BOP_CUDA(cudaMemset(b.p, 0, sizeof(int32_t) * (size_t)n));
+  return 0;
+}
+
+#define RC(x) do { if (int _rc = (x)) return _rc; } while (0)
+
+}  // namespace
+
+extern "C" int bop_re_te_host(const double* pose_est, const double* pose_gt, int n_pairs,
+                              double* re_out, double* te_out) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(bop_device_count() > 0, "no CUDA device (there is no CPU fallback)");
+  const size_t pb = sizeof(double) * 12 * (size_t)n_pairs, ob = sizeof(double) * (size_t)n_pairs;
+  DevBuf pe, pg, re, te;
+  RC(pe.upload(pose_est, pb)); RC(pg.upload(pose_gt, pb));
+  RC(re.alloc(ob)); RC(te.alloc(ob));
+  RC(bop_re_te_dev(pe.as<double>(), pg.as<double>(), n_pairs, re_out ? re.as<double>() : nullptr,
+                   te_out ? te.as<double>() : nullptr, nullptr));
+  if (re_out) RC(download(re_out, re.p, ob));
+  if (te_out) RC(download(te_out, te.p, ob));
+  return 0;
+}
+
+namespace {
+// kind: 0 mssd, 1 mspd, 2 add, 3 adi
+int points_host(int kind, const bop_model_dev* model_dev, int max_n, const double* pose_est,
+                const double* pose_gt, const double* K, int n_pairs, int gate, double* out) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(bop_device_count() > 0, "no CUDA device (there is no CPU fallback)");
+  BOP_REQUIRE(model_dev && pose_est && pose_gt && out, "null pointer");
+  const size_t pb = sizeof(double) * 12 * (size_t)n_pairs, ob = sizeof(double) * (size_t)n_pairs;
+  DevBuf pe, pg, kk, oi, o;
+  RC(pe.upload(pose_est, pb)); RC(pg.upload(pose_gt, pb));
+  RC(zeros_i32(oi, n_pairs)); RC(o.alloc(ob));
+  if (kind == 1) {
+    BOP_REQUIRE(K, "null K");
+    RC(kk.upload(K, sizeof(double) * 9 * (size_t)n_pairs));
+  }
+  switch (kind) {
+    case 0: RC(bop_mssd_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), n_pairs, max_n, gate, o.as<double>(), nullptr)); break;
+    case 1: RC(bop_mspd_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), kk.as<double>(), n_pairs, max_n, o.as<double>(), nullptr)); break;
+    case 2: RC(bop_add_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), n_pairs, max_n, gate, o.as<double>(), nullptr)); break;
+    default: RC(bop_adi_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), n_pairs, max_n, gate, o.as<double>(), nullptr)); break;
+  }
+  return download(out, o.p, ob);
+}
+}  // namespace
+
+extern "C" int bop_mssd_host(const bop_model_dev* model_dev, int n_syms, const double* pose_est,
+                             const double* pose_gt, int n_pairs, int gate, double* out) {
+  return points_host(0, model_dev, n_syms, pose_est, pose_gt, nullptr, n_pairs, gate, out);
+}
+extern "C" int bop_mspd_host(const bop_model_dev* model_dev, int n_syms, const double* pose_est,
+                             const double* pose_gt, const double* K, int n_pairs, double* out) {
+  return points_host(1, model_dev, n_syms, pose_est, pose_gt, K, n_pairs, 0, out);
+}
+extern "C" int bop_add_host(const bop_model_dev* model_dev, int n_pts, const double* pose_est,
+                            const double* pose_gt, int n_pairs, int gate, double* out) {
+  return points_host(2, model_dev, n_pts, pose_est, pose_gt, nullptr, n_pairs, gate, out);
+}
+extern "C" int bop_adi_host(const bop_model_dev* model_dev, int n_pts, const double* pose_est,
+                            const double* pose_gt, int n_pairs, int gate, double* out) {
+  return points_host(3, model_dev, n_pts, pose_est, pose_gt, nullptr, n_pairs, gate, out);
+}
+
+extern "C" int bop_render_depth_host(const bop_model_dev* model_dev, const double* pose,
+                                     const double* cam, int n, int height, int width,
+                                     float* depth_out) {
+  if (n <= 0) return 0;
+  BOP_REQUIRE(bop_device_count() > 0, "no CUDA device (there is no CPU fallback)");
+  BOP_REQUIRE(model_dev && pose && cam && depth_out, "null pointer");
+  DevBuf p, c, oi, o, ws;
+  const size_t ob = sizeof(float) * (size_t)n * height * width;
+  RC(p.upload(pose, sizeof(double) * 12 * (size_t)n));
+  RC(c.upload(cam, sizeof(double) * 4 * (size_t)n));
+  RC(zeros_i32(oi, n)); RC(o.alloc(ob));
+  const size_t wsb = bop_vsd_workspace_bytes(n, height, width);
+  RC(ws.alloc(wsb));
+  RC(bop_render_depth_dev(model_dev, oi.as<int32_t>(), p.as<double>(), c.as<double>(), n, height,
+                          width, o.as<float>(), ws.p, wsb, nullptr));
+  return download(depth_out, o.p, ob);
+}
+
+extern "C" int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_est,
+                            const double* pose_gt, const void* depth_test,
+                            const float* depth_scale, const int32_t* im_idx, const double* K,
+                            int n_im, int n_pairs, const bop_vsd_params* prm, double* errors_out) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(bop_device_count() > 0, "no CUDA device (there is no CPU fallback)");
+  BOP_REQUIRE(model_dev && pose_est && pose_gt && depth_test && im_idx && K && prm && errors_out && n_im > 0,
+              "null pointer");
+  const size_t px = (size_t)prm->height * prm->width;
+  const size_t db = px * (size_t)n_im * (prm->depth_dtype == BOP_DEPTH_U16 ? 2 : 4);
+  const size_t pb = sizeof(double) * 12 * (size_t)n_pairs;
+  const size_t eb = sizeof(double) * (size_t)n_pairs * prm->n_taus;
+  DevBuf pe, pg, d, sc, ii, kk, oi, e, ws;
+  RC(pe.upload(pose_est, pb)); RC(pg.upload(pose_gt, pb));
+  RC(d.upload(depth_test, db));
+  if (depth_scale) RC(sc.upload(depth_scale, sizeof(float) * (size_t)n_im));
+  RC(ii.upload(im_idx, sizeof(int32_t) * (size_t)n_pairs));
+  RC(kk.upload(K, sizeof(double) * 9 * (size_t)n_im));
+  RC(zeros_i32(oi, n_pairs)); RC(e.alloc(eb));
+  const size_t wsb = bop_vsd_workspace_bytes(n_pairs, prm->height, prm->width);
+  RC(ws.alloc(wsb));
+  RC(bop_vsd_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), d.p,
+                 depth_scale ? sc.as<float>() : nullptr, ii.as<int32_t>(), kk.as<double>(), nullptr, n_pairs,
+                 prm, e.as<double>(), nullptr, ws.p, wsb, nullptr));
+  return download(errors_out, e.p, eb);
+}

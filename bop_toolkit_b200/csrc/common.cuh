@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #include "../../include/bop_b200.h"
 
@@ -78,6 +79,3 @@ __device__ __forceinline__ void mat3_vec(const double* A, const double* v, doubl
   for (int i = 0; i < 3; ++i) o[i] = A[i * 3 + 0] * v[0] + A[i * 3 + 1] * v[1] + A[i * 3 + 2] * v[2];
 }
 
-// Internal launchers shared between api.cu and the kernel translation units.
-int bop_launch_re_te(const double* pe, const double* pg, int n, double* re, double* te,
-                     cudaStream_t s);

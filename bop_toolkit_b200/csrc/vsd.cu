@@ -1,0 +1,884 @@
+// K1 (batched depth rasteriser), K2 (fused depth->dist + visibility + tau sweep) and the fused
+// K1+K2 VSD kernel for sm_100a.
+//
+// Reference path: pose_error.vsd (bop_toolkit_lib/pose_error.py:17-93) =
+//   2x Renderer.render_object (renderer_vispy.py:433-466,509-538)
+//   3x misc.depth_im_to_dist_im_fast (misc.py:143-163)
+//   visibility.estimate_visib_mask_gt / _est (visibility.py:9-75)
+//   intersection / union / per-tau cost (pose_error.py:61-91)
+//
+// Fused design: a pose pair never materialises its two rendered depth images in HBM.  A
+// persistent CTA pulls (pair, row-band) work items from a device-side list, rasterises both poses
+// of the band into shared-memory z-tiles (atomicMin on float-as-uint depth), then streams the
+// matching rows of depth_test once (128-bit loads) and reduces (union, inter, per-tau cost) with
+// warp shuffles + shared atomics + one global atomic per counter.  The pixel arithmetic mirrors
+// the reference's dtype ladder operation by operation, so given equal rendered
+// depths the integer counts -- and hence the errors -- are bit-identical to numpy's.
+#include "raster.cuh"
+
+namespace {
+
+constexpr int kMinTilePx = 4096;
+constexpr int kMaxWidth = 4096;
+
+struct Tuning {
+  int tile_px = 24576;   // z-tile capacity per pose, pixels (2 poses x 4 B = 192 KB of smem)
+  int threads = 512;
+  int ctas_per_sm = 1;
+  int small_tri_px = 36; // triangles with more candidate pixels go to the warp-cooperative path
+};
+Tuning g_tune;
+
+struct PairDesc {
+  PoseCamF pose[2];       // 0 = est, 1 = gt
+  double kfx, kfy, kcx, kcy;
+  double diameter;
+  int x0, y0, w, h;       // union ROI; x0 and w are multiples of 4
+  int obj, im;
+  int n_poses, pad;
+};
+
+struct WorkItem {
+  int pair, row0, nrows, pad;
+};
+
+struct PlanCounters {
+  unsigned total;  // number of work items
+  unsigned next;   // persistent-CTA ticket
+};
+
+// overlapping_sphere_projections (bop_toolkit_lib/misc.py:309-331), float64.
+__device__ __forceinline__ bool sphere_projections_overlap(double radius, const double* p1,
+                                                           const double* p2) {
+  if (p1[2] == 0.0 || p2[2] == 0.0) return false;
+  const double ax = p1[0] / p1[2], ay = p1[1] / p1[2];
+  const double bx = p2[0] / p2[2], by = p2[1] / p2[2];
+  const double dx = ax - bx, dy = ay - by;
+  const double dist = sqrt(dx * dx + dy * dy);
+  const double thresh = radius * (1.0 / p1[2] + 1.0 / p2[2]);
+  return dist < thresh;
+}
+
+__device__ __forceinline__ void make_posecam(const double* pose, double fx, double fy, double cx,
+                                             double cy, PoseCamF& P) {
+#pragma unroll
+  for (int k = 0; k < 9; ++k) P.r[k] = (float)pose[k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) P.t[k] = (float)pose[9 + k];
+  P.fx = (float)fx;
+  P.fy = (float)fy;
+  P.cxh = (float)(cx - 0.5);
+  P.cyh = (float)(cy - 0.5);
+}
+
+// ---------------------------------------------------------------------------------
+// Pass A: exact projected bounding box per (item, pose).  One warp per (item, pose).
+// cam_mode 0: K is [n_im][9] indexed through im_idx (VSD); 1: cam is [n][4] fx,fy,cx,cy (render).
+// bbox out: [n][n_poses][4] = x0,y0,x1,y1 inclusive, clipped to the image; empty => x1 < x0.
+// ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bbox_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
+            const double* __restrict__ pose_a, const double* __restrict__ pose_b,
+            const int32_t* __restrict__ im_idx, const double* __restrict__ K,
+            const double* __restrict__ diameters, int cam_mode, int n,
+            int n_poses, int H, int W, int gate, int4* __restrict__ bbox) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= n * n_poses) return;
+  const int item = gw / n_poses, which = gw - item * n_poses;
+  const bop_model_dev M = models[obj_idx[item]];
+  const double* pose = (which == 0 ? pose_a : pose_b) + 12 * (size_t)item;
+  if (gate && n_poses == 2) {
+    const double* pe = pose_a + 12 * (size_t)item;
+    const double* pg = pose_b + 12 * (size_t)item;
+    const double diam = diameters ? diameters[item] : M.diameter;
+    if (!sphere_projections_overlap(0.5 * diam, pe + 9, pg + 9)) {
+      if (lane == 0) bbox[gw] = make_int4(0, 0, -1, -1);
+      return;
+    }
+  }
+  double fx, fy, cx, cy;
+  if (cam_mode == 0) {
+    const double* Kp = K + 9 * (size_t)im_idx[item];
+    fx = Kp[0]; fy = Kp[4]; cx = Kp[2]; cy = Kp[5];
+  } else {
+    const double* c = K + 4 * (size_t)item;
+    fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
+  }
+  PoseCamF P;
+  make_posecam(pose, fx, fy, cx, cy, P);
+  const float4* __restrict__ verts = (const float4*)M.verts4;
+  float minx = 3e38f, miny = 3e38f, maxx = -3e38f, maxy = -3e38f;
+  for (int i = lane; i < M.n_pts; i += 32) {
+    Vtx v;
+    if (project_vertex(P, __ldg(verts + i), v)) {
+      minx = fminf(minx, v.x); maxx = fmaxf(maxx, v.x);
+      miny = fminf(miny, v.y); maxy = fmaxf(maxy, v.y);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    minx = fminf(minx, __shfl_xor_sync(BOP_FULL_MASK, minx, o));
+    miny = fminf(miny, __shfl_xor_sync(BOP_FULL_MASK, miny, o));
+    maxx = fmaxf(maxx, __shfl_xor_sync(BOP_FULL_MASK, maxx, o));
+    maxy = fmaxf(maxy, __shfl_xor_sync(BOP_FULL_MASK, maxy, o));
+  }
+  if (lane == 0) {
+    int4 b;
+    b.x = max(0, (int)ceilf(fmaxf(minx, -1.0e6f)));
+    b.y = max(0, (int)ceilf(fmaxf(miny, -1.0e6f)));
+    b.z = min(W - 1, (int)floorf(fminf(maxx, 1.0e6f)));
+    b.w = min(H - 1, (int)floorf(fminf(maxy, 1.0e6f)));
+    if (b.z < b.x || b.w < b.y) b = make_int4(0, 0, -1, -1);
+    bbox[gw] = b;
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// Pass B: one thread per item: build the descriptor, split the union ROI into row bands that fit
+// the z-tile and append them to the work list (one atomicAdd per item).
+// ---------------------------------------------------------------------------------
+__global__ void plan_kernel(const bop_model_dev* __restrict__ models,
+                            const int32_t* __restrict__ obj_idx, const double* __restrict__ pose_a,
+                            const double* __restrict__ pose_b, const int32_t* __restrict__ im_idx,
+                            const double* __restrict__ K, const double* __restrict__ diameters,
+                            int cam_mode, int n, int n_poses, int H,
+                            int W, int tile_px, const int4* __restrict__ bbox,
+                            PairDesc* __restrict__ desc, WorkItem* __restrict__ work,
+                            PlanCounters* __restrict__ ctr, unsigned max_items) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  PairDesc D;
+  const int obj = obj_idx[i];
+  D.obj = obj;
+  D.diameter = diameters ? diameters[i] : models[obj].diameter;
+  D.n_poses = n_poses;
+  D.pad = 0;
+  double fx, fy, cx, cy;
+  if (cam_mode == 0) {
+    D.im = im_idx[i];
+    const double* Kp = K + 9 * (size_t)D.im;
+    fx = Kp[0]; fy = Kp[4]; cx = Kp[2]; cy = Kp[5];
+  } else {
+    D.im = i;
+    const double* c = K + 4 * (size_t)i;
+    fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
+  }
+  D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
+  make_posecam(pose_a + 12 * (size_t)i, fx, fy, cx, cy, D.pose[0]);
+  if (n_poses == 2) make_posecam(pose_b + 12 * (size_t)i, fx, fy, cx, cy, D.pose[1]);
+  else D.pose[1] = D.pose[0];
+  int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
+  for (int p = 0; p < n_poses; ++p) {
+    const int4 b = bbox[i * n_poses + p];
+    if (b.z >= b.x) {
+      x0 = min(x0, b.x); y0 = min(y0, b.y); x1 = max(x1, b.z); y1 = max(y1, b.w);
+    }
+  }
+  int nb = 0, band = 0;
+  if (x1 >= x0) {
+    x0 &= ~3;
+    const int w = ((x1 + 1 - x0) + 3) & ~3;
+    const int h = y1 + 1 - y0;
+    D.x0 = x0; D.y0 = y0; D.w = w; D.h = h;
+    const int cap_rows = max(1, tile_px / w);
+    nb = (h + cap_rows - 1) / cap_rows;
+    band = (h + nb - 1) / nb;  // balanced bands
+  } else {
+    D.x0 = D.y0 = D.w = D.h = 0;
+  }
+  desc[i] = D;
+  if (nb > 0) {
+    const unsigned start = atomicAdd(&ctr->total, (unsigned)nb);
+    for (int b = 0; b < nb; ++b) {
+      if (start + b >= max_items) break;  // cannot happen with the documented workspace size
+      WorkItem wi;
+      wi.pair = i;
+      wi.row0 = b * band;
+      wi.nrows = min(band, D.h - b * band);
+      wi.pad = 0;
+      work[start + b] = wi;
+    }
+  }
+}
+
+}  // namespace
+
+// =====================================================================================
+// Pixel arithmetic shared by the fused kernel and the stand-alone K2 pass.
+// =====================================================================================
+namespace {
+
+struct PixParams {
+  double taus[BOP_MAX_TAUS];
+  float delta_f32;   // `d_diff <= delta` is a float32 comparison (visibility.py:35-37, NEP 50)
+  int n_taus;
+  int normalized;
+  int visib_mode;
+  int H, W;
+  int depth_dtype;
+  int vec_ok;        // rows of depth_test are 16-byte (f32) / 8-byte (u16) aligned
+};
+
+constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2;
+
+template <int MODE>
+struct Acc {
+  int uni = 0, inter = 0;
+  int c[BOP_MAX_TAUS];
+  __device__ Acc() {
+#pragma unroll
+    for (int k = 0; k < BOP_MAX_TAUS; ++k) c[k] = 0;
+  }
+};
+template <>
+struct Acc<MODE_TLINEAR> {
+  int uni = 0, inter = 0;
+  double c[BOP_MAX_TAUS];
+  __device__ Acc() {
+#pragma unroll
+    for (int k = 0; k < BOP_MAX_TAUS; ++k) c[k] = 0.0;
+  }
+};
+
+// misc.depth_im_to_dist_im_fast (misc.py:158-161): sqrt((X*d)^2 + (Y*d)^2 + d^2) in float64,
+// every product and sum rounded separately (numpy does not contract to FMA).
+__device__ __forceinline__ double dist_of(double X, double Y, float d) {
+  const double dd = (double)d;
+  const double a = __dmul_rn(X, dd), b = __dmul_rn(Y, dd);
+  return __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(a, a), __dmul_rn(b, b)), __dmul_rn(dd, dd)));
+}
+
+// One pixel of pose_error.vsd lines 48-91.  dt/de/dg: depth_test, rendered est, rendered gt.
+template <int MODE>
+__device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double Y, float dt,
+                                          float de, float dg, double diameter, Acc<MODE>& acc) {
+  const bool he = de != 0.f, hg = dg != 0.f;   // d_model > 0 on the distance image
+  if (!he && !hg) return;
+  const double Dt = dist_of(X, Y, dt);
+  const float Dt32 = (float)Dt;
+  const bool t_zero = Dt == 0.0, t_pos = Dt > 0.0;
+  double Dg = 0.0, De = 0.0;
+  bool vg = false, ve = false;
+  if (hg) {
+    Dg = dist_of(X, Y, dg);
+    const bool c = __fsub_rn((float)Dg, Dt32) <= pp.delta_f32;
+    vg = (pp.visib_mode == BOP_VISIB_BOP19) ? (c || t_zero) : (c && t_pos);
+  }
+  if (he) {
+    De = dist_of(X, Y, de);
+    const bool c = __fsub_rn((float)De, Dt32) <= pp.delta_f32;
+    ve = (pp.visib_mode == BOP_VISIB_BOP19) ? (c || t_zero) : (c && t_pos);
+    ve = ve || vg;   // visibility.py:74: OR (visib_gt AND d_est > 0)
+  }
+  if (!(vg || ve)) return;
+  acc.uni += 1;
+  if (vg && ve) {
+    acc.inter += 1;
+    double d = fabs(__dsub_rn(Dg, De));
+    if (pp.normalized) d = __ddiv_rn(d, diameter);
+#pragma unroll
+    for (int k = 0; k < BOP_MAX_TAUS; ++k) {
+      if (k < pp.n_taus) {
+        if (MODE == MODE_TLINEAR) {
+          double c = __ddiv_rn(d, pp.taus[k]);
+          acc.c[k] += (c > 1.0) ? 1.0 : c;
+        } else {
+          acc.c[k] += (d >= pp.taus[k]) ? 1 : 0;
+        }
+      }
+    }
+  }
+}
+
+// Loads 4 horizontally adjacent depth_test samples as float32 millimetres.
+__device__ __forceinline__ void load_depth4(const PixParams& pp, const void* __restrict__ depth,
+                                            float scale, int im, int row, int col, float out[4]) {
+  const size_t base = ((size_t)im * pp.H + row) * (size_t)pp.W + col;
+  if (pp.depth_dtype == BOP_DEPTH_F32) {
+    const float* p = (const float*)depth + base;
+    if (pp.vec_ok && col + 3 < pp.W) {
+      const float4 v = ld_stream_f4(p);
+      out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = v.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) out[k] = (col + k < pp.W) ? __ldg(p + k) : 0.f;
+    }
+  } else {
+    const unsigned short* p = (const unsigned short*)depth + base;
+    unsigned short u[4];
+    if (pp.vec_ok && col + 3 < pp.W) {
+      const uint2 v = ld_stream_u2(p);
+      u[0] = v.x & 0xffff; u[1] = v.x >> 16; u[2] = v.y & 0xffff; u[3] = v.y >> 16;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) u[k] = (col + k < pp.W) ? __ldg(p + k) : 0;
+    }
+    // depth_im (float32) *= depth_scale  (scripts/eval_calc_errors.py:243): float32 product.
+#pragma unroll
+    for (int k = 0; k < 4; ++k) out[k] = __fmul_rn((float)u[k], scale);
+  }
+}
+
+}  // namespace
+
+// =====================================================================================
+// Fused persistent kernel: rasterise (K1) + pixel pass (K2) per (pair, row band).
+// MODE_RENDER writes the z-tile to depth_out instead of running the pixel pass.
+// =====================================================================================
+namespace {
+
+constexpr int kQueueCap = 2048;   // deferred (large) triangles per pose and work item
+
+struct FusedArgs {
+  const bop_model_dev* models;
+  const PairDesc* desc;
+  const WorkItem* work;
+  PlanCounters* ctr;
+  const void* depth_test;       // VSD
+  const float* depth_scale;     // VSD, u16 input only
+  unsigned long long* counts;   // VSD step: [n][2+BOP_MAX_TAUS] u64
+  double* tl_sums;              // VSD tlinear: [n][BOP_MAX_TAUS] f64
+  float* depth_out;             // RENDER: [n][H][W]
+  unsigned max_items;
+  int tile_px;
+  int small_tri_px;
+  PixParams pp;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(512, 1) fused_kernel(const __grid_constant__ FusedArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned* const zt = (unsigned*)smem_raw;                       // [2][tile_px]
+  double* const xh = (double*)(smem_raw + (size_t)2 * a.tile_px * 4);  // [wpad]
+  int* const queue = (int*)(xh + ((a.pp.W + 3) & ~3));            // [kQueueCap]
+
+  __shared__ PairDesc sD;
+  __shared__ WorkItem sW;
+  __shared__ unsigned s_ticket;
+  __shared__ int s_q;
+  __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS];
+  __shared__ double s_sum[BOP_MAX_TAUS];
+
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
+  const unsigned total = min(a.ctr->total, a.max_items);
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned t = atomicAdd(&a.ctr->next, 1u);
+      s_ticket = t;
+      if (t < total) sW = a.work[t];
+      s_q = 0;
+    }
+    if (tid < 2 + BOP_MAX_TAUS) s_cnt[tid] = 0ull;
+    if (tid < BOP_MAX_TAUS) s_sum[tid] = 0.0;
+    __syncthreads();
+    if (s_ticket >= total) break;
+    {
+      // Cooperative copy of the pair descriptor (word-wise).
+      const int* src = (const int*)(a.desc + sW.pair);
+      int* dst = (int*)&sD;
+      for (int i = tid; i < (int)(sizeof(PairDesc) / 4); i += nthr) dst[i] = src[i];
+    }
+    __syncthreads();
+    const int w = sD.w, nrows = sW.nrows;
+    const int cx0 = sD.x0, cx1 = min(sD.x0 + w - 1, a.pp.W - 1);
+    const int cy0 = sD.y0 + sW.row0, cy1 = cy0 + nrows - 1;
+    const int npx = nrows * w;
+    const int n_poses = sD.n_poses;
+    // Clear the z-tiles to +inf and build the x-ray table (misc.py:137: (xs - cx) / fx).
+    {
+      const uint4 inf4 = make_uint4(BOP_INF_BITS_F32, BOP_INF_BITS_F32, BOP_INF_BITS_F32, BOP_INF_BITS_F32);
+      for (int p = 0; p < n_poses; ++p) {
+        uint4* z4 = (uint4*)(zt + (size_t)p * a.tile_px);
+        for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = inf4;
+      }
+      if (MODE != MODE_RENDER)
+        for (int c = tid; c < w; c += nthr)
+          xh[c] = __ddiv_rn(__dsub_rn((double)(cx0 + c), sD.kcx), sD.kfx);
+    }
+    __syncthreads();
+
+    const bop_model_dev M = a.models[sD.obj];
+    const float4* __restrict__ verts = (const float4*)M.verts4;
+    const int4* __restrict__ faces = (const int4*)M.faces4;
+    const int F = M.n_faces;
+
+    for (int p = 0; p < n_poses; ++p) {
+      PoseCamF P = sD.pose[p];
+      unsigned* const z = zt + (size_t)p * a.tile_px;
+      for (int f = tid; f < F; f += nthr) {
+        TriSetup T;
+        const int n = tri_setup(P, verts, __ldg(faces + f), cx0, cy0, cx1, cy1, T);
+        if (n == 0) continue;
+        bool inline_it = n <= a.small_tri_px;
+        if (!inline_it) {
+          const int slot = atomicAdd(&s_q, 1);
+          if (slot < kQueueCap) queue[slot] = f;
+          else inline_it = true;   // queue full: draw it here (slow but correct)
+        }
+        if (inline_it) {
+          for (int y = T.by0; y <= T.by1; ++y)
+            for (int x = T.bx0; x <= T.bx1; ++x) tri_pixel(T, x, y, z, cx0, cy0, w);
+        }
+      }
+      __syncthreads();
+      const int nq = min(s_q, kQueueCap);
+      if (nq > 0) {
+        // Warp-cooperative path for large triangles: lanes stride over the candidate rectangle.
+        for (int qi = warp; qi < nq; qi += nwarps) {
+          TriSetup T;
+          const int n = tri_setup(P, verts, __ldg(faces + queue[qi]), cx0, cy0, cx1, cy1, T);
+          const int bw = T.bx1 - T.bx0 + 1;
+          for (int c = lane; c < n; c += 32) {
+            const int yy = c / bw, xx = c - yy * bw;
+            tri_pixel(T, T.bx0 + xx, T.by0 + yy, z, cx0, cy0, w);
+          }
+        }
+      }
+      __syncthreads();
+      if (tid == 0) s_q = 0;
+      // (the next pose's pushes happen after its own first barrier-free loop; s_q was reset by
+      //  tid 0 before any thread can pass the barrier below)
+      __syncthreads();
+    }
+
+    if (MODE == MODE_RENDER) {
+      float* out = a.depth_out + (size_t)sD.im * a.pp.H * a.pp.W;
+      for (int i = tid; i < npx; i += nthr) {
+        const unsigned zb = zt[i];
+        if (zb != BOP_INF_BITS_F32) {
+          const int r = i / w, c = i - r * w;
+          out[(size_t)(cy0 + r) * a.pp.W + (cx0 + c)] = __uint_as_float(zb);
+        }
+      }
+      continue;
+    }
+
+    // ---- pixel pass ------------------------------------------------------------------
+    Acc<MODE> acc;
+    const int w4 = w >> 2;
+    const int ngroups = nrows * w4;
+    const double diameter = sD.diameter;
+    const float scale = (a.pp.depth_dtype == BOP_DEPTH_U16 && a.depth_scale) ? a.depth_scale[sD.im] : 1.f;
+    for (int g = tid; g < ngroups; g += nthr) {
+      const int r = g / w4, c4 = g - r * w4;
+      const uint4 ze = *(const uint4*)(zt + r * w + 4 * c4);
+      const uint4 zg = *(const uint4*)(zt + a.tile_px + r * w + 4 * c4);
+      const bool e_empty = (ze.x & ze.y & ze.z & ze.w) == BOP_INF_BITS_F32 &&
+                           (ze.x | ze.y | ze.z | ze.w) == BOP_INF_BITS_F32;
+      const bool g_empty = (zg.x & zg.y & zg.z & zg.w) == BOP_INF_BITS_F32 &&
+                           (zg.x | zg.y | zg.z | zg.w) == BOP_INF_BITS_F32;
+      if (e_empty && g_empty)
+        continue;   // no model pixel in this group: depth_test is not even loaded
+      const int row = cy0 + r, col = cx0 + 4 * c4;
+      float dt[4];
+      load_depth4(a.pp, a.depth_test, scale, sD.im, row, col, dt);
+      const double Y = __ddiv_rn(__dsub_rn((double)row, sD.kcy), sD.kfy);   // misc.py:138
+      const unsigned zev[4] = {ze.x, ze.y, ze.z, ze.w};
+      const unsigned zgv[4] = {zg.x, zg.y, zg.z, zg.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float de = zev[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zev[k]);
+        const float dg = zgv[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zgv[k]);
+        vsd_pixel<MODE>(a.pp, xh[4 * c4 + k], Y, dt[k], de, dg, diameter, acc);
+      }
+    }
+    // ---- reduce: warp shuffle -> shared atomics -> one global atomic per counter ---------
+    {
+      const int u = warp_sum(acc.uni), in = warp_sum(acc.inter);
+      if (lane == 0) {
+        if (u) atomicAdd(&s_cnt[0], (unsigned long long)u);
+        if (in) atomicAdd(&s_cnt[1], (unsigned long long)in);
+      }
+#pragma unroll
+      for (int k = 0; k < BOP_MAX_TAUS; ++k) {
+        if (k < a.pp.n_taus) {
+          if (MODE == MODE_TLINEAR) {
+            const double s = warp_sum((double)acc.c[k]);
+            if (lane == 0 && s != 0.0) atomicAdd(&s_sum[k], s);
+          } else {
+            const int s = warp_sum((int)acc.c[k]);
+            if (lane == 0 && s) atomicAdd(&s_cnt[2 + k], (unsigned long long)s);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid < 2 + BOP_MAX_TAUS && s_cnt[tid])
+      atomicAdd(a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS) + tid, s_cnt[tid]);
+    if (MODE == MODE_TLINEAR && tid < a.pp.n_taus && s_sum[tid] != 0.0)
+      atomicAdd(a.tl_sums + (size_t)sW.pair * BOP_MAX_TAUS + tid, s_sum[tid]);
+  }
+}
+
+// errors[pair][k] = (cost_k + (union - inter)) / union, or 1.0 when union == 0
+// (pose_error.py:61-65,75-76,90).
+__global__ void vsd_finalize_kernel(const unsigned long long* __restrict__ counts,
+                                    const double* __restrict__ tl_sums, int n, int n_taus,
+                                    int cost_type, double* __restrict__ errors,
+                                    long long* __restrict__ counts_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long* c = counts + (size_t)i * (2 + BOP_MAX_TAUS);
+  const unsigned long long uni = c[0], inter = c[1];
+  if (counts_out) {
+    counts_out[(size_t)i * (2 + n_taus) + 0] = (long long)uni;
+    counts_out[(size_t)i * (2 + n_taus) + 1] = (long long)inter;
+  }
+  for (int k = 0; k < n_taus; ++k) {
+    double e;
+    if (uni == 0ull) {
+      e = 1.0;
+    } else if (cost_type == BOP_COST_TLINEAR) {
+      e = (tl_sums[(size_t)i * BOP_MAX_TAUS + k] + (double)(uni - inter)) / (double)uni;
+    } else {
+      e = (double)(c[2 + k] + (uni - inter)) / (double)uni;
+    }
+    errors[(size_t)i * n_taus + k] = e;
+    if (counts_out) counts_out[(size_t)i * (2 + n_taus) + 2 + k] = (long long)c[2 + k];
+  }
+}
+
+}  // namespace
+
+// =====================================================================================
+// Stand-alone K2: pre-rendered depth images in HBM (e.g. from a foreign Renderer).
+// grid = (n_pairs, chunks); each thread owns groups of 4 horizontally adjacent pixels.
+// Pure streaming: 3 x 4 B per pixel, 128-bit loads; depth_test is only fetched where a model
+// pixel exists.
+// =====================================================================================
+namespace {
+
+constexpr int kK2Threads = 256;
+constexpr int kK2GroupsPerThread = 8;
+
+template <int MODE>
+__global__ void __launch_bounds__(kK2Threads)
+pixel_pass_kernel(const void* __restrict__ depth_test, const float* __restrict__ depth_scale,
+                  const int32_t* __restrict__ im_idx, const double* __restrict__ K,
+                  const float* __restrict__ depth_est, const float* __restrict__ depth_gt,
+                  const double* __restrict__ diameters, unsigned long long* __restrict__ counts,
+                  double* __restrict__ tl_sums, const __grid_constant__ PixParams pp) {
+  const int pair = blockIdx.x;
+  const int W = pp.W, H = pp.H;
+  const int w4 = (W + 3) >> 2;
+  const int ngroups = H * w4;
+  const int g0 = blockIdx.y * (kK2Threads * kK2GroupsPerThread);
+  if (g0 >= ngroups) return;
+  const int im = im_idx[pair];
+  const double* Kp = K + 9 * (size_t)im;
+  const double fx = Kp[0], fy = Kp[4], cx = Kp[2], cy = Kp[5];
+  const double diameter = diameters[pair];
+  const float scale = (pp.depth_dtype == BOP_DEPTH_U16 && depth_scale) ? depth_scale[im] : 1.f;
+  const float* pe = depth_est + (size_t)pair * H * W;
+  const float* pg = depth_gt + (size_t)pair * H * W;
+  const bool vec = pp.vec_ok != 0;
+
+  Acc<MODE> acc;
+#pragma unroll 2
+  for (int j = 0; j < kK2GroupsPerThread; ++j) {
+    const int g = g0 + j * kK2Threads + threadIdx.x;
+    if (g >= ngroups) break;
+    const int row = g / w4, col = (g - row * w4) << 2;
+    float de[4], dg[4];
+    if (vec) {
+      const float4 a = ld_stream_f4(pe + (size_t)row * W + col);
+      const float4 b = ld_stream_f4(pg + (size_t)row * W + col);
+      de[0] = a.x; de[1] = a.y; de[2] = a.z; de[3] = a.w;
+      dg[0] = b.x; dg[1] = b.y; dg[2] = b.z; dg[3] = b.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const bool in = col + k < W;
+        de[k] = in ? __ldg(pe + (size_t)row * W + col + k) : 0.f;
+        dg[k] = in ? __ldg(pg + (size_t)row * W + col + k) : 0.f;
+      }
+    }
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) any = any || de[k] != 0.f || dg[k] != 0.f;
+    if (!any) continue;
+    float dt[4];
+    load_depth4(pp, depth_test, scale, im, row, col, dt);
+    const double Y = __ddiv_rn(__dsub_rn((double)row, cy), fy);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (de[k] != 0.f || dg[k] != 0.f) {
+        const double X = __ddiv_rn(__dsub_rn((double)(col + k), cx), fx);
+        vsd_pixel<MODE>(pp, X, Y, dt[k], de[k], dg[k], diameter, acc);
+      }
+    }
+  }
+  __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS];
+  __shared__ double s_sum[BOP_MAX_TAUS];
+  if (threadIdx.x < 2 + BOP_MAX_TAUS) s_cnt[threadIdx.x] = 0ull;
+  if (threadIdx.x < BOP_MAX_TAUS) s_sum[threadIdx.x] = 0.0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int u = warp_sum(acc.uni), in = warp_sum(acc.inter);
+  if (lane == 0) {
+    if (u) atomicAdd(&s_cnt[0], (unsigned long long)u);
+    if (in) atomicAdd(&s_cnt[1], (unsigned long long)in);
+  }
+#pragma unroll
+  for (int k = 0; k < BOP_MAX_TAUS; ++k) {
+    if (k < pp.n_taus) {
+      if (MODE == MODE_TLINEAR) {
+        const double s = warp_sum((double)acc.c[k]);
+        if (lane == 0 && s != 0.0) atomicAdd(&s_sum[k], s);
+      } else {
+        const int s = warp_sum((int)acc.c[k]);
+        if (lane == 0 && s) atomicAdd(&s_cnt[2 + k], (unsigned long long)s);
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 + BOP_MAX_TAUS && s_cnt[threadIdx.x])
+    atomicAdd(counts + (size_t)pair * (2 + BOP_MAX_TAUS) + threadIdx.x, s_cnt[threadIdx.x]);
+  if (MODE == MODE_TLINEAR && threadIdx.x < pp.n_taus && s_sum[threadIdx.x] != 0.0)
+    atomicAdd(tl_sums + (size_t)pair * BOP_MAX_TAUS + threadIdx.x, s_sum[threadIdx.x]);
+}
+
+}  // namespace
+
+// =====================================================================================
+// Host launchers / C ABI
+// =====================================================================================
+namespace {
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct WsLayout {
+  size_t ctr, counts, tl, bbox, desc, work, total;
+  unsigned max_items;
+};
+
+WsLayout ws_layout(int n, int H, int W) {
+  WsLayout L;
+  const int wp = (W + 3) & ~3;
+  const int rows_per_band = kMinTilePx / (wp > 0 ? wp : 1);
+  const size_t per_item = (size_t)H / (size_t)(rows_per_band > 0 ? rows_per_band : 1) + 2;
+  size_t mi = per_item * (size_t)(n > 0 ? n : 1);
+  if (mi > 0x7fffffffull) mi = 0x7fffffffull;
+  L.max_items = (unsigned)mi;
+  size_t off = 0;
+  L.ctr = off;    off = align_up(off + sizeof(PlanCounters), 256);
+  L.counts = off; off = align_up(off + (size_t)n * (2 + BOP_MAX_TAUS) * 8, 256);
+  L.tl = off;     off = align_up(off + (size_t)n * BOP_MAX_TAUS * 8, 256);
+  L.bbox = off;   off = align_up(off + (size_t)n * 2 * sizeof(int4), 256);
+  L.desc = off;   off = align_up(off + (size_t)n * sizeof(PairDesc), 256);
+  L.work = off;   off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
+  L.total = off;
+  return L;
+}
+
+int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams& pp) {
+  BOP_REQUIRE(prm, "vsd: null params");
+  BOP_REQUIRE(prm->n_taus >= 1 && prm->n_taus <= BOP_MAX_TAUS, "vsd: n_taus must be in [1, BOP_MAX_TAUS]");
+  BOP_REQUIRE(prm->height > 0 && prm->width > 0 && prm->width <= kMaxWidth, "vsd: bad image size");
+  BOP_REQUIRE(prm->cost_type == BOP_COST_STEP || prm->cost_type == BOP_COST_TLINEAR,
+              "Unknown pixel matching cost.");
+  BOP_REQUIRE(prm->visib_mode == BOP_VISIB_BOP19 || prm->visib_mode == BOP_VISIB_BOP18,
+              "Unknown visibility mode.");
+  BOP_REQUIRE(prm->depth_dtype == BOP_DEPTH_F32 || prm->depth_dtype == BOP_DEPTH_U16,
+              "vsd: unknown depth dtype");
+  for (int k = 0; k < BOP_MAX_TAUS; ++k) pp.taus[k] = k < prm->n_taus ? prm->taus[k] : 0.0;
+  pp.delta_f32 = (float)prm->delta;
+  pp.n_taus = prm->n_taus;
+  pp.normalized = prm->normalized_by_diameter;
+  pp.visib_mode = prm->visib_mode;
+  pp.H = prm->height;
+  pp.W = prm->width;
+  pp.depth_dtype = prm->depth_dtype;
+  const size_t al = prm->depth_dtype == BOP_DEPTH_F32 ? 16 : 8;
+  pp.vec_ok = (prm->width % 4 == 0) && (((uintptr_t)depth_test) % al == 0);
+  return 0;
+}
+
+int g_sm_count = 0;
+int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+template <int MODE>
+int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
+  const int wp = (W + 3) & ~3;
+  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
+  BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = sm_count() * g_tune.ctas_per_sm;
+  fused_kernel<MODE><<<grid, g_tune.threads, smem, s>>>(a);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+// bbox + plan; shared by VSD and render.
+int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const double* pose_a,
+                const double* pose_b, const int32_t* im_idx, const double* K,
+                const double* diameters, int cam_mode, int n,
+                int n_poses, int H, int W, int gate, unsigned char* ws, const WsLayout& L,
+                cudaStream_t s) {
+  // counters + counts + tl sums are contiguous at the head of the workspace.
+  BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
+  int4* bbox = (int4*)(ws + L.bbox);
+  const int warps = n * n_poses;
+  bbox_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
+                                                       diameters, cam_mode, n, n_poses, H, W, gate, bbox);
+  BOP_LAUNCH_CHECK();
+  plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
+                                              n, n_poses, H, W, g_tune.tile_px, bbox,
+                                              (PairDesc*)(ws + L.desc), (WorkItem*)(ws + L.work),
+                                              (PlanCounters*)(ws + L.ctr), L.max_items);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_px) {
+  if (tile_px) {
+    BOP_REQUIRE(tile_px >= kMinTilePx && tile_px % 4 == 0 && tile_px <= 26624, "tuning: tile_px out of range");
+    g_tune.tile_px = tile_px;
+  }
+  if (threads) {
+    BOP_REQUIRE(threads >= 64 && threads <= 512 && threads % 32 == 0, "tuning: threads out of range");
+    g_tune.threads = threads;
+  }
+  if (ctas_per_sm) {
+    BOP_REQUIRE(ctas_per_sm >= 1 && ctas_per_sm <= 8, "tuning: ctas_per_sm out of range");
+    g_tune.ctas_per_sm = ctas_per_sm;
+  }
+  if (small_tri_px) {
+    BOP_REQUIRE(small_tri_px >= 1, "tuning: small_tri_px out of range");
+    g_tune.small_tri_px = small_tri_px;
+  }
+  return 0;
+}
+
+extern "C" size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width) {
+  return ws_layout(n_pairs, height, width).total;
+}
+extern "C" size_t bop_render_workspace_bytes(int n) {
+  // Image size is not known here; sized for the widest supported image with 1-row bands per 4096 px.
+  return ws_layout(n, 4096, kMaxWidth).total;
+}
+
+extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                           const double* pose_est, const double* pose_gt, const void* depth_test,
+                           const float* depth_scale, const int32_t* im_idx, const double* K,
+                           const double* diameters, int n_pairs, const bop_vsd_params* prm,
+                           double* errors_out,
+                           int64_t* counts_out, void* workspace, size_t workspace_bytes,
+                           void* stream) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && depth_test && im_idx && K && errors_out,
+              "bop_vsd_dev: null pointer");
+  PixParams pp;
+  if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
+  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W);
+  BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_vsd_dev: workspace too small");
+  BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_vsd_dev: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  if (int rc = launch_plan(models, obj_idx, pose_est, pose_gt, im_idx, K, diameters, 0, n_pairs, 2, pp.H, pp.W,
+                           prm->gate, ws, L, s))
+    return rc;
+  FusedArgs a;
+  a.models = models;
+  a.desc = (const PairDesc*)(ws + L.desc);
+  a.work = (const WorkItem*)(ws + L.work);
+  a.ctr = (PlanCounters*)(ws + L.ctr);
+  a.depth_test = depth_test;
+  a.depth_scale = depth_scale;
+  a.counts = (unsigned long long*)(ws + L.counts);
+  a.tl_sums = (double*)(ws + L.tl);
+  a.depth_out = nullptr;
+  a.max_items = L.max_items;
+  a.tile_px = g_tune.tile_px;
+  a.small_tri_px = g_tune.small_tri_px;
+  a.pp = pp;
+  int rc = prm->cost_type == BOP_COST_TLINEAR ? launch_fused<MODE_TLINEAR>(a, pp.W, s)
+                                              : launch_fused<MODE_STEP>(a, pp.W, s);
+  if (rc) return rc;
+  vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(a.counts, a.tl_sums, n_pairs, pp.n_taus,
+                                                            prm->cost_type, errors_out,
+                                                            (long long*)counts_out);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                                    const double* pose, const double* cam, int n, int height,
+                                    int width, float* depth_out, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  if (n <= 0) return 0;
+  BOP_REQUIRE(models && obj_idx && pose && cam && depth_out, "bop_render_depth_dev: null pointer");
+  BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_render_depth_dev: bad image size");
+  const WsLayout L = ws_layout(n, height, width);
+  BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_render_depth_dev: workspace too small");
+  BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_render_depth_dev: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  BOP_CUDA(cudaMemsetAsync(depth_out, 0, sizeof(float) * (size_t)n * height * width, s));
+  if (int rc = launch_plan(models, obj_idx, pose, pose, nullptr, cam, nullptr, 1, n, 1, height, width, 0, ws, L, s))
+    return rc;
+  FusedArgs a;
+  memset(&a, 0, sizeof(a));
+  a.models = models;
+  a.desc = (const PairDesc*)(ws + L.desc);
+  a.work = (const WorkItem*)(ws + L.work);
+  a.ctr = (PlanCounters*)(ws + L.ctr);
+  a.depth_out = depth_out;
+  a.max_items = L.max_items;
+  a.tile_px = g_tune.tile_px;
+  a.small_tri_px = g_tune.small_tri_px;
+  a.pp.H = height;
+  a.pp.W = width;
+  a.pp.n_taus = 1;
+  return launch_fused<MODE_RENDER>(a, width, s);
+}
+
+extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
+                                      const int32_t* im_idx, const double* K,
+                                      const float* depth_est, const float* depth_gt,
+                                      const double* diameters, int n_pairs,
+                                      const bop_vsd_params* prm, double* errors_out,
+                                      int64_t* counts_out, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(depth_test && im_idx && K && depth_est && depth_gt && diameters && errors_out,
+              "bop_vsd_from_depth_dev: null pointer");
+  PixParams pp;
+  if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
+  pp.vec_ok = pp.vec_ok && ((uintptr_t)depth_est % 16 == 0) && ((uintptr_t)depth_gt % 16 == 0);
+  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W);
+  BOP_REQUIRE(workspace && workspace_bytes >= L.bbox, "bop_vsd_from_depth_dev: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
+  unsigned long long* counts = (unsigned long long*)(ws + L.counts);
+  double* tl = (double*)(ws + L.tl);
+  const int ngroups = pp.H * ((pp.W + 3) >> 2);
+  const int chunk = kK2Threads * kK2GroupsPerThread;
+  dim3 grid(n_pairs, (ngroups + chunk - 1) / chunk);
+  if (prm->cost_type == BOP_COST_TLINEAR)
+    pixel_pass_kernel<MODE_TLINEAR><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
+                                                               depth_gt, diameters, counts, tl, pp);
+  else
+    pixel_pass_kernel<MODE_STEP><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
+                                                            depth_gt, diameters, counts, tl, pp);
+  BOP_LAUNCH_CHECK();
+  vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, tl, n_pairs, pp.n_taus,
+                                                            prm->cost_type, errors_out,
+                                                            (long long*)counts_out);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}

@@ -158,11 +158,14 @@ int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
  * pose_error.vsd (pose_error.py:17-93) with the library's own rasteriser: both
  * poses are rendered into shared-memory z-tiles over the union ROI and consumed
  * by the pixel pass without ever being written to HBM.
+ * diameters: optional [n_pairs] float64 overriding models[obj].diameter (the `diameter`
+ * argument of pose_error.vsd); NULL = use the model table.
  * errors_out: [n_pairs][n_taus] float64; counts_out optional as above.        */
 int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const double* pose_est, const double* pose_gt,
                 const void* depth_test, const float* depth_scale,
-                const int32_t* im_idx, const double* K, int n_pairs,
+                const int32_t* im_idx, const double* K,
+                const double* diameters, int n_pairs,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
