@@ -1,0 +1,130 @@
+"""CPU: the oracle restatement must reproduce the golden vectors produced by the REAL reference
+(tests/golden/make_golden.py).  This is what pins the oracle."""
+import numpy as np
+import pytest
+
+from conftest import syms_from_array
+from oracle import pose_error_oracle as po
+from oracle import renderer_oracle
+
+MODELS_INFO = None
+
+
+def _models_info():
+  from bop_toolkit_b200 import synth
+  return [
+    {'diameter': 150.0},
+    {'diameter': 150.0, 'symmetries_discrete': synth.discrete_z_symmetries(4)},
+    {'diameter': 150.0, 'symmetries_continuous': [{'axis': [0, 0, 1], 'offset': [0, 0, 0]}]},
+    {'diameter': 150.0, 'symmetries_discrete': synth.discrete_z_symmetries(2),
+     'symmetries_continuous': [{'axis': [0, 1, 0], 'offset': [1.5, 0, -2.0]}]},
+  ]
+
+
+def test_symmetry_sets_bit_exact(golden):
+  from bop_toolkit_b200 import batch, misc
+  for i, (mi, st) in enumerate(zip(_models_info(), golden['sym_steps'])):
+    ref = golden['sym_%d' % i]
+    got_oracle = batch.pack_syms(po.get_symmetry_transformations(mi, float(st)))
+    got_pkg = batch.pack_syms(misc.get_symmetry_transformations(mi, float(st)))
+    assert got_oracle.shape == ref.shape
+    assert np.array_equal(got_oracle, ref)
+    assert np.array_equal(got_pkg, ref)     # host precompute of the product: bit-identical
+  assert golden['sym_2'].shape[0] == 36     # "discretised to 36" (BASELINE configs[2])
+  assert golden['sym_0'].shape[0] == 1 and golden['sym_1'].shape[0] == 4
+
+
+@pytest.mark.parametrize('mname', ['f32', 'f64'])
+def test_point_errors(golden, mname):
+  g = golden
+  pts = g['pts_small'] if mname == 'f32' else g['pts_f64']
+  n = g['R_e'].shape[0]
+  col = lambda t: t.reshape(3, 1)
+  for si in range(4):
+    key = 'mssd_%s_%d' % (mname, si)
+    if key not in g:
+      continue
+    syms = syms_from_array(g['sym_%d' % si])
+    ms = [po.mssd(g['R_e'][i], col(g['t_e'][i]), g['R_g'][i], col(g['t_g'][i]), pts, syms) for i in range(n)]
+    mp = [po.mspd(g['R_e'][i], col(g['t_e'][i]), g['R_g'][i], col(g['t_g'][i]), g['K'], pts, syms) for i in range(n)]
+    assert np.array_equal(np.array(ms), g[key])
+    assert np.array_equal(np.array(mp), g['mspd_%s_%d' % (mname, si)])
+  ad = [po.add(g['R_e'][i], col(g['t_e'][i]), g['R_g'][i], col(g['t_g'][i]), pts) for i in range(n)]
+  ai = [po.adi(g['R_e'][i], col(g['t_e'][i]), g['R_g'][i], col(g['t_g'][i]), pts) for i in range(n)]
+  pj = [po.proj(g['R_e'][i], col(g['t_e'][i]), g['R_g'][i], col(g['t_g'][i]), g['K'], pts) for i in range(n)]
+  assert np.array_equal(np.array(ad), g['add_' + mname])
+  assert np.array_equal(np.array(ai), g['adi_' + mname])
+  assert np.array_equal(np.array(pj), g['proj_' + mname])
+
+
+def test_re_te_gate(golden):
+  g = golden
+  n = g['R_e'].shape[0]
+  assert np.array_equal(np.array([po.re(g['R_e'][i], g['R_g'][i]) for i in range(n)]), g['re'])
+  assert np.array_equal(np.array([po.te(g['t_e'][i], g['t_g'][i]) for i in range(n)]), g['te'])
+  got = [po.overlapping_sphere_projections(75.0, g['t_e'][i], g['t_g'][i]) for i in range(n)]
+  assert np.array_equal(np.array(got), g['sphere_proj_overlap'])
+  assert 0 < g['sphere_proj_overlap'].sum() < n   # both branches are exercised
+
+
+def test_known_answers(golden):
+  g = golden
+  # est == gt  =>  all errors 0 (SURVEY §4 invariant i); est = gt o sym => mssd = mspd ~ 0.
+  assert g['mssd_f32_0'][0] == 0 and g['add_f32'][0] == 0 and g['adi_f32'][0] == 0
+  assert g['re'][0] < 1e-5 and g['te'][0] == 0
+  assert g['mssd_f32_1'][1] < 1e-9 and g['mspd_f32_1'][1] < 1e-9
+  assert np.all(g['adi_f32'] <= g['add_f32'] + 1e-12)   # invariant vi
+
+
+def test_vsd_pipeline(golden, oracle_built):
+  g = golden
+  H, W = g['vsd_depth_test'].shape[1:]
+  ren = renderer_oracle.RendererOracle(W, H)
+  ren.add_object(7, pts=g['vsd_pts'], faces=g['vsd_faces'])
+  taus = list(g['vsd_taus'])
+  K = g['vsd_K']
+  for i in range(g['vsd_R_e'].shape[0]):
+    de = ren.render_object(7, g['vsd_R_e'][i], g['vsd_t_e'][i], K[0, 0], K[1, 1], K[0, 2], K[1, 2])['depth']
+    dg = ren.render_object(7, g['vsd_R_g'][i], g['vsd_t_g'][i], K[0, 0], K[1, 1], K[0, 2], K[1, 2])['depth']
+    assert np.array_equal(de, g['vsd_render_est'][i])   # C oracle is deterministic
+    assert np.array_equal(dg, g['vsd_render_gt'][i])
+    args = (g['vsd_R_e'][i], g['vsd_t_e'][i], g['vsd_R_g'][i], g['vsd_t_g'][i],
+            g['vsd_depth_test'][i], K, 15, taus)
+    assert po.vsd(*args, True, 180.0, ren, 7, 'step') == list(g['vsd_step'][i])
+    assert np.allclose(po.vsd(*args, True, 180.0, ren, 7, 'tlinear'), g['vsd_tlinear'][i], rtol=0, atol=1e-15)
+    assert po.vsd(*args[:6], 15, [5.0, 20.0], False, 180.0, ren, 7, 'step') == list(g['vsd_unnorm'][i])
+  # est == gt and unoccluded-enough: VSD = 0 at the largest tau; step VSD non-increasing in tau.
+  assert np.all(np.diff(g['vsd_step'], axis=1) <= 0)
+  assert g['vsd_step'][0].max() == 0.0
+
+
+def test_dist_and_visibility(golden):
+  g = golden
+  K = g['vsd_K']
+  d_test = po.depth_im_to_dist_im(g['vsd_depth_test'][1], K)
+  assert np.array_equal(d_test, g['dist_test_1'])
+  d_gt = po.depth_im_to_dist_im(g['vsd_render_gt'][1], K)
+  d_est = po.depth_im_to_dist_im(g['vsd_render_est'][1], K)
+  for mode in ('bop19', 'bop18'):
+    vg = po.estimate_visib_mask_gt(d_test, d_gt, 15, mode)
+    ve = po.estimate_visib_mask_est(d_test, d_est, vg, 15, mode)
+    assert np.array_equal(np.packbits(vg), g['visib_gt_1_' + mode])
+    assert np.array_equal(np.packbits(ve), g['visib_est_1_' + mode])
+  with pytest.raises(ValueError):
+    po.estimate_visib_mask_gt(d_test, d_gt, 15, 'nope')
+
+
+def test_oracle_raster_known_answer(oracle_built):
+  """A fronto-parallel square whose edges pass exactly through pixel centres: top-left rule."""
+  pts = np.array([[-10, -10, 0], [10, -10, 0], [10, 10, 0], [-10, 10, 0]], dtype=np.float64)
+  faces = np.array([[0, 1, 2], [0, 2, 3]], dtype=np.int32)
+  # fx = Z so that 1 mm = 1 px; cx = 20.5 puts x=-10 at window 10.5 = centre of pixel 10.
+  d = renderer_oracle.render_depth(pts, faces, np.eye(3), [0, 0, 100.0], 100.0, 100.0, 20.5, 20.5, 40, 40)
+  cov = d > 0
+  rows, cols = np.nonzero(cov)
+  assert rows.min() == 10 and rows.max() == 29 and cols.min() == 10 and cols.max() == 29
+  assert cov.sum() == 400            # shared diagonal drawn exactly once, no holes
+  assert np.all(d[cov] == 100.0)
+  # reversed winding gives the same image (no culling)
+  d2 = renderer_oracle.render_depth(pts, faces[:, ::-1].copy(), np.eye(3), [0, 0, 100.0], 100.0, 100.0, 20.5, 20.5, 40, 40)
+  assert np.array_equal(d, d2)
