@@ -1,0 +1,474 @@
+#!/usr/bin/env python
+"""Benchmark of the pose-error hot path: pose-error pairs/sec (VSD + MSSD + MSPD).
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run)
+  python bench.py --impl reference ...                      (CPU oracle port on all host cores)
+
+Workload at every N (weak scaling, per GPU): BASELINE.json configs[1] -- VSD (delta = 15 mm,
+taus 0.05..0.5, step cost) on 640x480 synthetic depth, 1 object / image, 10,000 pose pairs (one
+distinct depth image per pair) -- with MSSD and MSPD evaluated on the same pairs using the 4
+symmetry transforms of configs[0].  A "step" is one pass of the hot path over all pairs; a pair
+counts once when all three errors are computed.  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+  sys.path.insert(0, ROOT)
+
+H, W = 480, 640
+N_OBJ = 8
+DEPTH_SCALE = 0.1          # uint16 samples x 0.1 = mm (BOP depth_scale convention)
+DELTA = 15.0
+TAUS = [float(t) for t in np.arange(0.05, 0.51, 0.05)]
+N_SYMS = 4
+WORKLOAD = ('cfg2: VSD(delta=15,taus=.05-.5,step)+MSSD+MSPD(S=4), 640x480, 1 obj/image, '
+            '%d pose pairs/GPU, 8 models of 4902 verts/9800 faces')
+
+
+def build_models():
+  from bop_toolkit_b200 import synth, misc
+  models = []
+  for k in range(N_OBJ):
+    diameter = 80.0 + (300.0 - 80.0) * k / (N_OBJ - 1)
+    pts, faces = synth.make_mesh(50, 100, diameter, seed=100 + k)
+    info = {'diameter': diameter, 'symmetries_discrete': synth.discrete_z_symmetries(N_SYMS)}
+    syms = misc.get_symmetry_transformations(info, 0.01)
+    models.append(dict(obj_id=k + 1, pts=pts, faces=faces, syms=syms, diameter=diameter))
+  return models
+
+
+def build_pairs(n_pairs, seed):
+  from bop_toolkit_b200 import synth
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n_pairs, seed=seed)
+  obj = (np.arange(n_pairs) % N_OBJ).astype(np.int32)
+  return R_e, t_e, R_g, t_g, obj
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler(object):
+  """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+  Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+       'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+       'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+  def __init__(self, gpu_index):
+    self.gpu = gpu_index
+    self.rows = []
+    self.proc = None
+
+  def start(self):
+    try:
+      self.proc = subprocess.Popen(
+        ['nvidia-smi', '-i', str(self.gpu), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits',
+         '-lms', '100'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+      self.t = threading.Thread(target=self._read, daemon=True)
+      self.t.start()
+    except Exception:
+      self.proc = None
+
+  def _read(self):
+    for line in self.proc.stdout:
+      self.rows.append((time.time(), line.strip()))
+
+  def stop(self):
+    if self.proc is not None:
+      self.proc.terminate()
+      try:
+        self.proc.wait(timeout=2)
+      except Exception:
+        pass
+
+  def summary(self, t0, t1):
+    sm, mx, reasons = [], [], set()
+    for ts, line in self.rows:
+      if ts < t0 or ts > t1 + 0.2:
+        continue
+      f = [x.strip() for x in line.split(',')]
+      if len(f) < 9:
+        continue
+      try:
+        sm.append(float(f[1])); mx.append(float(f[2]))
+      except ValueError:
+        continue
+      for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), f[5:9]):
+        if v.lower().startswith('active'):
+          reasons.add(name)
+    if not sm:
+      return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+    return {'sm_mhz': float(np.median(sm)), 'sm_max_mhz': float(max(mx)), 'reasons': sorted(reasons),
+            'samples': len(sm)}
+
+
+# ----------------------------------------------------------------------- CPU (oracle) arm
+def _cpu_init():
+  os.environ['OMP_NUM_THREADS'] = '1'
+  os.environ['OPENBLAS_NUM_THREADS'] = '1'
+  os.environ['MKL_NUM_THREADS'] = '1'
+
+
+_CPU = {}
+
+
+def _cpu_setup_pair(args):
+  """Untimed: synthesises the depth image of one sample pair with the oracle renderer."""
+  i, seed = args
+  from bop_toolkit_b200 import synth
+  from oracle import renderer_oracle
+  if 'models' not in _CPU:
+    _CPU['models'] = build_models()
+  if ('pairs', seed) not in _CPU:
+    _CPU[('pairs', seed)] = build_pairs(_CPU_NPAIRS[0], seed)
+  R_e, t_e, R_g, t_g, obj = _CPU[('pairs', seed)]
+  m = _CPU['models'][obj[i]]
+  if 'ren' not in _CPU:
+    ren = _CPU['ren'] = renderer_oracle.RendererOracle(W, H)
+    for mm in _CPU['models']:
+      ren.add_object(mm['obj_id'], pts=mm['pts'], faces=mm['faces'])
+  K = synth.LM_K
+  d = renderer_oracle.render_depth(m['pts'], m['faces'], R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], H, W)
+  d = synth.degrade_depth(d, seed=seed * 100003 + i)
+  d16 = np.round(d / DEPTH_SCALE).astype(np.uint16)
+  return i, d16.astype(np.float32) * np.float32(DEPTH_SCALE)
+
+
+_CPU_NPAIRS = [10000]
+
+
+def _cpu_eval_pair(args):
+  """Timed: what scripts/eval_calc_errors.py does for one (est, gt) pair for vsd + mssd + mspd,
+  with the oracle port of pose_error.py and the C oracle rasteriser as the renderer."""
+  i, seed, depth = args
+  from bop_toolkit_b200 import synth
+  from oracle import pose_error_oracle as po
+  from oracle import renderer_oracle
+  if 'models' not in _CPU:
+    _CPU['models'] = build_models()
+  if ('pairs', seed) not in _CPU:
+    _CPU[('pairs', seed)] = build_pairs(_CPU_NPAIRS[0], seed)
+  R_e, t_e, R_g, t_g, obj = _CPU[('pairs', seed)]
+  m = _CPU['models'][obj[i]]
+  ren = _CPU['ren']
+  K = synth.LM_K
+  te, tg = t_e[i].reshape(3, 1), t_g[i].reshape(3, 1)
+  if po.overlapping_sphere_projections(0.5 * m['diameter'], t_e[i], t_g[i]):
+    e_vsd = po.vsd(R_e[i], te, R_g[i], tg, depth, K, DELTA, TAUS, True, m['diameter'], ren, m['obj_id'], 'step')
+  else:
+    e_vsd = [1.0] * len(TAUS)
+  if np.linalg.norm(te - tg) < m['diameter']:
+    e_mssd = po.mssd(R_e[i], te, R_g[i], tg, m['pts'], m['syms'])
+  else:
+    e_mssd = float('inf')
+  e_mspd = po.mspd(R_e[i], te, R_g[i], tg, K, m['pts'], m['syms'])
+  return i, e_vsd, e_mssd, e_mspd
+
+
+def cpu_arm(n_pairs_cfg, sample, cores, steps, warmup, seed=0):
+  """Times the oracle port on `cores` host processes over `sample` pairs per step.
+  Returns (pairs_per_s, ms_per_step, results of the last step)."""
+  import multiprocessing as mp
+  from oracle import renderer_oracle
+  renderer_oracle.build()
+  _CPU_NPAIRS[0] = n_pairs_cfg
+  idx = list(range(sample))
+  if cores <= 1:
+    _cpu_init()
+    depths = dict(_cpu_setup_pair((i, seed)) for i in idx)
+    run = lambda: [_cpu_eval_pair((i, seed, depths[i])) for i in idx]
+    for _ in range(warmup):
+      run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+      res = run()
+    dt = time.perf_counter() - t0
+  else:
+    ctx = mp.get_context('fork')
+    with ctx.Pool(cores, initializer=_cpu_init) as pool:
+      depths = dict(pool.map(_cpu_setup_pair, [(i, seed) for i in idx]))
+      work = [(i, seed, depths[i]) for i in idx]
+      for _ in range(warmup):
+        pool.map(_cpu_eval_pair, work, chunksize=1)
+      t0 = time.perf_counter()
+      for _ in range(steps):
+        res = pool.map(_cpu_eval_pair, work, chunksize=1)
+      dt = time.perf_counter() - t0
+  return sample * steps / dt, 1e3 * dt / steps, res
+
+
+# ------------------------------------------------------------------------------ GPU arm
+def make_depth_gpu(batch, torch, ms, obj, pose_gt, t_gt, diam, K, device, seed, chunk=400):
+  """Synthetic sensor depth (uint16 samples, scale 0.1 mm) for every pair, generated on the GPU:
+  GT render over a tilted background plane + N(0, 2 mm) noise + 3 % missing pixels + an occluder
+  box in front of ~30 % of the objects.  Not timed."""
+  P = pose_gt.shape[0]
+  gen = torch.Generator(device=device)
+  gen.manual_seed(seed)
+  d16 = torch.empty((P, H, W), dtype=torch.int16, device=device)
+  ys = torch.arange(H, device=device, dtype=torch.float32).view(1, H, 1)
+  xs = torch.arange(W, device=device, dtype=torch.float32).view(1, 1, W)
+  cams = torch.tensor([K[0, 0], K[1, 1], K[0, 2], K[1, 2]], dtype=torch.float64, device=device)
+  for c0 in range(0, P, chunk):
+    c1 = min(P, c0 + chunk)
+    n = c1 - c0
+    d = batch.render_batch(ms, obj[c0:c1], pose_gt[c0:c1], cams, H, W)
+    u = lambda lo, hi: torch.rand((n, 1, 1), device=device, generator=gen) * (hi - lo) + lo
+    bg = u(1200.0, 2000.0) + u(-0.3, 0.3) * (xs - W / 2) + u(-0.3, 0.3) * (ys - H / 2)
+    out = torch.where(d > 0, d, bg)
+    tz = t_gt[c0:c1, 2].view(n, 1, 1).float()
+    pu = (t_gt[c0:c1, 0].view(n, 1, 1).float() / tz) * float(K[0, 0]) + float(K[0, 2])
+    pv = (t_gt[c0:c1, 1].view(n, 1, 1).float() / tz) * float(K[1, 1]) + float(K[1, 2])
+    half = 0.25 * diam[c0:c1].view(n, 1, 1).float() * float(K[0, 0]) / tz
+    ou, ov = pu + u(-1.0, 1.0) * half, pv + u(-1.0, 1.0) * half
+    occ = (u(0.0, 1.0) < 0.3) & ((xs - ou).abs() < half) & ((ys - ov).abs() < half)
+    out = torch.where(occ, 0.6 * tz.expand_as(out), out)
+    out = out + 2.0 * torch.randn(out.shape, device=device, generator=gen)
+    out = torch.where(torch.rand(out.shape, device=device, generator=gen) < 0.03, torch.zeros_like(out), out)
+    v = torch.round(out / DEPTH_SCALE).clamp_(0, 65535).to(torch.int32)
+    d16[c0:c1] = torch.where(v >= 32768, v - 65536, v).to(torch.int16)
+  return d16
+
+
+def gpu_arm(args):
+  import torch
+  import torch.distributed as dist
+  from bop_toolkit_b200 import _lib, batch, misc, sharding, synth
+
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+  if world > 1:
+    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+  assert torch.cuda.is_available(), 'bench.py needs a GPU (there is no CPU fallback)'
+  torch.cuda.set_device(local_rank)
+  device = torch.device('cuda', local_rank)
+  _lib.require_cuda()
+  lib = _lib.lib()
+  P = args.pairs
+  K = synth.LM_K
+
+  # ---- per-GPU model residency + this rank's shard of pose pairs (weak scaling) -------------
+  models = build_models()
+  ms = batch.ModelSet(device)
+  for m in models:
+    ms.add(m['obj_id'], m['pts'], m['faces'], m['syms'], m['diameter'])
+  n_verts, n_faces = models[0]['pts'].shape[0], models[0]['faces'].shape[0]
+  R_e, t_e, R_g, t_g, obj_np = build_pairs(P, seed=rank)
+  pe_np, pg_np = batch.pack_poses(R_e, t_e), batch.pack_poses(R_g, t_g)
+  diam_np = np.array([models[o]['diameter'] for o in obj_np])
+  gate_ok = np.array([misc.overlapping_sphere_projections(0.5 * diam_np[i], t_e[i], t_g[i]) for i in range(P)])
+  n_active = int(gate_ok.sum())
+
+  pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+  h_pe, h_pg, h_obj = pin(pe_np), pin(pg_np), pin(obj_np)
+  h_im = pin(np.arange(P, dtype=np.int32))
+  h_K = pin(np.tile(K.reshape(1, 9), (P, 1)))
+  h_scale = pin(np.full(P, DEPTH_SCALE, dtype=np.float32))
+  d_pe, d_pg, d_obj = h_pe.to(device), h_pg.to(device), h_obj.to(device)
+  d_im, d_K = h_im.to(device), h_K.to(device)
+  d16 = make_depth_gpu(batch, torch, ms, d_obj, d_pg, torch.from_numpy(t_g).to(device),
+                       torch.from_numpy(diam_np).to(device), K, device, seed=1234 + rank)
+  h_d16 = torch.empty((P, H, W), dtype=torch.int16).pin_memory()
+  h_d16.copy_(d16)
+  # Resident float32 millimetres: bit-identical to what the u16 path computes (u16 * 0.1f).
+  d_f32 = torch.empty((P, H, W), dtype=torch.float32, device=device)
+  for c0 in range(0, P, 1000):
+    v = d16[c0:c0 + 1000].to(torch.int32)
+    d_f32[c0:c0 + 1000] = torch.where(v < 0, v + 65536, v).to(torch.float32) * DEPTH_SCALE
+  del d16
+  ids = torch.stack([torch.full((P,), rank, dtype=torch.int32, device=device), d_im, d_obj + 1,
+                     torch.zeros(P, dtype=torch.int32, device=device),
+                     torch.zeros(P, dtype=torch.int32, device=device)], dim=1)
+  h_out = torch.empty((P, len(TAUS) + 2), dtype=torch.float64).pin_memory()
+  torch.cuda.synchronize()
+
+  def step_resident():
+    vsd = batch.vsd_batch(ms, d_obj, d_pe, d_pg, d_f32, d_im, d_K, DELTA, TAUS, True, 'step', 'bop19', gate=True)
+    mssd = batch.mssd_batch(ms, d_obj, d_pe, d_pg, gate=True)
+    mspd = batch.mspd_batch(ms, d_obj, d_pe, d_pg, d_K)
+    errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
+    if world > 1:   # the path's one exchange step: all-gather of fixed-width error records
+      return sharding.gather_records(ids, errs)[1]
+    return errs
+
+  def step_e2e():
+    # HOST buffers in, host results out: H2D of every input of the step + D2H of the errors.
+    vsd = batch.vsd_batch(ms, h_obj, h_pe, h_pg, h_d16, h_im, h_K, DELTA, TAUS, True, 'step', 'bop19',
+                          gate=True, depth_scale=h_scale)
+    o, a, b = (x.to(device, non_blocking=True) for x in (h_obj, h_pe, h_pg))
+    mssd = batch.mssd_batch(ms, o, a, b, gate=True)
+    mspd = batch.mspd_batch(ms, o, a, b, h_K)
+    errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
+    if world > 1:
+      sharding.gather_records(ids, errs)
+    h_out.copy_(errs, non_blocking=True)
+    return errs
+
+  def timed(fn, steps, warmup, sampler):
+    for _ in range(warmup):
+      fn()
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+    lib.bop_profile_reset()
+    l0 = batch.kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.time()
+    e0.record()
+    for _ in range(steps):
+      out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    w1 = time.time()
+    if world > 1:
+      dist.barrier()
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=device)
+    if world > 1:
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), batch.kernel_launch_count() - l0, (w0, w1), out
+
+  sampler = ClockSampler(local_rank)
+  if rank == 0:
+    sampler.start()
+    time.sleep(0.3)
+  lib.bop_profile_enable(1)
+  ms_res, launches, win_res, out_res = timed(step_resident, args.steps, args.warmup, sampler)
+  s_ms, s_n = ctypes_double(), ctypes_int()
+  lib.bop_profile_sum_ms(0, args.steps, byref(s_ms), byref(s_n))
+  fused_ms = s_ms.value / max(1, s_n.value)
+  parts = {}
+  for name, slot in (('vsd_plan', 1), ('mssd', 2), ('mspd', 3)):
+    lib.bop_profile_sum_ms(slot, args.steps, byref(s_ms), byref(s_n))
+    parts[name] = s_ms.value / max(1, s_n.value)
+  ms_e2e, _, win_e2e, out_e2e = timed(step_e2e, args.steps, args.warmup, sampler)
+  lib.bop_profile_enable(0)
+  same = bool(torch.equal(out_res[:, :len(TAUS) + 2] if world == 1 else out_res[:0], out_e2e if world == 1 else out_e2e[:0]))
+  clocks = None
+  if rank == 0:
+    time.sleep(0.2)
+    sampler.stop()
+    clocks = sampler.summary(win_res[0], win_res[1])
+
+  if rank != 0:
+    if world > 1:
+      dist.destroy_process_group()
+    return None
+
+  value = P * world * args.steps / (ms_res * 1e-3)
+  e2e_v = P * world * args.steps / (ms_e2e * 1e-3)
+  peaks = {}
+  try:
+    peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+  except Exception:
+    pass
+  peak = float(peaks.get('hbm_gbs', 6650.0))
+  # Algorithmic bytes of the fused VSD kernel per launch: per evaluated pair
+  # 3 reads + 2 z-buffer writes of 4 B x H x W plus the mesh twice; gated pairs move nothing.
+  alg_pair = 5 * 4 * H * W + 2 * (12 * n_verts + 12 * n_faces)
+  achieved = n_active * alg_pair / (fused_ms * 1e-3) / 1e9
+  traffic = None
+  try:
+    traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['fused_kernel_dram_bytes_per_launch']
+  except Exception:
+    pass
+  h2d = sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_d16, h_im, h_K, h_scale)) + \
+    sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_K))
+  line = {
+    'metric': 'pose-error pairs/sec (VSD+MSSD+MSPD)', 'value': value, 'unit': 'pairs/s',
+    'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+    'ms_per_step': ms_res / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+    'vs_baseline': None, 'dtype': 'f32 raster + f64 pixel/vertex arithmetic', 'data': 'synthetic',
+    'config': {'workload': WORKLOAD % P, 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
+               'l2': 'inputs larger than L2 (12.3 GB of depth per pass)',
+               'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
+               'exchange': 'all-gather of error records per step' if world > 1 else 'none'},
+    'e2e': {'value': e2e_v, 'unit': 'pairs/s', 'ms_per_step': ms_e2e / args.steps,
+            'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(h_out.numel() * 8),
+            'matches_resident': same},
+    'gpu_launches': int(launches),
+    'clocks': clocks,
+    'roofline': {'bound': 'hbm', 'kernel': 'fused_kernel<STEP> (raster x2 + pixel pass)',
+                 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                 'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback 6650',
+                 'traffic': traffic, 'kernel_ms': fused_ms, 'algorithmic_bytes_per_pair': alg_pair,
+                 'other_kernels_ms': parts},
+  }
+  if world == 1 and not args.no_cpu_baseline:
+    v, ms_step, _ = cpu_arm(P, args.cpu_sample, 1, 1, 0)
+    line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': 1, 'kind': 'port',
+                            'sample': '%d of the %d pairs, oracle port (numpy pose_error + C rasteriser), 1 core'
+                                      % (args.cpu_sample, P)}
+  if world > 1:
+    dist.destroy_process_group()
+  return line
+
+
+def ctypes_double():
+  import ctypes
+  return ctypes.c_double(0.0)
+
+
+def ctypes_int():
+  import ctypes
+  return ctypes.c_int(0)
+
+
+def byref(x):
+  import ctypes
+  return ctypes.byref(x)
+
+
+def reference_arm(args):
+  """The reference's CPU implementation of the path = the oracle port (the reference is Python
+  + OpenGL and cannot run on the box), on all host cores, bounded sample per step."""
+  rank = int(os.environ.get('RANK', '0'))
+  if rank != 0:
+    return None
+  cores = os.cpu_count() or 1
+  cores = min(cores, 64)
+  sample = max(8 * cores, 64)
+  v, ms_step, _ = cpu_arm(args.pairs, sample, cores, max(1, args.steps), min(args.warmup, 1))
+  cb = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port',
+        'sample': '%d of the %d pairs per step, oracle port on %d processes' % (sample, args.pairs, cores)}
+  return {
+    'impl': 'reference', 'metric': 'pose-error pairs/sec (VSD+MSSD+MSPD)', 'value': v, 'unit': 'pairs/s',
+    'n_gpus': int(os.environ.get('WORLD_SIZE', '1')), 'steps': args.steps, 'warmup': args.warmup,
+    'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+    'dtype': 'f64', 'data': 'synthetic', 'config': {'workload': WORKLOAD % args.pairs},
+    'cpu_baseline': cb,
+    'e2e': {'value': v, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    'gpu_launches': 0,
+  }
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--steps', type=int, default=10)
+  ap.add_argument('--warmup', type=int, default=3)
+  ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+  ap.add_argument('--pairs', type=int, default=10000)
+  ap.add_argument('--cpu-sample', type=int, default=256)
+  ap.add_argument('--no-cpu-baseline', action='store_true')
+  args = ap.parse_args()
+  if args.impl == 'reference':
+    line = reference_arm(args)
+  else:
+    args.warmup = max(args.warmup, 3)
+    line = gpu_arm(args)
+  if line is not None:
+    print(json.dumps(line))
+
+
+if __name__ == '__main__':
+  main()

@@ -24,6 +24,65 @@ int bop_set_error_msg(int code, const char* msg) {
 }
 void bop_count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
+// ---------------------------------------------------------------------------------
+// Per-kernel timing: a ring of CUDA event pairs per slot, recorded on the launching stream.
+// ---------------------------------------------------------------------------------
+namespace {
+constexpr int kProfRing = 256;
+struct ProfSlot {
+  cudaEvent_t beg[kProfRing], end[kProfRing];
+  bool made = false;
+  uint64_t n = 0;   // completed begin/end pairs
+};
+ProfSlot g_prof[BOP_PROF_SLOTS];
+bool g_prof_on = false;
+}  // namespace
+
+void bop_prof_begin(int slot, cudaStream_t s) {
+  if (!g_prof_on) return;
+  ProfSlot& p = g_prof[slot];
+  if (!p.made) {
+    for (int i = 0; i < kProfRing; ++i) { cudaEventCreate(&p.beg[i]); cudaEventCreate(&p.end[i]); }
+    p.made = true;
+  }
+  cudaEventRecord(p.beg[p.n % kProfRing], s);
+}
+void bop_prof_end(int slot, cudaStream_t s) {
+  if (!g_prof_on) return;
+  ProfSlot& p = g_prof[slot];
+  cudaEventRecord(p.end[p.n % kProfRing], s);
+  p.n++;
+}
+
+extern "C" int bop_profile_enable(int on) {
+  g_prof_on = on != 0;
+  if (!g_prof_on) for (int i = 0; i < BOP_PROF_SLOTS; ++i) g_prof[i].n = 0;
+  return 0;
+}
+extern "C" int bop_profile_reset(void) {
+  for (int i = 0; i < BOP_PROF_SLOTS; ++i) g_prof[i].n = 0;
+  return 0;
+}
+// Sum of the device durations (ms) of the last `last_n` timed launches of `slot` (all if 0).
+// Synchronises on the recorded events.
+extern "C" int bop_profile_sum_ms(int slot, int last_n, double* sum_ms, int* count) {
+  BOP_REQUIRE(slot >= 0 && slot < BOP_PROF_SLOTS && sum_ms && count, "bop_profile_sum_ms: bad arguments");
+  ProfSlot& p = g_prof[slot];
+  uint64_t n = p.n < (uint64_t)kProfRing ? p.n : (uint64_t)kProfRing;
+  if (last_n > 0 && (uint64_t)last_n < n) n = (uint64_t)last_n;
+  double sum = 0.0;
+  for (uint64_t k = 0; k < n; ++k) {
+    const uint64_t i = (p.n - 1 - k) % kProfRing;
+    BOP_CUDA(cudaEventSynchronize(p.end[i]));
+    float ms = 0.f;
+    BOP_CUDA(cudaEventElapsedTime(&ms, p.beg[i], p.end[i]));
+    sum += ms;
+  }
+  *sum_ms = sum;
+  *count = (int)n;
+  return 0;
+}
+
 extern "C" int bop_abi_version(void) { return BOP_B200_ABI_VERSION; }
 extern "C" const char* bop_last_error(void) { return g_err.c_str(); }
 extern "C" int bop_device_count(void) {

@@ -444,10 +444,12 @@ static int launch_sym_max(int mode, const bop_model_dev* models, const int32_t* 
   fill_u64_kernel<<<(n_pairs + 255) / 256, 256, 0, s>>>(bits, BOP_INF_BITS_F64, n_pairs);
   BOP_LAUNCH_CHECK();
   dim3 grid(n_pairs, groups);
+  bop_prof_begin(mode == 0 ? BOP_PROF_MSSD : BOP_PROF_MSPD, s);
   if (mode == 0)
     sym_max_kernel<0><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, bits);
   else
     sym_max_kernel<1><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, bits);
+  bop_prof_end(mode == 0 ? BOP_PROF_MSSD : BOP_PROF_MSPD, s);
   BOP_LAUNCH_CHECK();
   return 0;
 }
@@ -514,7 +516,9 @@ extern "C" int bop_adi_dev(const bop_model_dev* models, const int32_t* obj_idx,
   BOP_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)n_pairs, s));
   const int qblocks = (max_pts + kThreads * kAdiQ - 1) / (kThreads * kAdiQ);
   dim3 grid(n_pairs, qblocks);
+  bop_prof_begin(BOP_PROF_ADI, s);
   adi_kernel<<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, gate, out);
+  bop_prof_end(BOP_PROF_ADI, s);
   BOP_LAUNCH_CHECK();
   mean_finalize_kernel<<<(n_pairs + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_est, pose_gt,
                                                             n_pairs, gate, out);

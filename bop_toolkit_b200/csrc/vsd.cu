@@ -715,7 +715,10 @@ int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
   const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
   BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = sm_count() * g_tune.ctas_per_sm;
+  const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : BOP_PROF_VSD_FUSED;
+  bop_prof_begin(slot, s);
   fused_kernel<MODE><<<grid, g_tune.threads, smem, s>>>(a);
+  bop_prof_end(slot, s);
   BOP_LAUNCH_CHECK();
   return 0;
 }
@@ -730,6 +733,7 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
   BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
   int4* bbox = (int4*)(ws + L.bbox);
   const int warps = n * n_poses;
+  bop_prof_begin(BOP_PROF_VSD_PLAN, s);
   bbox_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
                                                        diameters, cam_mode, n, n_poses, H, W, gate, bbox);
   BOP_LAUNCH_CHECK();
@@ -737,6 +741,7 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
                                               n, n_poses, H, W, g_tune.tile_px, bbox,
                                               (PairDesc*)(ws + L.desc), (WorkItem*)(ws + L.work),
                                               (PlanCounters*)(ws + L.ctr), L.max_items);
+  bop_prof_end(BOP_PROF_VSD_PLAN, s);
   BOP_LAUNCH_CHECK();
   return 0;
 }
@@ -869,12 +874,14 @@ extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth
   const int ngroups = pp.H * ((pp.W + 3) >> 2);
   const int chunk = kK2Threads * kK2GroupsPerThread;
   dim3 grid(n_pairs, (ngroups + chunk - 1) / chunk);
+  bop_prof_begin(BOP_PROF_K2, s);
   if (prm->cost_type == BOP_COST_TLINEAR)
     pixel_pass_kernel<MODE_TLINEAR><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
                                                                depth_gt, diameters, counts, tl, pp);
   else
     pixel_pass_kernel<MODE_STEP><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
                                                             depth_gt, diameters, counts, tl, pp);
+  bop_prof_end(BOP_PROF_K2, s);
   BOP_LAUNCH_CHECK();
   vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, tl, n_pairs, pp.n_taus,
                                                             prm->cost_type, errors_out,

@@ -88,6 +88,14 @@ int         bop_device_count(void);
 /* Number of kernels launched by this library in the calling process so far. */
 uint64_t    bop_kernel_launch_count(void);
 
+/* Per-kernel device timing (CUDA events on the launching stream), used by bench.py for the
+ * roofline figure.  Slots: 0 fused VSD kernel, 1 VSD bbox+plan, 2 MSSD, 3 MSPD, 4 K2 pixel pass,
+ * 5 render, 6 ADI.  bop_profile_sum_ms synchronises on the recorded events and returns the summed
+ * duration of the last `last_n` timed launches of the slot (0 = all kept, ring of 256).        */
+int bop_profile_enable(int on);
+int bop_profile_reset(void);
+int bop_profile_sum_ms(int slot, int last_n, double* sum_ms, int* count);
+
 /* ---- K5: re / te ----------------------------------------------------------
  * pose_error.re (pose_error.py:187-202), pose_error.te (pose_error.py:205-214).
  * re_out / te_out: [n_pairs] float64; either may be NULL.                      */
