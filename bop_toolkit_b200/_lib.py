@@ -66,12 +66,12 @@ _SIGNATURES = {
   'bop_add_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
   'bop_proj_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P]),
   'bop_adi_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
-  'bop_render_workspace_bytes': (ctypes.c_size_t, [_I]),
-  'bop_render_depth_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P, ctypes.c_size_t, _P]),
-  'bop_vsd_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I]),
+  'bop_render_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I, _I]),
+  'bop_render_depth_dev': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, ctypes.c_size_t, _P]),
+  'bop_vsd_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I, _I]),
   'bop_vsd_from_depth_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P,
                                    ctypes.c_size_t, _P]),
-  'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, ctypes.c_size_t,
+  'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
                        _P]),
   'bop_model_upload': (_I, [_P, _I, _P, _I, _P, _I, ctypes.c_double, _P, _P]),
   'bop_model_free': (_I, [_P, _P]),

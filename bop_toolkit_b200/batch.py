@@ -323,7 +323,7 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
       diam = to_device(np.ascontiguousarray(np.broadcast_to(
         np.asarray(diameter_override, dtype=np.float64), (n,))), torch.float64, dev, (n,))
   outs, cnts = [], []
-  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W, models.max_pts)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     for chunk in _tau_chunks(taus):
@@ -334,7 +334,7 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
       rc = _lib.lib().bop_vsd_dev(
         models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
         sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
-        diam.data_ptr() if diam is not None else None, n,
+        diam.data_ptr() if diam is not None else None, n, models.max_pts,
         ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
         ws.data_ptr(), wsb, _stream_ptr())
       _lib.check(rc)
@@ -375,7 +375,7 @@ def vsd_from_depth_batch(depth_est, depth_gt, depth_test, im_idx, K, diameters, 
   if code == _lib.DEPTH_U16:
     sc = to_device(depth_scale if depth_scale is not None else np.ones(n_im, np.float32),
                    torch.float32, dev, (n_im,))
-  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W, 1)
   ws = _workspace(dev, wsb)
   outs, cnts = [], []
   with torch.cuda.device(dev):
@@ -409,11 +409,12 @@ def render_batch(models, obj, poses, cams, height, width):
   if c.numel() == 4:
     c = c.reshape(1, 4).expand(n, 4).contiguous()
   out = torch.empty((n, int(height), int(width)), dtype=torch.float32, device=dev)
-  wsb = _lib.lib().bop_vsd_workspace_bytes(n, int(height), int(width))
+  wsb = _lib.lib().bop_render_workspace_bytes(n, int(height), int(width), models.max_pts)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     rc = _lib.lib().bop_render_depth_dev(models.table.data_ptr(), oi.data_ptr(), p.data_ptr(),
-                                         c.data_ptr(), n, int(height), int(width), out.data_ptr(),
+                                         c.data_ptr(), n, models.max_pts, int(height), int(width),
+                                         out.data_ptr(),
                                          ws.data_ptr(), wsb, _stream_ptr())
   _lib.check(rc)
   return out

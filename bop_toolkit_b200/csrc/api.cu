@@ -280,10 +280,12 @@ extern "C" int bop_render_depth_host(const bop_model_dev* model_dev, const doubl
   RC(p.upload(pose, sizeof(double) * 12 * (size_t)n));
   RC(c.upload(cam, sizeof(double) * 4 * (size_t)n));
   RC(zeros_i32(oi, n)); RC(o.alloc(ob));
-  const size_t wsb = bop_vsd_workspace_bytes(n, height, width);
+  bop_model_dev mh;
+  BOP_CUDA(cudaMemcpy(&mh, model_dev, sizeof(mh), cudaMemcpyDeviceToHost));
+  const size_t wsb = bop_render_workspace_bytes(n, height, width, mh.n_pts);
   RC(ws.alloc(wsb));
-  RC(bop_render_depth_dev(model_dev, oi.as<int32_t>(), p.as<double>(), c.as<double>(), n, height,
-                          width, o.as<float>(), ws.p, wsb, nullptr));
+  RC(bop_render_depth_dev(model_dev, oi.as<int32_t>(), p.as<double>(), c.as<double>(), n, mh.n_pts,
+                          height, width, o.as<float>(), ws.p, wsb, nullptr));
   return download(depth_out, o.p, ob);
 }
 
@@ -306,10 +308,12 @@ extern "C" int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_e
   RC(ii.upload(im_idx, sizeof(int32_t) * (size_t)n_pairs));
   RC(kk.upload(K, sizeof(double) * 9 * (size_t)n_im));
   RC(zeros_i32(oi, n_pairs)); RC(e.alloc(eb));
-  const size_t wsb = bop_vsd_workspace_bytes(n_pairs, prm->height, prm->width);
+  bop_model_dev mh;
+  BOP_CUDA(cudaMemcpy(&mh, model_dev, sizeof(mh), cudaMemcpyDeviceToHost));
+  const size_t wsb = bop_vsd_workspace_bytes(n_pairs, prm->height, prm->width, mh.n_pts);
   RC(ws.alloc(wsb));
   RC(bop_vsd_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), d.p,
                  depth_scale ? sc.as<float>() : nullptr, ii.as<int32_t>(), kk.as<double>(), nullptr, n_pairs,
-                 prm, e.as<double>(), nullptr, ws.p, wsb, nullptr));
+                 mh.n_pts, prm, e.as<double>(), nullptr, ws.p, wsb, nullptr));
   return download(errors_out, e.p, eb);
 }

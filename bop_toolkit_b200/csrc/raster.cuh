@@ -8,14 +8,20 @@
 //     (u, v) = (c + 0.5, r + 0.5);
 //   * value = nearest-surface camera Z at the sample point (1/Z is affine in screen space), depth
 //     test LESS, no culling, no blending; background = 0;
-//   * coverage ties (sample exactly on an edge) are resolved with the top-left rule, so that a
-//     shared edge is drawn exactly once and a closed mesh is watertight.
+//   * like every OpenGL implementation, window positions are snapped to a sub-pixel grid before
+//     rasterisation (GL_SUBPIXEL_BITS; 8 bits here = 1/256 px), which makes the edge functions
+//     exact integers: coverage is watertight by construction and the top-left rule resolves
+//     samples that lie exactly on an edge, so a shared edge is drawn exactly once.
 //
-// Watertightness in float32: the edge function of an edge is always evaluated from a CANONICAL
-// endpoint order (lexicographic in the projected position) with a pinned operation sequence, so
-// the two triangles sharing an edge see bit-identical values of opposite sign.
+// Vertices are projected ONCE per (pose, vertex) by project_kernel (vsd.cu) into a 16-byte record;
+// the per-triangle work here is three 128-bit gathers plus integer setup.
 #pragma once
 #include "common.cuh"
+
+constexpr int kSubBits = 8;
+constexpr int kSubOne = 1 << kSubBits;          // 256 sub-pixel units per pixel
+constexpr int kFpClamp = 1 << 29;               // |x_fp| <= 2^29  (2^21 px)
+constexpr int kSmallExtentFp = 1 << 15;         // 128 px: 32-bit edge functions are exact below
 
 struct PoseCamF {
   float r[9];
@@ -23,112 +29,160 @@ struct PoseCamF {
   float fx, fy, cxh, cyh;  // cxh = cx - 0.5, cyh = cy - 0.5: pixel centres land on integers
 };
 
-struct Vtx {
-  float x, y, iz;  // shifted window position and 1/Z
+// Projected vertex record: snapped window position (sub-pixel units, pixel centres at multiples
+// of 256), 1/Z, validity.
+struct __align__(16) PVert {
+  int x, y;
+  float iz;
+  int valid;
 };
 
-// Projects one model vertex.  Returns false for points on or behind the camera plane (outside the
-// parity domain: the reference's near plane would be <= 0 there, renderer_vispy.py:447-452).
-__device__ __forceinline__ bool project_vertex(const PoseCamF& P, const float4 v, Vtx& o) {
+__device__ __forceinline__ PVert project_vertex(const PoseCamF& P, const float4 v) {
+  PVert o;
   const float X = __fmaf_rn(P.r[0], v.x, __fmaf_rn(P.r[1], v.y, __fmaf_rn(P.r[2], v.z, P.t[0])));
   const float Y = __fmaf_rn(P.r[3], v.x, __fmaf_rn(P.r[4], v.y, __fmaf_rn(P.r[5], v.z, P.t[1])));
   const float Z = __fmaf_rn(P.r[6], v.x, __fmaf_rn(P.r[7], v.y, __fmaf_rn(P.r[8], v.z, P.t[2])));
-  if (!(Z > 1e-6f)) return false;
-  const float iz = __frcp_rn(Z);
+  // Points on or behind the camera plane are outside the parity domain (the reference's near
+  // plane would be <= 0 there, renderer_vispy.py:447-452): triangles touching them are dropped.
+  o.valid = (Z > 1e-6f) ? 1 : 0;
+  const float iz = __frcp_rn(o.valid ? Z : 1.f);
   o.iz = iz;
-  o.x = __fmaf_rn(__fmul_rn(P.fx, X), iz, P.cxh);
-  o.y = __fmaf_rn(__fmul_rn(P.fy, Y), iz, P.cyh);
+  const float px = __fmaf_rn(__fmul_rn(P.fx, X), iz, P.cxh);
+  const float py = __fmaf_rn(__fmul_rn(P.fy, Y), iz, P.cyh);
+  const float lim = (float)(kFpClamp >> kSubBits);
+  o.x = __float2int_rn(fminf(fmaxf(px, -lim), lim) * (float)kSubOne);
+  o.y = __float2int_rn(fminf(fmaxf(py, -lim), lim) * (float)kSubOne);
+  return o;
+}
+
+// Per-triangle state of the 32-bit path.  Edge k is opposite vertex k:
+//   E_k(x, y) = A_k * (x - x0) + B_k * (y - y0) + C_k     (pixel steps, relative to the bbox origin)
+// oriented so that inside <=> E_k >= 0 for all k after the top-left bias (non-owning edges are
+// biased by -1, which turns "E > 0" into "E - 1 >= 0" on integers).
+struct TriSetup {
+  int A[3], B[3], C[3];   // C already carries the top-left bias
+  int bias[3];            // 0 or 1: added back to get the true edge value for interpolation
+  float iz[3];
+  float inv_area;         // 1 / (E_0 + E_1 + E_2) (true values) = 1 / |2 * area|
+  int bx0, by0, bx1, by1; // candidate pixel rectangle (inclusive), already clipped
+};
+
+// Returns the number of candidate pixels (0: nothing to draw; < 0: -count, the triangle is too
+// large for 32-bit edge functions and must take the 64-bit path).
+__device__ __forceinline__ int tri_setup(const PVert& v0, const PVert& v1, const PVert& v2, int cx0,
+                                         int cy0, int cx1, int cy1, TriSetup& T) {
+  if (!(v0.valid & v1.valid & v2.valid)) return 0;
+  const int minx = min(v0.x, min(v1.x, v2.x)), maxx = max(v0.x, max(v1.x, v2.x));
+  const int miny = min(v0.y, min(v1.y, v2.y)), maxy = max(v0.y, max(v1.y, v2.y));
+  // Pixel centre c is a candidate iff minx <= c*256 <= maxx.
+  const int bx0 = max(cx0, (minx + kSubOne - 1) >> kSubBits), bx1 = min(cx1, maxx >> kSubBits);
+  const int by0 = max(cy0, (miny + kSubOne - 1) >> kSubBits), by1 = min(cy1, maxy >> kSubBits);
+  if (bx1 < bx0 || by1 < by0) return 0;
+  const int n = (bx1 - bx0 + 1) * (by1 - by0 + 1);
+  T.bx0 = bx0; T.bx1 = bx1; T.by0 = by0; T.by1 = by1;
+  if (maxx - minx >= kSmallExtentFp || maxy - miny >= kSmallExtentFp) return -n;
+  // Directed edges a->b: k=0: v1->v2, k=1: v2->v0, k=2: v0->v1.
+  // E(p) = (bx-ax)*(py-ay) - (by-ay)*(px-ax); positive area = clockwise on screen (y down).
+  const int ax[3] = {v1.x, v2.x, v0.x}, ay[3] = {v1.y, v2.y, v0.y};
+  const int bx[3] = {v2.x, v0.x, v1.x}, by[3] = {v2.y, v0.y, v1.y};
+  const int area2 = (v1.x - v0.x) * (v2.y - v0.y) - (v1.y - v0.y) * (v2.x - v0.x);
+  if (area2 == 0) return 0;
+  const int s = area2 > 0 ? 1 : -1;
+  const int px0 = bx0 << kSubBits, py0 = by0 << kSubBits;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int dx = s * (bx[k] - ax[k]), dy = s * (by[k] - ay[k]);
+    // value at the bbox origin pixel; per-pixel steps are dE/dx = -dy*256, dE/dy = dx*256
+    const int e0 = dx * (py0 - ay[k]) - dy * (px0 - ax[k]);
+    // top-left rule on the clockwise-normalised edge direction: left edge goes up (dy < 0), top
+    // edge is horizontal and goes right (dy == 0, dx > 0)
+    const int own = (dy < 0 || (dy == 0 && dx > 0)) ? 1 : 0;
+    T.bias[k] = 1 - own;
+    T.A[k] = -dy * kSubOne;
+    T.B[k] = dx * kSubOne;
+    T.C[k] = e0 - (1 - own);
+  }
+  T.iz[0] = v0.iz; T.iz[1] = v1.iz; T.iz[2] = v2.iz;
+  T.inv_area = __frcp_rn((float)(s * area2));
+  return n;
+}
+
+__device__ __forceinline__ void z_merge(unsigned* __restrict__ p, float Z) {
+  if (Z > 0.f && Z < 3.0e38f) {
+    const unsigned zb = __float_as_uint(Z);
+    if (zb < *p) atomicMin(p, zb);
+  }
+}
+
+// Rasterises a small triangle (32-bit path) into the z-tile.  One thread.
+__device__ __forceinline__ void tri_raster_small(const TriSetup& T, unsigned* __restrict__ z, int zx0,
+                                                 int zy0, int zstride) {
+  int r0 = T.C[0], r1 = T.C[1], r2 = T.C[2];
+  for (int y = T.by0; y <= T.by1; ++y) {
+    int e0 = r0, e1 = r1, e2 = r2;
+    unsigned* zrow = z + (y - zy0) * zstride - zx0;
+    for (int x = T.bx0; x <= T.bx1; ++x) {
+      if ((e0 | e1 | e2) >= 0) {
+        const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]),
+                    w2 = (float)(e2 + T.bias[2]);
+        // 1/Z is affine in screen space: barycentric blend of the vertex 1/Z values.
+        const float izp = __fmaf_rn(w0, T.iz[0], __fmaf_rn(w1, T.iz[1], __fmul_rn(w2, T.iz[2]))) * T.inv_area;
+        z_merge(zrow + x, __frcp_rn(izp));
+      }
+      e0 += T.A[0]; e1 += T.A[1]; e2 += T.A[2];
+    }
+    r0 += T.B[0]; r1 += T.B[1]; r2 += T.B[2];
+  }
+}
+
+// 64-bit path for large triangles; the candidate rectangle is strided over by `nlanes` lanes.
+struct TriSetup64 {
+  long long A[3], B[3], C[3];
+  int bias[3];
+  float iz[3];
+  float inv_area;
+  int bx0, by0, bx1, by1;
+};
+
+__device__ __forceinline__ bool tri_setup64(const PVert& v0, const PVert& v1, const PVert& v2,
+                                            const TriSetup& Tb, TriSetup64& T) {
+  T.bx0 = Tb.bx0; T.bx1 = Tb.bx1; T.by0 = Tb.by0; T.by1 = Tb.by1;
+  const long long ax[3] = {v1.x, v2.x, v0.x}, ay[3] = {v1.y, v2.y, v0.y};
+  const long long bx[3] = {v2.x, v0.x, v1.x}, by[3] = {v2.y, v0.y, v1.y};
+  const long long area2 = (long long)(v1.x - v0.x) * (v2.y - v0.y) - (long long)(v1.y - v0.y) * (v2.x - v0.x);
+  if (area2 == 0) return false;
+  const long long s = area2 > 0 ? 1 : -1;
+  const long long px0 = (long long)T.bx0 << kSubBits, py0 = (long long)T.by0 << kSubBits;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const long long dx = s * (bx[k] - ax[k]), dy = s * (by[k] - ay[k]);
+    const long long e0 = dx * (py0 - ay[k]) - dy * (px0 - ax[k]);
+    const int own = (dy < 0 || (dy == 0 && dx > 0)) ? 1 : 0;
+    T.bias[k] = 1 - own;
+    T.A[k] = -dy * kSubOne;
+    T.B[k] = dx * kSubOne;
+    T.C[k] = e0 - (1 - own);
+  }
+  T.iz[0] = v0.iz; T.iz[1] = v1.iz; T.iz[2] = v2.iz;
+  T.inv_area = __frcp_rn((float)(s * area2));
   return true;
 }
 
-struct TriSetup {
-  float ax[3], ay[3], dx[3], dy[3];  // canonical edge k: origin (ax,ay), direction (dx,dy)
-  float sg[3];                       // +1/-1: orientation x canonical flip
-  unsigned tl;                       // bit k: edge k owns samples that lie exactly on it
-  float iz[3];                       // 1/Z of the vertex OPPOSITE edge k
-  int bx0, by0, bx1, by1;            // candidate pixel rectangle (inclusive), already clipped
-};
-
-__device__ __forceinline__ void make_edge(const Vtx& a, const Vtx& b, TriSetup& T, int k,
-                                          float& flip) {
-  const bool canon = (a.x < b.x) || (a.x == b.x && a.y < b.y);
-  const float px = canon ? a.x : b.x, py = canon ? a.y : b.y;
-  const float qx = canon ? b.x : a.x, qy = canon ? b.y : a.y;
-  T.ax[k] = px;
-  T.ay[k] = py;
-  T.dx[k] = qx - px;
-  T.dy[k] = qy - py;
-  flip = canon ? 1.f : -1.f;
-}
-
-// Canonical edge function value at (x, y): dx*(y-ay) - dy*(x-ax), operation order pinned.
-__device__ __forceinline__ float edge_eval(const TriSetup& T, int k, float x, float y) {
-  const float t1 = __fmul_rn(T.dy[k], x - T.ax[k]);
-  return __fmaf_rn(T.dx[k], y - T.ay[k], -t1);
-}
-
-// Builds the per-triangle state.  clip = inclusive pixel rectangle of the z-tile.
-// Returns the number of candidate pixels (0 = nothing to draw).
-__device__ __forceinline__ int tri_setup(const PoseCamF& P, const float4* __restrict__ verts,
-                                         const int4 f, int cx0, int cy0, int cx1, int cy1,
-                                         TriSetup& T) {
-  Vtx v0, v1, v2;
-  const bool ok0 = project_vertex(P, __ldg(verts + f.x), v0);
-  const bool ok1 = project_vertex(P, __ldg(verts + f.y), v1);
-  const bool ok2 = project_vertex(P, __ldg(verts + f.z), v2);
-  if (!(ok0 && ok1 && ok2)) return 0;
-  const float minx = fminf(v0.x, fminf(v1.x, v2.x)), maxx = fmaxf(v0.x, fmaxf(v1.x, v2.x));
-  const float miny = fminf(v0.y, fminf(v1.y, v2.y)), maxy = fmaxf(v0.y, fmaxf(v1.y, v2.y));
-  // Clamp in float before the int conversion (projections can be huge near Z -> 0).
-  const int bx0 = max(cx0, (int)ceilf(fmaxf(minx, -1.0e6f)));
-  const int bx1 = min(cx1, (int)floorf(fminf(maxx, 1.0e6f)));
-  const int by0 = max(cy0, (int)ceilf(fmaxf(miny, -1.0e6f)));
-  const int by1 = min(cy1, (int)floorf(fminf(maxy, 1.0e6f)));
-  if (bx1 < bx0 || by1 < by0) return 0;
-  T.bx0 = bx0; T.bx1 = bx1; T.by0 = by0; T.by1 = by1;
-  // Directed edges: k=0: v1->v2 (opposite v0), k=1: v2->v0, k=2: v0->v1.
-  float f0, f1, f2;
-  make_edge(v1, v2, T, 0, f0);
-  make_edge(v2, v0, T, 1, f1);
-  make_edge(v0, v1, T, 2, f2);
-  T.iz[0] = v0.iz; T.iz[1] = v1.iz; T.iz[2] = v2.iz;
-  // Twice the signed area: directed edge v0->v1 evaluated at v2.  Positive = clockwise on screen
-  // (y down).
-  const float area2 = f2 * edge_eval(T, 2, v2.x, v2.y);
-  if (!(area2 != 0.f)) return 0;  // degenerate (also rejects NaN)
-  const float o = area2 > 0.f ? 1.f : -1.f;
-  T.sg[0] = f0 * o; T.sg[1] = f1 * o; T.sg[2] = f2 * o;
-  // Top-left ownership, on the edge direction as seen by the clockwise-normalised triangle:
-  // left edge = going up (dy < 0), top edge = horizontal going right (dy == 0, dx > 0).
-  unsigned tl = 0;
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const float ex = T.sg[k] * T.dx[k], ey = T.sg[k] * T.dy[k];
-    if (ey < 0.f || (ey == 0.f && ex > 0.f)) tl |= 1u << k;
-  }
-  T.tl = tl;
-  return (bx1 - bx0 + 1) * (by1 - by0 + 1);
-}
-
-// Tests one pixel centre and, if covered, merges its depth into the z-tile.
-// zrow0/zx0: tile origin (pixel coords), zstride: tile row pitch in pixels.
-__device__ __forceinline__ void tri_pixel(const TriSetup& T, int x, int y, unsigned* __restrict__ z,
-                                          int zx0, int zy0, int zstride) {
-  const float fx = (float)x, fy = (float)y;
-  const float w0 = T.sg[0] * edge_eval(T, 0, fx, fy);
-  const float w1 = T.sg[1] * edge_eval(T, 1, fx, fy);
-  const float w2 = T.sg[2] * edge_eval(T, 2, fx, fy);
-  const bool in0 = (w0 > 0.f) || (w0 == 0.f && (T.tl & 1u));
-  const bool in1 = (w1 > 0.f) || (w1 == 0.f && (T.tl & 2u));
-  const bool in2 = (w2 > 0.f) || (w2 == 0.f && (T.tl & 4u));
-  if (in0 && in1 && in2) {
-    const float num = w0 + w1 + w2;
-    const float den = __fmaf_rn(w0, T.iz[0], __fmaf_rn(w1, T.iz[1], __fmul_rn(w2, T.iz[2])));
-    const float Z = __fdiv_rn(num, den);
-    if (Z > 0.f && Z < 3.0e38f) {
-      const unsigned zb = __float_as_uint(Z);
-      unsigned* p = z + (y - zy0) * zstride + (x - zx0);
-      if (zb < *p) atomicMin(p, zb);
+__device__ __forceinline__ void tri_raster_large(const TriSetup64& T, int lane, int nlanes,
+                                                 unsigned* __restrict__ z, int zx0, int zy0,
+                                                 int zstride) {
+  const int bw = T.bx1 - T.bx0 + 1;
+  const int n = bw * (T.by1 - T.by0 + 1);
+  for (int c = lane; c < n; c += nlanes) {
+    const int yy = c / bw, xx = c - yy * bw;
+    const long long e0 = T.C[0] + T.A[0] * xx + T.B[0] * yy;
+    const long long e1 = T.C[1] + T.A[1] * xx + T.B[1] * yy;
+    const long long e2 = T.C[2] + T.A[2] * xx + T.B[2] * yy;
+    if ((e0 | e1 | e2) >= 0) {
+      // Same expression as the 32-bit path, so a pixel's depth does not depend on which path drew it.
+      const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]), w2 = (float)(e2 + T.bias[2]);
+      const float izp = __fmaf_rn(w0, T.iz[0], __fmaf_rn(w1, T.iz[1], __fmul_rn(w2, T.iz[2]))) * T.inv_area;
+      z_merge(z + (T.by0 + yy - zy0) * zstride + (T.bx0 + xx - zx0), __frcp_rn(izp));
     }
   }
 }

@@ -14,6 +14,8 @@
 // warp shuffles + shared atomics + one global atomic per counter.  The pixel arithmetic mirrors
 // the reference's dtype ladder operation by operation, so given equal rendered
 // depths the integer counts -- and hence the errors -- are bit-identical to numpy's.
+#include <limits.h>
+
 #include "raster.cuh"
 
 namespace {
@@ -72,16 +74,20 @@ __device__ __forceinline__ void make_posecam(const double* pose, double fx, doub
 }
 
 // ---------------------------------------------------------------------------------
-// Pass A: exact projected bounding box per (item, pose).  One warp per (item, pose).
+// Pass A: project every vertex ONCE per (item, pose) into a 16-byte PVert record (snapped window
+// position + 1/Z) and reduce the exact projected bounding box.  One warp per (item, pose);
+// coalesced 128-bit loads and stores.
 // cam_mode 0: K is [n_im][9] indexed through im_idx (VSD); 1: cam is [n][4] fx,fy,cx,cy (render).
+// pv out:   [n][n_poses][pv_stride] PVert
 // bbox out: [n][n_poses][4] = x0,y0,x1,y1 inclusive, clipped to the image; empty => x1 < x0.
 // ---------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-bbox_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
-            const double* __restrict__ pose_a, const double* __restrict__ pose_b,
-            const int32_t* __restrict__ im_idx, const double* __restrict__ K,
-            const double* __restrict__ diameters, int cam_mode, int n,
-            int n_poses, int H, int W, int gate, int4* __restrict__ bbox) {
+project_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
+               const double* __restrict__ pose_a, const double* __restrict__ pose_b,
+               const int32_t* __restrict__ im_idx, const double* __restrict__ K,
+               const double* __restrict__ diameters, int cam_mode, int n,
+               int n_poses, int H, int W, int gate, int pv_stride, PVert* __restrict__ pv,
+               int4* __restrict__ bbox) {
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (gw >= n * n_poses) return;
@@ -108,28 +114,27 @@ bbox_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict_
   PoseCamF P;
   make_posecam(pose, fx, fy, cx, cy, P);
   const float4* __restrict__ verts = (const float4*)M.verts4;
-  float minx = 3e38f, miny = 3e38f, maxx = -3e38f, maxy = -3e38f;
+  PVert* __restrict__ out = pv + (size_t)gw * pv_stride;
+  int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
   for (int i = lane; i < M.n_pts; i += 32) {
-    Vtx v;
-    if (project_vertex(P, __ldg(verts + i), v)) {
-      minx = fminf(minx, v.x); maxx = fmaxf(maxx, v.x);
-      miny = fminf(miny, v.y); maxy = fmaxf(maxy, v.y);
+    const PVert v = project_vertex(P, __ldg(verts + i));
+    *(int4*)(out + i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
+    if (v.valid) {
+      minx = min(minx, v.x); maxx = max(maxx, v.x);
+      miny = min(miny, v.y); maxy = max(maxy, v.y);
     }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    minx = fminf(minx, __shfl_xor_sync(BOP_FULL_MASK, minx, o));
-    miny = fminf(miny, __shfl_xor_sync(BOP_FULL_MASK, miny, o));
-    maxx = fmaxf(maxx, __shfl_xor_sync(BOP_FULL_MASK, maxx, o));
-    maxy = fmaxf(maxy, __shfl_xor_sync(BOP_FULL_MASK, maxy, o));
-  }
+  minx = __reduce_min_sync(BOP_FULL_MASK, minx); miny = __reduce_min_sync(BOP_FULL_MASK, miny);
+  maxx = __reduce_max_sync(BOP_FULL_MASK, maxx); maxy = __reduce_max_sync(BOP_FULL_MASK, maxy);
   if (lane == 0) {
-    int4 b;
-    b.x = max(0, (int)ceilf(fmaxf(minx, -1.0e6f)));
-    b.y = max(0, (int)ceilf(fmaxf(miny, -1.0e6f)));
-    b.z = min(W - 1, (int)floorf(fminf(maxx, 1.0e6f)));
-    b.w = min(H - 1, (int)floorf(fminf(maxy, 1.0e6f)));
-    if (b.z < b.x || b.w < b.y) b = make_int4(0, 0, -1, -1);
+    int4 b = make_int4(0, 0, -1, -1);
+    if (maxx >= minx) {
+      b.x = max(0, (minx + kSubOne - 1) >> kSubBits);
+      b.y = max(0, (miny + kSubOne - 1) >> kSubBits);
+      b.z = min(W - 1, maxx >> kSubBits);
+      b.w = min(H - 1, maxy >> kSubBits);
+      if (b.z < b.x || b.w < b.y) b = make_int4(0, 0, -1, -1);
+    }
     bbox[gw] = b;
   }
 }
@@ -335,6 +340,8 @@ struct FusedArgs {
   const PairDesc* desc;
   const WorkItem* work;
   PlanCounters* ctr;
+  const PVert* pv;              // [n][n_poses][pv_stride] projected vertices
+  int pv_stride;
   const void* depth_test;       // VSD
   const float* depth_scale;     // VSD, u16 input only
   unsigned long long* counts;   // VSD step: [n][2+BOP_MAX_TAUS] u64
@@ -402,26 +409,32 @@ __global__ void __launch_bounds__(512, 1) fused_kernel(const __grid_constant__ F
     __syncthreads();
 
     const bop_model_dev M = a.models[sD.obj];
-    const float4* __restrict__ verts = (const float4*)M.verts4;
     const int4* __restrict__ faces = (const int4*)M.faces4;
     const int F = M.n_faces;
 
     for (int p = 0; p < n_poses; ++p) {
-      PoseCamF P = sD.pose[p];
       unsigned* const z = zt + (size_t)p * a.tile_px;
+      const PVert* __restrict__ pv = a.pv + ((size_t)sW.pair * n_poses + p) * a.pv_stride;
       for (int f = tid; f < F; f += nthr) {
+        const int4 fi = __ldg(faces + f);
+        const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
+                   r2 = __ldg((const int4*)(pv + fi.z));
+        const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
+        const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
+        const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
         TriSetup T;
-        const int n = tri_setup(P, verts, __ldg(faces + f), cx0, cy0, cx1, cy1, T);
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
         if (n == 0) continue;
-        bool inline_it = n <= a.small_tri_px;
-        if (!inline_it) {
+        if (n > 0 && n <= a.small_tri_px) {
+          tri_raster_small(T, z, cx0, cy0, w);
+        } else {
           const int slot = atomicAdd(&s_q, 1);
-          if (slot < kQueueCap) queue[slot] = f;
-          else inline_it = true;   // queue full: draw it here (slow but correct)
-        }
-        if (inline_it) {
-          for (int y = T.by0; y <= T.by1; ++y)
-            for (int x = T.bx0; x <= T.bx1; ++x) tri_pixel(T, x, y, z, cx0, cy0, w);
+          if (slot < kQueueCap) {
+            queue[slot] = f;
+          } else {   // queue full: draw it here (slow but correct)
+            TriSetup64 T64;
+            if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+          }
         }
       }
       __syncthreads();
@@ -429,19 +442,20 @@ __global__ void __launch_bounds__(512, 1) fused_kernel(const __grid_constant__ F
       if (nq > 0) {
         // Warp-cooperative path for large triangles: lanes stride over the candidate rectangle.
         for (int qi = warp; qi < nq; qi += nwarps) {
+          const int4 fi = __ldg(faces + queue[qi]);
+          const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
+                     r2 = __ldg((const int4*)(pv + fi.z));
+          const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
+          const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
+          const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
           TriSetup T;
-          const int n = tri_setup(P, verts, __ldg(faces + queue[qi]), cx0, cy0, cx1, cy1, T);
-          const int bw = T.bx1 - T.bx0 + 1;
-          for (int c = lane; c < n; c += 32) {
-            const int yy = c / bw, xx = c - yy * bw;
-            tri_pixel(T, T.bx0 + xx, T.by0 + yy, z, cx0, cy0, w);
-          }
+          TriSetup64 T64;
+          if (tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T) != 0 && tri_setup64(v0, v1, v2, T, T64))
+            tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
         }
       }
       __syncthreads();
       if (tid == 0) s_q = 0;
-      // (the next pose's pushes happen after its own first barrier-free loop; s_q was reset by
-      //  tid 0 before any thread can pass the barrier below)
       __syncthreads();
     }
 
@@ -651,26 +665,38 @@ namespace {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+constexpr size_t kPvBudgetBytes = (size_t)2 << 30;   // projected-vertex scratch per chunk
+
 struct WsLayout {
-  size_t ctr, counts, tl, bbox, desc, work, total;
+  size_t ctr, counts, tl, bbox, desc, work, pv, total;
   unsigned max_items;
+  int chunk;       // items processed per pass (the batch is split so that pv fits the budget)
+  int pv_stride;   // PVert records per (item, pose)
 };
 
-WsLayout ws_layout(int n, int H, int W) {
+WsLayout ws_layout(int n, int H, int W, int n_poses, int max_pts) {
   WsLayout L;
+  L.pv_stride = (max_pts + 7) & ~7;
+  const size_t per_item_pv = (size_t)n_poses * L.pv_stride * sizeof(PVert);
+  size_t chunk = kPvBudgetBytes / (per_item_pv ? per_item_pv : 1);
+  if (chunk < 1) chunk = 1;
+  if (chunk > (size_t)(n > 0 ? n : 1)) chunk = (size_t)(n > 0 ? n : 1);
+  L.chunk = (int)chunk;
+  const int c = L.chunk;
   const int wp = (W + 3) & ~3;
   const int rows_per_band = kMinTilePx / (wp > 0 ? wp : 1);
   const size_t per_item = (size_t)H / (size_t)(rows_per_band > 0 ? rows_per_band : 1) + 2;
-  size_t mi = per_item * (size_t)(n > 0 ? n : 1);
+  size_t mi = per_item * (size_t)c;
   if (mi > 0x7fffffffull) mi = 0x7fffffffull;
   L.max_items = (unsigned)mi;
   size_t off = 0;
   L.ctr = off;    off = align_up(off + sizeof(PlanCounters), 256);
-  L.counts = off; off = align_up(off + (size_t)n * (2 + BOP_MAX_TAUS) * 8, 256);
-  L.tl = off;     off = align_up(off + (size_t)n * BOP_MAX_TAUS * 8, 256);
-  L.bbox = off;   off = align_up(off + (size_t)n * 2 * sizeof(int4), 256);
-  L.desc = off;   off = align_up(off + (size_t)n * sizeof(PairDesc), 256);
+  L.counts = off; off = align_up(off + (size_t)c * (2 + BOP_MAX_TAUS) * 8, 256);
+  L.tl = off;     off = align_up(off + (size_t)c * BOP_MAX_TAUS * 8, 256);
+  L.bbox = off;   off = align_up(off + (size_t)c * 2 * sizeof(int4), 256);
+  L.desc = off;   off = align_up(off + (size_t)c * sizeof(PairDesc), 256);
   L.work = off;   off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
+  L.pv = off;     off = align_up(off + (size_t)c * per_item_pv, 256);
   L.total = off;
   return L;
 }
@@ -734,8 +760,9 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
   int4* bbox = (int4*)(ws + L.bbox);
   const int warps = n * n_poses;
   bop_prof_begin(BOP_PROF_VSD_PLAN, s);
-  bbox_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
-                                                       diameters, cam_mode, n, n_poses, H, W, gate, bbox);
+  project_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
+                                                          diameters, cam_mode, n, n_poses, H, W, gate,
+                                                          L.pv_stride, (PVert*)(ws + L.pv), bbox);
   BOP_LAUNCH_CHECK();
   plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
                                               n, n_poses, H, W, g_tune.tile_px, bbox,
@@ -768,87 +795,100 @@ extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int
   return 0;
 }
 
-extern "C" size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width) {
-  return ws_layout(n_pairs, height, width).total;
+extern "C" size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_pts) {
+  return ws_layout(n_pairs, height, width, 2, max_pts).total;
 }
-extern "C" size_t bop_render_workspace_bytes(int n) {
-  // Image size is not known here; sized for the widest supported image with 1-row bands per 4096 px.
-  return ws_layout(n, 4096, kMaxWidth).total;
+extern "C" size_t bop_render_workspace_bytes(int n, int height, int width, int max_pts) {
+  return ws_layout(n, height, width, 1, max_pts).total;
 }
 
 extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                            const double* pose_est, const double* pose_gt, const void* depth_test,
                            const float* depth_scale, const int32_t* im_idx, const double* K,
-                           const double* diameters, int n_pairs, const bop_vsd_params* prm,
-                           double* errors_out,
-                           int64_t* counts_out, void* workspace, size_t workspace_bytes,
-                           void* stream) {
+                           const double* diameters, int n_pairs, int max_pts,
+                           const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
+                           void* workspace, size_t workspace_bytes, void* stream) {
   if (n_pairs <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && depth_test && im_idx && K && errors_out,
               "bop_vsd_dev: null pointer");
+  BOP_REQUIRE(max_pts >= 1, "bop_vsd_dev: max_pts must be >= 1");
   PixParams pp;
   if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
-  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W);
+  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W, 2, max_pts);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_vsd_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_vsd_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   unsigned char* ws = (unsigned char*)workspace;
-  if (int rc = launch_plan(models, obj_idx, pose_est, pose_gt, im_idx, K, diameters, 0, n_pairs, 2, pp.H, pp.W,
-                           prm->gate, ws, L, s))
-    return rc;
-  FusedArgs a;
-  a.models = models;
-  a.desc = (const PairDesc*)(ws + L.desc);
-  a.work = (const WorkItem*)(ws + L.work);
-  a.ctr = (PlanCounters*)(ws + L.ctr);
-  a.depth_test = depth_test;
-  a.depth_scale = depth_scale;
-  a.counts = (unsigned long long*)(ws + L.counts);
-  a.tl_sums = (double*)(ws + L.tl);
-  a.depth_out = nullptr;
-  a.max_items = L.max_items;
-  a.tile_px = g_tune.tile_px;
-  a.small_tri_px = g_tune.small_tri_px;
-  a.pp = pp;
-  int rc = prm->cost_type == BOP_COST_TLINEAR ? launch_fused<MODE_TLINEAR>(a, pp.W, s)
-                                              : launch_fused<MODE_STEP>(a, pp.W, s);
-  if (rc) return rc;
-  vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(a.counts, a.tl_sums, n_pairs, pp.n_taus,
-                                                            prm->cost_type, errors_out,
-                                                            (long long*)counts_out);
-  BOP_LAUNCH_CHECK();
+  for (int c0 = 0; c0 < n_pairs; c0 += L.chunk) {
+    const int nc = n_pairs - c0 < L.chunk ? n_pairs - c0 : L.chunk;
+    if (int rc = launch_plan(models, obj_idx + c0, pose_est + 12 * (size_t)c0, pose_gt + 12 * (size_t)c0,
+                             im_idx + c0, K, diameters ? diameters + c0 : nullptr, 0, nc, 2, pp.H,
+                             pp.W, prm->gate, ws, L, s))
+      return rc;
+    FusedArgs a;
+    a.models = models;
+    a.desc = (const PairDesc*)(ws + L.desc);
+    a.work = (const WorkItem*)(ws + L.work);
+    a.ctr = (PlanCounters*)(ws + L.ctr);
+    a.pv = (const PVert*)(ws + L.pv);
+    a.pv_stride = L.pv_stride;
+    a.depth_test = depth_test;
+    a.depth_scale = depth_scale;
+    a.counts = (unsigned long long*)(ws + L.counts);
+    a.tl_sums = (double*)(ws + L.tl);
+    a.depth_out = nullptr;
+    a.max_items = L.max_items;
+    a.tile_px = g_tune.tile_px;
+    a.small_tri_px = g_tune.small_tri_px;
+    a.pp = pp;
+    int rc = prm->cost_type == BOP_COST_TLINEAR ? launch_fused<MODE_TLINEAR>(a, pp.W, s)
+                                                : launch_fused<MODE_STEP>(a, pp.W, s);
+    if (rc) return rc;
+    vsd_finalize_kernel<<<(nc + 127) / 128, 128, 0, s>>>(
+        a.counts, a.tl_sums, nc, pp.n_taus, prm->cost_type, errors_out + (size_t)c0 * pp.n_taus,
+        counts_out ? (long long*)counts_out + (size_t)c0 * (2 + pp.n_taus) : nullptr);
+    BOP_LAUNCH_CHECK();
+  }
   return 0;
 }
 
 extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
-                                    const double* pose, const double* cam, int n, int height,
-                                    int width, float* depth_out, void* workspace,
+                                    const double* pose, const double* cam, int n, int max_pts,
+                                    int height, int width, float* depth_out, void* workspace,
                                     size_t workspace_bytes, void* stream) {
   if (n <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose && cam && depth_out, "bop_render_depth_dev: null pointer");
   BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_render_depth_dev: bad image size");
-  const WsLayout L = ws_layout(n, height, width);
+  BOP_REQUIRE(max_pts >= 1, "bop_render_depth_dev: max_pts must be >= 1");
+  const WsLayout L = ws_layout(n, height, width, 1, max_pts);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_render_depth_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_render_depth_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   unsigned char* ws = (unsigned char*)workspace;
   BOP_CUDA(cudaMemsetAsync(depth_out, 0, sizeof(float) * (size_t)n * height * width, s));
-  if (int rc = launch_plan(models, obj_idx, pose, pose, nullptr, cam, nullptr, 1, n, 1, height, width, 0, ws, L, s))
-    return rc;
-  FusedArgs a;
-  memset(&a, 0, sizeof(a));
-  a.models = models;
-  a.desc = (const PairDesc*)(ws + L.desc);
-  a.work = (const WorkItem*)(ws + L.work);
-  a.ctr = (PlanCounters*)(ws + L.ctr);
-  a.depth_out = depth_out;
-  a.max_items = L.max_items;
-  a.tile_px = g_tune.tile_px;
-  a.small_tri_px = g_tune.small_tri_px;
-  a.pp.H = height;
-  a.pp.W = width;
-  a.pp.n_taus = 1;
-  return launch_fused<MODE_RENDER>(a, width, s);
+  for (int c0 = 0; c0 < n; c0 += L.chunk) {
+    const int nc = n - c0 < L.chunk ? n - c0 : L.chunk;
+    if (int rc = launch_plan(models, obj_idx + c0, pose + 12 * (size_t)c0, pose + 12 * (size_t)c0, nullptr,
+                             cam + 4 * (size_t)c0, nullptr, 1, nc, 1, height, width, 0, ws, L, s))
+      return rc;
+    FusedArgs a;
+    memset(&a, 0, sizeof(a));
+    a.models = models;
+    a.desc = (const PairDesc*)(ws + L.desc);
+    a.work = (const WorkItem*)(ws + L.work);
+    a.ctr = (PlanCounters*)(ws + L.ctr);
+    a.pv = (const PVert*)(ws + L.pv);
+    a.pv_stride = L.pv_stride;
+    a.depth_out = depth_out + (size_t)c0 * height * width;
+    a.max_items = L.max_items;
+    a.tile_px = g_tune.tile_px;
+    a.small_tri_px = g_tune.small_tri_px;
+    a.pp.H = height;
+    a.pp.W = width;
+    a.pp.n_taus = 1;
+    if (int rc = launch_fused<MODE_RENDER>(a, width, s)) return rc;
+  }
+  return 0;
 }
 
 extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
@@ -864,7 +904,15 @@ extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth
   PixParams pp;
   if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
   pp.vec_ok = pp.vec_ok && ((uintptr_t)depth_est % 16 == 0) && ((uintptr_t)depth_gt % 16 == 0);
-  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W);
+  // Only the counters at the head of the layout are used here (no projected vertices).
+  WsLayout L = ws_layout(n_pairs, pp.H, pp.W, 2, 1);
+  {
+    size_t off = 0;
+    L.ctr = off;    off = align_up(off + sizeof(PlanCounters), 256);
+    L.counts = off; off = align_up(off + (size_t)n_pairs * (2 + BOP_MAX_TAUS) * 8, 256);
+    L.tl = off;     off = align_up(off + (size_t)n_pairs * BOP_MAX_TAUS * 8, 256);
+    L.bbox = off;
+  }
   BOP_REQUIRE(workspace && workspace_bytes >= L.bbox, "bop_vsd_from_depth_dev: workspace too small");
   cudaStream_t s = (cudaStream_t)stream;
   unsigned char* ws = (unsigned char*)workspace;

@@ -137,10 +137,12 @@ int bop_adi_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * renderer_vispy.py:433-466,509-538; shaders :123-146).  One image per pose:
  * depth_out[b] is H x W float32, nearest-surface camera Z in mm at the pixel
  * centre (c+0.5, r+0.5), 0 = background.  cam: [n][4] float64 fx,fy,cx,cy.
- * workspace: bop_render_workspace_bytes(n) bytes of device memory.             */
-size_t bop_render_workspace_bytes(int n);
+ * max_pts: largest n_pts among the models used (sizes the projected-vertex scratch).
+ * workspace: bop_render_workspace_bytes(n, H, W, max_pts) bytes of device memory, 256-byte
+ * aligned.  Batches whose scratch would exceed 2 GiB are processed in several passes.   */
+size_t bop_render_workspace_bytes(int n, int height, int width, int max_pts);
 int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
-                         const double* pose, const double* cam, int n,
+                         const double* pose, const double* cam, int n, int max_pts,
                          int height, int width, float* depth_out,
                          void* workspace, size_t workspace_bytes, void* stream);
 
@@ -152,8 +154,10 @@ int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * depth_test: [n_im][H][W] (prm->depth_dtype); im_idx: [n_pairs]; K: [n_im][9];
  * depth_scale: [n_im] float32 or NULL; diameters: [n_pairs] float64.
  * errors_out: [n_pairs][n_taus] float64.  counts_out (optional, may be NULL):
- * [n_pairs][2+n_taus] int64 = union, inter, per-tau cost counts (step cost).  */
-size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width);
+ * [n_pairs][2+n_taus] int64 = union, inter, per-tau cost counts (step cost).
+ * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_pts) bytes (max_pts = 1 suffices for
+ * bop_vsd_from_depth_dev, which projects nothing).                              */
+size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_pts);
 int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
                            const int32_t* im_idx, const double* K,
                            const float* depth_est, const float* depth_gt,
@@ -173,7 +177,7 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const double* pose_est, const double* pose_gt,
                 const void* depth_test, const float* depth_scale,
                 const int32_t* im_idx, const double* K,
-                const double* diameters, int n_pairs,
+                const double* diameters, int n_pairs, int max_pts,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);

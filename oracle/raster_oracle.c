@@ -43,9 +43,24 @@ static inline int top_left(double dx, double dy) {
  * depth: [H][W] float32 output, 0 = background
  * Returns 0.
  */
+int oracle_render_depth_sub(const double* pts, int n_pts, const int32_t* faces, int n_faces,
+                            const double* R, const double* t, double fx, double fy, double cx,
+                            double cy, int H, int W, int subpixel_bits, float* depth);
+
 int oracle_render_depth(const double* pts, int n_pts, const int32_t* faces, int n_faces,
                         const double* R, const double* t, double fx, double fy, double cx,
                         double cy, int H, int W, float* depth) {
+  return oracle_render_depth_sub(pts, n_pts, faces, n_faces, R, t, fx, fy, cx, cy, H, W, 0, depth);
+}
+
+/*
+ * subpixel_bits > 0: window positions are snapped to a 2^-bits pixel grid before rasterisation,
+ * as every OpenGL implementation does (GL_SUBPIXEL_BITS, typically 8); 0 = exact positions.
+ */
+int oracle_render_depth_sub(const double* pts, int n_pts, const int32_t* faces, int n_faces,
+                            const double* R, const double* t, double fx, double fy, double cx,
+                            double cy, int H, int W, int subpixel_bits, float* depth) {
+  const double sub = subpixel_bits > 0 ? (double)(1 << subpixel_bits) : 0.0;
   double* zbuf = (double*)malloc(sizeof(double) * (size_t)H * W);
   double* proj = (double*)malloc(sizeof(double) * 3 * (size_t)n_pts); /* u', v', Z */
   if (!zbuf || !proj) { free(zbuf); free(proj); return 1; }
@@ -64,6 +79,10 @@ int oracle_render_depth(const double* pts, int n_pts, const int32_t* faces, int 
       /* shifted so that pixel centres sit on integers */
       proj[3 * i + 0] = fx * X / Z + cx - 0.5;
       proj[3 * i + 1] = fy * Y / Z + cy - 0.5;
+      if (sub > 0.0) {
+        proj[3 * i + 0] = nearbyint(proj[3 * i + 0] * sub) / sub;
+        proj[3 * i + 1] = nearbyint(proj[3 * i + 1] * sub) / sub;
+      }
     } else {
       proj[3 * i + 0] = proj[3 * i + 1] = NAN;
     }

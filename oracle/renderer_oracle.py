@@ -34,19 +34,26 @@ def _lib():
       ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
       ctypes.c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
       ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    _LIB.oracle_render_depth_sub.restype = ctypes.c_int
+    _LIB.oracle_render_depth_sub.argtypes = [
+      ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+      ctypes.c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
+      ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
   return _LIB
 
 
-def render_depth(pts, faces, R, t, fx, fy, cx, cy, height, width):
+def render_depth(pts, faces, R, t, fx, fy, cx, cy, height, width, subpixel_bits=0):
+  """subpixel_bits=0: exact window positions; 8: GL-style snapping to 1/256 px (what the CUDA
+  rasteriser and OpenGL implementations do)."""
   pts = np.ascontiguousarray(pts, dtype=np.float64)
   faces = np.ascontiguousarray(faces, dtype=np.int32)
   R = np.ascontiguousarray(R, dtype=np.float64).reshape(9)
   t = np.ascontiguousarray(t, dtype=np.float64).reshape(3)
   depth = np.empty((height, width), dtype=np.float32)
-  rc = _lib().oracle_render_depth(
+  rc = _lib().oracle_render_depth_sub(
     pts.ctypes.data, pts.shape[0], faces.ctypes.data, faces.shape[0], R.ctypes.data,
     t.ctypes.data, float(fx), float(fy), float(cx), float(cy), int(height), int(width),
-    depth.ctypes.data)
+    int(subpixel_bits), depth.ctypes.data)
   if rc != 0:
     raise MemoryError('oracle_render_depth failed')
   return depth
@@ -55,10 +62,12 @@ def render_depth(pts, faces, R, t, fx, fy, cx, cy, height, width):
 class RendererOracle(object):
   """Renderer interface of bop_toolkit_lib/renderer.py:11-74 ('depth' mode only)."""
 
-  def __init__(self, width, height, mode='depth', shading='phong', bg_color=(0, 0, 0, 0)):
+  def __init__(self, width, height, mode='depth', shading='phong', bg_color=(0, 0, 0, 0),
+               subpixel_bits=0):
     self.width = width
     self.height = height
     self.models = {}
+    self.subpixel_bits = subpixel_bits
 
   def add_object(self, obj_id, model_path=None, **kwargs):
     """`model_path` may be a path to a PLY (read with the package's loader) or kwargs
@@ -76,4 +85,5 @@ class RendererOracle(object):
 
   def render_object(self, obj_id, R, t, fx, fy, cx, cy):
     pts, faces = self.models[obj_id]
-    return {'depth': render_depth(pts, faces, R, t, fx, fy, cx, cy, self.height, self.width)}
+    return {'depth': render_depth(pts, faces, R, t, fx, fy, cx, cy, self.height, self.width,
+                                  self.subpixel_bits)}

@@ -230,6 +230,7 @@ def test_render_vs_oracle_full_size(B, oracle_built):
   t_g[1] = [400.0, 250.0, 700.0]        # partly outside the image
   t_g[2] = [5000.0, 0.0, 700.0]         # fully outside: empty image
   tot_sil = tot_mis = tot_far = n_bad = n_px = 0
+  snap_mis = snap_far = 0
   for i in range(n):
     d = ren.render_object(3, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2])['depth']
     assert d.dtype == np.float32 and d.shape == (480, 640)
@@ -237,12 +238,21 @@ def test_render_vs_oracle_full_size(B, oracle_built):
     sil, mis, far, rel, bad = _render_compare(d, ref)
     tot_sil += sil; tot_mis += mis; tot_far += far
     n_bad += int(bad.sum()); n_px += rel.size
+    # oracle with the same GL-style 1/256 px vertex snapping as the CUDA rasteriser
+    ref8 = renderer_oracle.render_depth(pts, faces, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], 480, 640, 8)
+    _, mis8, far8, _, _ = _render_compare(d, ref8)
+    snap_mis += mis8; snap_far += far8
     if i == 2:
       assert not (d > 0).any() and not (ref > 0).any()
-  assert tot_far == 0                               # zero interior coverage mismatches
+  assert tot_far == 0 and snap_far == 0             # zero interior coverage mismatches
+  # vs exact positions: snapping moves an edge by <= 1/512 px -> <= 0.5 % of silhouette pixels
   assert tot_mis <= 0.005 * tot_sil + 2, (tot_mis, tot_sil)
+  # vs the snapped oracle only float32-vs-float64 projection rounding is left
+  assert snap_mis <= 0.0005 * tot_sil + 2, (snap_mis, tot_sil)
   # per-pixel depth: 1e-3 relative, except pixels straddling a self-occlusion edge
   assert n_bad <= 1e-4 * n_px + 2, (n_bad, n_px)
+  print('render parity: silhouette px %d, coverage mismatches exact-oracle %d, snapped-oracle %d, '
+        'depth outliers %d of %d' % (tot_sil, tot_mis, snap_mis, n_bad, n_px))
 
 
 def test_render_known_answer_top_left(B):
@@ -364,7 +374,7 @@ def test_vsd_fused_equals_render_plus_k2(B):
         if cost == 'step':
           assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
         else:
-          assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=0, atol=1e-12)
+          assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=0, atol=1e-11)
   finally:
     _lib.check(_lib.lib().bop_vsd_set_tuning(24576, 512, 1, 36))
 
