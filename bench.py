@@ -252,6 +252,8 @@ def gpu_arm(args):
   device = torch.device('cuda', local_rank)
   _lib.require_cuda()
   lib = _lib.lib()
+  if os.environ.get('BOP_TUNE'):   # "tile_px,threads,ctas_per_sm,small_tri_px" (0 = keep)
+    _lib.check(lib.bop_vsd_set_tuning(*[int(x) for x in os.environ['BOP_TUNE'].split(',')]))
   P = args.pairs
   K = synth.LM_K
 

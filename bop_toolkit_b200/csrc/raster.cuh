@@ -107,6 +107,20 @@ __device__ __forceinline__ int tri_setup(const PVert& v0, const PVert& v1, const
   return n;
 }
 
+// 1/x on the SFU (MUFU.RCP, <= 1 ulp): deterministic, so a pixel's depth does not depend on the
+// path that drew it; far inside the 1e-3 relative depth tolerance.
+__device__ __forceinline__ float rcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// Depth at a covered sample from the three (true) edge values: 1/Z is affine in screen space.
+__device__ __forceinline__ float tri_depth(float w0, float w1, float w2, const float* iz, float inv_area) {
+  const float izp = __fmaf_rn(w0, iz[0], __fmaf_rn(w1, iz[1], __fmul_rn(w2, iz[2]))) * inv_area;
+  return rcp_fast(izp);
+}
+
 __device__ __forceinline__ void z_merge(unsigned* __restrict__ p, float Z) {
   if (Z > 0.f && Z < 3.0e38f) {
     const unsigned zb = __float_as_uint(Z);
@@ -125,13 +139,35 @@ __device__ __forceinline__ void tri_raster_small(const TriSetup& T, unsigned* __
       if ((e0 | e1 | e2) >= 0) {
         const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]),
                     w2 = (float)(e2 + T.bias[2]);
-        // 1/Z is affine in screen space: barycentric blend of the vertex 1/Z values.
-        const float izp = __fmaf_rn(w0, T.iz[0], __fmaf_rn(w1, T.iz[1], __fmul_rn(w2, T.iz[2]))) * T.inv_area;
-        z_merge(zrow + x, __frcp_rn(izp));
+        z_merge(zrow + x, tri_depth(w0, w1, w2, T.iz, T.inv_area));
       }
       e0 += T.A[0]; e1 += T.A[1]; e2 += T.A[2];
     }
     r0 += T.B[0]; r1 += T.B[1]; r2 += T.B[2];
+  }
+}
+
+// Warp-cooperative variant of the 32-bit path for triangles with many candidate pixels: the 32
+// lanes tile the candidate rectangle in blocks of (lw x 32/lw) pixels, lw in {4, 8, 16, 32}.
+__device__ __forceinline__ void tri_raster_warp(const TriSetup& T, int lane, unsigned* __restrict__ z,
+                                                int zx0, int zy0, int zstride) {
+  const int bw = T.bx1 - T.bx0 + 1;
+  const int lw_log = bw > 16 ? 5 : (bw > 8 ? 4 : (bw > 4 ? 3 : 2));
+  const int lx = lane & ((1 << lw_log) - 1), ly = lane >> lw_log;
+  const int sx = 1 << lw_log, sy = 32 >> lw_log;
+  for (int y = T.by0 + ly; y <= T.by1; y += sy) {
+    const int dy = y - T.by0;
+    for (int x = T.bx0 + lx; x <= T.bx1; x += sx) {
+      const int dx = x - T.bx0;
+      const int e0 = T.C[0] + T.A[0] * dx + T.B[0] * dy;
+      const int e1 = T.C[1] + T.A[1] * dx + T.B[1] * dy;
+      const int e2 = T.C[2] + T.A[2] * dx + T.B[2] * dy;
+      if ((e0 | e1 | e2) >= 0) {
+        const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]),
+                    w2 = (float)(e2 + T.bias[2]);
+        z_merge(z + (y - zy0) * zstride + (x - zx0), tri_depth(w0, w1, w2, T.iz, T.inv_area));
+      }
+    }
   }
 }
 
@@ -181,8 +217,7 @@ __device__ __forceinline__ void tri_raster_large(const TriSetup64& T, int lane, 
     if ((e0 | e1 | e2) >= 0) {
       // Same expression as the 32-bit path, so a pixel's depth does not depend on which path drew it.
       const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]), w2 = (float)(e2 + T.bias[2]);
-      const float izp = __fmaf_rn(w0, T.iz[0], __fmaf_rn(w1, T.iz[1], __fmul_rn(w2, T.iz[2]))) * T.inv_area;
-      z_merge(z + (T.by0 + yy - zy0) * zstride + (T.bx0 + xx - zx0), __frcp_rn(izp));
+      z_merge(z + (T.by0 + yy - zy0) * zstride + (T.bx0 + xx - zx0), tri_depth(w0, w1, w2, T.iz, T.inv_area));
     }
   }
 }

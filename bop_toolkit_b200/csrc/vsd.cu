@@ -25,7 +25,7 @@ constexpr int kMaxWidth = 4096;
 
 struct Tuning {
   int tile_px = 24576;   // z-tile capacity per pose, pixels (2 poses x 4 B = 192 KB of smem)
-  int threads = 512;
+  int threads = 1024;
   int ctas_per_sm = 1;
   int small_tri_px = 36; // triangles with more candidate pixels go to the warp-cooperative path
 };
@@ -353,8 +353,11 @@ struct FusedArgs {
   PixParams pp;
 };
 
-template <int MODE>
-__global__ void __launch_bounds__(512, 1) fused_kernel(const __grid_constant__ FusedArgs a) {
+// VARIANT 0: <= 512 threads, 1 CTA/SM (up to 128 registers); VARIANT 1: up to 1024 resident
+// threads per SM (64 registers): 1024-thread CTAs or two 512-thread CTAs per SM.
+template <int MODE, int VARIANT>
+__global__ void __launch_bounds__(VARIANT == 0 ? 512 : 1024, 1)
+fused_kernel(const __grid_constant__ FusedArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned* const zt = (unsigned*)smem_raw;                       // [2][tile_px]
   double* const xh = (double*)(smem_raw + (size_t)2 * a.tile_px * 4);  // [wpad]
@@ -412,52 +415,64 @@ __global__ void __launch_bounds__(512, 1) fused_kernel(const __grid_constant__ F
     const int4* __restrict__ faces = (const int4*)M.faces4;
     const int F = M.n_faces;
 
-    for (int p = 0; p < n_poses; ++p) {
+    // One loop over the triangles of BOTH poses (they draw into different z-tiles, so no barrier
+    // is needed between them).  Triangles with many candidate pixels are deferred to a queue and
+    // drawn warp-cooperatively afterwards.
+    const PVert* __restrict__ pv_base = a.pv + (size_t)sW.pair * n_poses * a.pv_stride;
+    const int nF = F * n_poses;
+    for (int g = tid; g < nF; g += nthr) {
+      const int p = g >= F ? 1 : 0;
+      const int f = g - p * F;
+      const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
+      const int4 fi = __ldg(faces + f);
+      const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
+                 r2 = __ldg((const int4*)(pv + fi.z));
+      const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
+      const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
+      const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
+      TriSetup T;
+      const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+      if (n == 0) continue;
       unsigned* const z = zt + (size_t)p * a.tile_px;
-      const PVert* __restrict__ pv = a.pv + ((size_t)sW.pair * n_poses + p) * a.pv_stride;
-      for (int f = tid; f < F; f += nthr) {
-        const int4 fi = __ldg(faces + f);
+      if (n > 0 && n <= a.small_tri_px) {
+        tri_raster_small(T, z, cx0, cy0, w);
+      } else {
+        const int slot = atomicAdd(&s_q, 1);
+        if (slot < kQueueCap) {
+          queue[slot] = g;
+        } else if (n > 0) {   // queue full: draw it here (slow but correct)
+          tri_raster_small(T, z, cx0, cy0, w);
+        } else {
+          TriSetup64 T64;
+          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+        }
+      }
+    }
+    __syncthreads();
+    {
+      const int nq = min(s_q, kQueueCap);
+      for (int qi = warp; qi < nq; qi += nwarps) {
+        const int g = queue[qi];
+        const int p = g >= F ? 1 : 0;
+        const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
+        const int4 fi = __ldg(faces + (g - p * F));
         const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
                    r2 = __ldg((const int4*)(pv + fi.z));
         const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
         const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
         const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
+        unsigned* const z = zt + (size_t)p * a.tile_px;
         TriSetup T;
         const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
-        if (n == 0) continue;
-        if (n > 0 && n <= a.small_tri_px) {
-          tri_raster_small(T, z, cx0, cy0, w);
-        } else {
-          const int slot = atomicAdd(&s_q, 1);
-          if (slot < kQueueCap) {
-            queue[slot] = f;
-          } else {   // queue full: draw it here (slow but correct)
-            TriSetup64 T64;
-            if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
-          }
-        }
-      }
-      __syncthreads();
-      const int nq = min(s_q, kQueueCap);
-      if (nq > 0) {
-        // Warp-cooperative path for large triangles: lanes stride over the candidate rectangle.
-        for (int qi = warp; qi < nq; qi += nwarps) {
-          const int4 fi = __ldg(faces + queue[qi]);
-          const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
-                     r2 = __ldg((const int4*)(pv + fi.z));
-          const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
-          const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
-          const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
-          TriSetup T;
+        if (n > 0) {
+          tri_raster_warp(T, lane, z, cx0, cy0, w);
+        } else if (n < 0) {
           TriSetup64 T64;
-          if (tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T) != 0 && tri_setup64(v0, v1, v2, T, T64))
-            tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
+          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
         }
       }
-      __syncthreads();
-      if (tid == 0) s_q = 0;
-      __syncthreads();
     }
+    __syncthreads();
 
     if (MODE == MODE_RENDER) {
       float* out = a.depth_out + (size_t)sD.im * a.pp.H * a.pp.W;
@@ -739,11 +754,18 @@ template <int MODE>
 int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
   const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
-  BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = sm_count() * g_tune.ctas_per_sm;
   const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : BOP_PROF_VSD_FUSED;
+  const bool dense = g_tune.threads * g_tune.ctas_per_sm > 512;
+  if (dense)
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  else
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   bop_prof_begin(slot, s);
-  fused_kernel<MODE><<<grid, g_tune.threads, smem, s>>>(a);
+  if (dense)
+    fused_kernel<MODE, 1><<<grid, g_tune.threads, smem, s>>>(a);
+  else
+    fused_kernel<MODE, 0><<<grid, g_tune.threads, smem, s>>>(a);
   bop_prof_end(slot, s);
   BOP_LAUNCH_CHECK();
   return 0;
@@ -781,7 +803,7 @@ extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int
     g_tune.tile_px = tile_px;
   }
   if (threads) {
-    BOP_REQUIRE(threads >= 64 && threads <= 512 && threads % 32 == 0, "tuning: threads out of range");
+    BOP_REQUIRE(threads >= 64 && threads <= 1024 && threads % 32 == 0, "tuning: threads out of range");
     g_tune.threads = threads;
   }
   if (ctas_per_sm) {
