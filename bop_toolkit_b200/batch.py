@@ -264,7 +264,19 @@ def make_vsd_params(height, width, delta, taus, normalized_by_diameter=True, cos
   return p
 
 
-def _depth_input(depth_test, device):
+def _depth_input(depth_test, device, zero_copy=False):
+  """-> (tensor whose data_ptr() the kernel reads, dtype code).  zero_copy: a PINNED host tensor
+  is handed to the kernel as is (unified addressing) and read across PCIe on demand."""
+  if zero_copy and isinstance(depth_test, torch.Tensor) and not depth_test.is_cuda:
+    if not depth_test.is_pinned() or not depth_test.is_contiguous():
+      raise ValueError('zero-copy depth needs a contiguous pinned host tensor')
+    if depth_test.dtype in (torch.uint16, torch.int16):
+      dd, code = depth_test.view(torch.int16), _lib.DEPTH_U16
+    elif depth_test.dtype == torch.float32:
+      dd, code = depth_test, _lib.DEPTH_F32
+    else:
+      raise ValueError('zero-copy depth must be float32 or uint16')
+    return (dd.unsqueeze(0) if dd.dim() == 2 else dd), code
   if isinstance(depth_test, np.ndarray):
     depth_test = torch.from_numpy(np.ascontiguousarray(depth_test))
   if depth_test.dtype == torch.uint16 or depth_test.dtype == torch.int16:
@@ -285,7 +297,7 @@ def _tau_chunks(taus):
 
 def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus,
               normalized_by_diameter=True, cost_type='step', visib_mode='bop19', gate=False,
-              depth_scale=None, return_counts=False, diameter_override=None):
+              depth_scale=None, return_counts=False, diameter_override=None, zero_copy=False):
   """pose_error.vsd for P pairs with the fused raster + pixel-pass kernel.
 
   depth_test: [n_im,H,W] float32 mm (or uint16 raw + depth_scale[n_im]); im_idx: [P] image of
@@ -295,7 +307,7 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
   pe, pg, n = _poses(models, pose_est, pose_gt)
   dev = models.device
   oi = _obj_idx(models, obj, n)
-  dd, code = _depth_input(depth_test, dev)
+  dd, code = _depth_input(depth_test, dev, zero_copy)
   n_im, H, W = dd.shape
   Kd = to_device(K, torch.float64, dev).reshape(-1, 9)
   if Kd.shape[0] != n_im:
@@ -418,6 +430,14 @@ def render_batch(models, obj, poses, cams, height, width):
                                          ws.data_ptr(), wsb, _stream_ptr())
   _lib.check(rc)
   return out
+
+
+def depth_bytes_fetched(device, depth_dtype_code):
+  """Bytes of depth_test the last vsd_batch pass on `device` fetched (synchronises)."""
+  ws = _workspaces[(device.type, device.index)].buf
+  out = ctypes.c_uint64(0)
+  _lib.check(_lib.lib().bop_vsd_depth_bytes_fetched(ws.data_ptr(), depth_dtype_code, ctypes.byref(out)))
+  return int(out.value)
 
 
 def kernel_launch_count():

@@ -47,6 +47,7 @@ struct WorkItem {
 struct PlanCounters {
   unsigned total;  // number of work items
   unsigned next;   // persistent-CTA ticket
+  unsigned long long depth_groups;  // 4-pixel groups of depth_test actually fetched (statistics)
 };
 
 // overlapping_sphere_projections (bop_toolkit_lib/misc.py:309-331), float64.
@@ -367,6 +368,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
   __shared__ WorkItem sW;
   __shared__ unsigned s_ticket;
   __shared__ int s_q;
+  __shared__ int s_next;
   __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS];
   __shared__ double s_sum[BOP_MAX_TAUS];
 
@@ -381,6 +383,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       s_ticket = t;
       if (t < total) sW = a.work[t];
       s_q = 0;
+      s_next = 0;
     }
     if (tid < 2 + BOP_MAX_TAUS) s_cnt[tid] = 0ull;
     if (tid < BOP_MAX_TAUS) s_sum[tid] = 0.0;
@@ -420,31 +423,41 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     // drawn warp-cooperatively afterwards.
     const PVert* __restrict__ pv_base = a.pv + (size_t)sW.pair * n_poses * a.pv_stride;
     const int nF = F * n_poses;
-    for (int g = tid; g < nF; g += nthr) {
-      const int p = g >= F ? 1 : 0;
-      const int f = g - p * F;
-      const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
-      const int4 fi = __ldg(faces + f);
-      const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
-                 r2 = __ldg((const int4*)(pv + fi.z));
-      const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
-      const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
-      const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
-      TriSetup T;
-      const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
-      if (n == 0) continue;
-      unsigned* const z = zt + (size_t)p * a.tile_px;
-      if (n > 0 && n <= a.small_tri_px) {
-        tri_raster_small(T, z, cx0, cy0, w);
-      } else {
-        const int slot = atomicAdd(&s_q, 1);
-        if (slot < kQueueCap) {
-          queue[slot] = g;
-        } else if (n > 0) {   // queue full: draw it here (slow but correct)
-          tri_raster_small(T, z, cx0, cy0, w);
-        } else {
-          TriSetup64 T64;
-          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+    // Warps claim 32 consecutive triangles at a time from a shared ticket: triangle cost varies
+    // (0 .. small_tri_px candidate pixels), static striding leaves warps idle at the barrier.
+    for (;;) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&s_next, 32);
+      base = __shfl_sync(BOP_FULL_MASK, base, 0);
+      if (base >= nF) break;
+      const int g = base + lane;
+      if (g < nF) {
+        const int p = g >= F ? 1 : 0;
+        const int f = g - p * F;
+        const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
+        const int4 fi = __ldg(faces + f);
+        const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
+                   r2 = __ldg((const int4*)(pv + fi.z));
+        const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
+        const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
+        const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
+        TriSetup T;
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+        if (n != 0) {
+          unsigned* const z = zt + (size_t)p * a.tile_px;
+          if (n > 0 && n <= a.small_tri_px) {
+            tri_raster_small(T, z, cx0, cy0, w);
+          } else {
+            const int slot = atomicAdd(&s_q, 1);
+            if (slot < kQueueCap) {
+              queue[slot] = g;
+            } else if (n > 0) {   // queue full: draw it here (slow but correct)
+              tri_raster_small(T, z, cx0, cy0, w);
+            } else {
+              TriSetup64 T64;
+              if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+            }
+          }
         }
       }
     }
@@ -488,6 +501,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
 
     // ---- pixel pass ------------------------------------------------------------------
     Acc<MODE> acc;
+    int n_loaded = 0;
     const int w4 = w >> 2;
     const int ngroups = nrows * w4;
     const double diameter = sD.diameter;
@@ -505,6 +519,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int row = cy0 + r, col = cx0 + 4 * c4;
       float dt[4];
       load_depth4(a.pp, a.depth_test, scale, sD.im, row, col, dt);
+      ++n_loaded;
       const double Y = __ddiv_rn(__dsub_rn((double)row, sD.kcy), sD.kfy);   // misc.py:138
       const unsigned zev[4] = {ze.x, ze.y, ze.z, ze.w};
       const unsigned zgv[4] = {zg.x, zg.y, zg.z, zg.w};
@@ -517,10 +532,11 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
     // ---- reduce: warp shuffle -> shared atomics -> one global atomic per counter ---------
     {
-      const int u = warp_sum(acc.uni), in = warp_sum(acc.inter);
+      const int u = warp_sum(acc.uni), in = warp_sum(acc.inter), nl = warp_sum(n_loaded);
       if (lane == 0) {
         if (u) atomicAdd(&s_cnt[0], (unsigned long long)u);
         if (in) atomicAdd(&s_cnt[1], (unsigned long long)in);
+        if (nl) atomicAdd(&a.ctr->depth_groups, (unsigned long long)nl);
       }
 #pragma unroll
       for (int k = 0; k < BOP_MAX_TAUS; ++k) {
@@ -814,6 +830,16 @@ extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int
     BOP_REQUIRE(small_tri_px >= 1, "tuning: small_tri_px out of range");
     g_tune.small_tri_px = small_tri_px;
   }
+  return 0;
+}
+
+// Bytes of depth_test the fused kernel fetched in the most recent pass that used `workspace`
+// (synchronises the device).  With host-mapped (pinned) depth images this is the PCIe traffic.
+extern "C" int bop_vsd_depth_bytes_fetched(const void* workspace, int depth_dtype, uint64_t* bytes) {
+  BOP_REQUIRE(workspace && bytes, "bop_vsd_depth_bytes_fetched: null pointer");
+  PlanCounters c;
+  BOP_CUDA(cudaMemcpy(&c, workspace, sizeof(c), cudaMemcpyDeviceToHost));
+  *bytes = c.depth_groups * (depth_dtype == BOP_DEPTH_U16 ? 8ull : 16ull);
   return 0;
 }
 

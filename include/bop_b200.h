@@ -182,6 +182,13 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
 
+/* depth_test may also be a pointer into PINNED HOST memory (cudaHostAlloc / cudaHostRegister;
+ * with unified addressing the host pointer is valid on the device): the fused kernel then pulls
+ * only the depth samples it needs (the pixels under the two rendered silhouettes) across PCIe
+ * instead of the caller copying whole images.  bop_vsd_depth_bytes_fetched reports how many
+ * bytes of depth_test the most recent pass on `workspace` fetched (synchronises the device). */
+int bop_vsd_depth_bytes_fetched(const void* workspace, int depth_dtype, uint64_t* bytes);
+
 /* ---- host-buffer convenience layer -----------------------------------------
  * Upload a model (host arrays, float64 pts as pose_error.* receives them) and get a
  * filled descriptor whose pointers are device memory owned by the library until

@@ -457,3 +457,31 @@ def test_dense_model_adi_add(B):
          [po.mssd(R_e[i], col(t_e[i]), R_g[i], col(t_g[i]), pts, syms) for i in range(n)])
   _close(B.mspd_batch(ms, 0, pe, pg, synth.LM_K).cpu().numpy(),
          [po.mspd(R_e[i], col(t_e[i]), R_g[i], col(t_g[i]), synth.LM_K, pts, syms) for i in range(n)])
+
+
+def test_vsd_zero_copy_pinned_depth(B):
+  """depth_test read straight from pinned host memory (kernel pulls ROI pixels over PCIe):
+  identical results to the device-resident copy, far fewer bytes moved."""
+  import torch
+  from bop_toolkit_b200 import _lib
+  n = 6
+  K, pts, faces, R_e, t_e, R_g, t_g, depth, _ = _vsd_case(B, n, seed=60)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  taus = list(np.arange(0.05, 0.51, 0.05))
+  Ks = np.tile(K.reshape(1, 9), (n, 1))
+  pe, pg = _poses(B, R_e, t_e), _poses(B, R_g, t_g)
+  im = np.arange(n, dtype=np.int32)
+  d16 = torch.from_numpy(np.round(depth / 0.1).astype(np.uint16).view(np.int16)).pin_memory()
+  sc = np.full(n, 0.1, np.float32)
+  a = B.vsd_batch(ms, 0, pe, pg, d16, im, Ks, 15, taus, True, 'step', depth_scale=sc, zero_copy=True)
+  fetched = B.depth_bytes_fetched(ms.device, _lib.DEPTH_U16)
+  b = B.vsd_batch(ms, 0, pe, pg, d16, im, Ks, 15, taus, True, 'step', depth_scale=sc)
+  assert torch.equal(a, b)
+  assert 0 < fetched < 0.5 * d16.numel() * 2
+  f32 = torch.from_numpy(depth).pin_memory()
+  c = B.vsd_batch(ms, 0, pe, pg, f32, im, Ks, 15, taus, True, 'step', zero_copy=True)
+  d = B.vsd_batch(ms, 0, pe, pg, depth, im, Ks, 15, taus, True, 'step')
+  assert torch.equal(c, d)
+  with pytest.raises(ValueError):
+    B.vsd_batch(ms, 0, pe, pg, torch.from_numpy(depth), im, Ks, 15, taus, zero_copy=True)
