@@ -24,10 +24,10 @@ constexpr int kMinTilePx = 4096;
 constexpr int kMaxWidth = 4096;
 
 struct Tuning {
-  int tile_px = 24576;   // z-tile capacity per pose, pixels (2 poses x 4 B = 192 KB of smem)
+  int tile_px = 18432;   // z-tile capacity per pose, pixels (2 poses x 4 B = 144 KB of smem; leaves L1 for gathers)
   int threads = 1024;
   int ctas_per_sm = 1;
-  int small_tri_px = 36; // triangles with more candidate pixels go to the warp-cooperative path
+  int small_tri_px = 256; // triangles with more candidate pixels go to the warp-cooperative path
 };
 Tuning g_tune;
 

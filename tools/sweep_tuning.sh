@@ -1,4 +1,4 @@
-for t in "24576,512,1,36" "24576,1024,1,36" "12288,512,2,36" "24576,512,1,16" "24576,512,1,64" "16384,768,1,36" "12288,1024,1,36" "8192,512,2,36"; do
+for t in "20480,1024,1,160" "16384,1024,1,160" "20480,1024,1,256" "16384,1024,1,256" "12288,1024,1,256" "20480,1024,1,1000" "18432,1024,1,400"; do
   echo "TUNE $t"; BOP_TUNE=$t python bench.py --pairs 4000 --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
