@@ -104,15 +104,20 @@ def save_bop_results(path, results, version='bop19'):
 
 
 # ---------------------------------------------------------------------------- depth
-def load_depth_u16(path):
-  """16-bit depth PNG -> HxW uint16 (raw samples; the kernels apply depth_scale in float32)."""
+def load_depth_raw(path):
+  """Depth image file -> HxW array in the file's own sample type (uint16 for BOP PNGs)."""
   import cv2
   d = cv2.imread(path, cv2.IMREAD_UNCHANGED)
   if d is None:
     raise IOError('cannot read depth image: ' + path)
   if d.ndim == 3:
     d = d[:, :, 0]
-  return np.ascontiguousarray(d.astype(np.uint16))
+  return np.ascontiguousarray(d)
+
+
+def load_depth_u16(path):
+  """16-bit depth PNG -> HxW uint16 (raw samples; the kernels apply depth_scale in float32)."""
+  return np.ascontiguousarray(load_depth_raw(path).astype(np.uint16))
 
 
 def load_depth(path):

@@ -141,3 +141,100 @@ def discrete_z_symmetries(n):
     c, s = math.cos(a), math.sin(a)
     out.append([c, -s, 0, 0, s, c, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1])
   return out
+
+
+def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2, 3), n_images=3,
+                      obj_ids=(1, 5, 6, 8), objs_per_image=3, ests_per_target=3, seed=0,
+                      mesh_res=(12, 24), K=LM_K, width=IM_W, height=IM_H, method='synth',
+                      depth_scales=(0.1, 1.0)):
+  """Writes a small synthetic dataset in BOP layout under `root` (docs/bop_datasets_format.md):
+    <root>/datasets/<dataset>/models_eval/{obj_XXXXXX.ply, models_info.json}
+    <root>/datasets/<dataset>/<split>/<scene:06d>/{scene_camera.json, scene_gt.json, depth/*.png}
+    <root>/datasets/<dataset>/test_targets_bop19.json
+    <root>/results/<method>_<dataset>-<split>.csv
+  render_fn(pts, faces, R, t, K) -> HxW float32 depth [mm] (the caller chooses the renderer).
+  Exercises: several GT instances of one object in an image, targets without estimates,
+  estimates for non-target objects, tied scores, gross outliers, depth_scale != 1.
+  Returns a dict with the paths and the result file name."""
+  import json
+  import os
+  import cv2
+  from . import inout
+  rng = np.random.default_rng(seed)
+  ds = os.path.join(root, 'datasets', dataset)
+  os.makedirs(os.path.join(ds, 'models_eval'), exist_ok=True)
+  os.makedirs(os.path.join(root, 'results'), exist_ok=True)
+  models, info = {}, {}
+  for k, oid in enumerate(obj_ids):
+    diameter = 90.0 + 40.0 * k
+    pts, faces = make_mesh(mesh_res[0], mesh_res[1], diameter, seed=seed * 100 + oid)
+    models[oid] = (pts, faces)
+    inout.save_ply(os.path.join(ds, 'models_eval', 'obj_%06d.ply' % oid), pts, faces)
+    mi = {'diameter': diameter, 'min_x': float(pts[:, 0].min()), 'min_y': float(pts[:, 1].min()),
+          'min_z': float(pts[:, 2].min()), 'size_x': float(np.ptp(pts[:, 0])),
+          'size_y': float(np.ptp(pts[:, 1])), 'size_z': float(np.ptp(pts[:, 2]))}
+    if k % 4 == 1:
+      mi['symmetries_discrete'] = discrete_z_symmetries(4)
+    if k % 4 == 3:
+      mi['symmetries_continuous'] = [{'axis': [0, 0, 1], 'offset': [0, 0, 0]}]
+    info[str(oid)] = mi
+  with open(os.path.join(ds, 'models_eval', 'models_info.json'), 'w') as f:
+    json.dump(info, f)
+  targets, lines = [], ['scene_id,im_id,obj_id,score,R,t,time']
+  fmt = lambda a: ' '.join(repr(float(x)) for x in np.asarray(a).reshape(-1))
+  for si, scene_id in enumerate(scene_ids):
+    sdir = os.path.join(ds, split, '%06d' % scene_id)
+    os.makedirs(os.path.join(sdir, 'depth'), exist_ok=True)
+    scale = float(depth_scales[si % len(depth_scales)])
+    cam, gt = {}, {}
+    for im_id in range(n_images):
+      Kim = K.copy()
+      Kim[0, 2] += float(rng.uniform(-3, 3))     # per-image intrinsics differ slightly
+      cam[str(im_id)] = {'cam_K': [float(x) for x in Kim.reshape(-1)], 'depth_scale': scale}
+      chosen = list(rng.choice(obj_ids, size=min(objs_per_image, len(obj_ids)), replace=False))
+      chosen.append(chosen[0])                    # a second instance of the first object
+      _, _, R_g, t_g = make_pose_pairs(len(chosen), seed=int(rng.integers(1 << 30)), K=Kim,
+                                       width=width, height=height, z_range=(500.0, 1100.0))
+      gts, comp = [], np.zeros((height, width), np.float32)
+      for j, oid in enumerate(chosen):
+        gts.append({'cam_R_m2c': [float(x) for x in R_g[j].reshape(-1)],
+                    'cam_t_m2c': [float(x) for x in t_g[j]], 'obj_id': int(oid)})
+        d = render_fn(models[oid][0], models[oid][1], R_g[j], t_g[j], Kim)
+        comp = np.where((d > 0) & ((comp == 0) | (d < comp)), d, comp)
+      gt[str(im_id)] = gts
+      depth = degrade_depth(comp, seed=int(rng.integers(1 << 30)), K=Kim)
+      cv2.imwrite(os.path.join(sdir, 'depth', '%06d.png' % im_id),
+                  np.clip(np.round(depth / scale), 0, 65535).astype(np.uint16))
+      present = sorted(set(int(o) for o in chosen))
+      for oid in present:
+        targets.append({'im_id': im_id, 'inst_count': chosen.count(oid), 'obj_id': oid,
+                        'scene_id': int(scene_id)})
+      absent = [o for o in obj_ids if o not in present]
+      if absent and im_id == 0:                   # a target without any GT instance
+        targets.append({'im_id': im_id, 'inst_count': 1, 'obj_id': int(absent[0]),
+                        'scene_id': int(scene_id)})
+      for j, oid in enumerate(chosen):
+        if im_id == 1 and j == 1:
+          continue                                # a target without estimates
+        for e in range(ests_per_target):
+          ang = math.radians(rng.uniform(0.0, 12.0))
+          R_e = R_g[j] @ axis_angle(rng.normal(size=3), ang)
+          t_e = t_g[j] + rng.normal(size=3) * np.array([4.0, 4.0, 12.0])
+          if e == 2 and j == 0:                   # gross outlier (fails the sphere gates)
+            t_e = t_g[j] + np.array([300.0, -200.0, 400.0])
+          score = 0.5 if e < 2 and j == 2 else float(np.round(rng.uniform(), 3))   # tied scores
+          lines.append('%d,%d,%d,%r,%s,%s,%r' % (scene_id, im_id, oid, score, fmt(R_e), fmt(t_e), 0.25))
+      lines.append('%d,%d,%d,%r,%s,%s,%r' % (scene_id, im_id, 99, 0.9, fmt(np.eye(3)),
+                                             fmt([0, 0, 800.0]), 0.25))   # non-target object
+    with open(os.path.join(sdir, 'scene_camera.json'), 'w') as f:
+      json.dump(cam, f)
+    with open(os.path.join(sdir, 'scene_gt.json'), 'w') as f:
+      json.dump(gt, f)
+  with open(os.path.join(ds, 'test_targets_bop19.json'), 'w') as f:
+    json.dump(targets, f)
+  result_filename = '%s_%s-%s.csv' % (method, dataset, split)
+  with open(os.path.join(root, 'results', result_filename), 'w') as f:
+    f.write('\n'.join(lines))
+  return {'datasets_path': os.path.join(root, 'datasets'), 'results_path': os.path.join(root, 'results'),
+          'eval_path': os.path.join(root, 'eval'), 'result_filename': result_filename,
+          'obj_ids': list(obj_ids), 'scene_ids': list(scene_ids)}

@@ -1,0 +1,161 @@
+"""Driver (eval_calc_errors drop-in) against the error files written by the REAL reference
+script on the same synthetic BOP-layout dataset (tests/golden/driver_golden.json, produced by
+tests/golden/make_golden_driver.py).
+
+CPU part: the dataset regenerates byte-identically; the flattened record skeleton (order,
+im_id / obj_id / est_id / score, GT ids) equals the reference's for every n_top mode.
+GPU part: the files our driver writes carry the same records with errors within tolerance
+(1e-5 relative for the point errors, 1e-3 absolute per tau for VSD, bars of BASELINE.json).
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _oracle_render_fn(pts, faces, R, t, K):
+  from oracle import renderer_oracle
+  from bop_toolkit_b200 import synth
+  return renderer_oracle.render_depth(pts, faces, R, t, K[0, 0], K[1, 1], K[0, 2], K[1, 2],
+                                      synth.IM_H, synth.IM_W)
+
+
+def _checksum(info):
+  import cv2
+  h = hashlib.sha256()
+  base = os.path.join(info['datasets_path'], 'lmo')
+  for scene_id in info['scene_ids']:
+    ddir = os.path.join(base, 'test', '%06d' % scene_id, 'depth')
+    for name in sorted(os.listdir(ddir)):
+      h.update(cv2.imread(os.path.join(ddir, name), cv2.IMREAD_UNCHANGED).tobytes())
+  for path in (os.path.join(info['results_path'], info['result_filename']),
+               os.path.join(base, 'test_targets_bop19.json')):
+    h.update(open(path, 'rb').read())
+  return h.hexdigest()
+
+
+@pytest.fixture(scope='module')
+def driver_golden():
+  return json.load(open(os.path.join(ROOT, 'tests', 'golden', 'driver_golden.json')))
+
+
+@pytest.fixture(scope='module')
+def dataset(tmp_path_factory, driver_golden, oracle_built):
+  from bop_toolkit_b200 import synth
+  root = str(tmp_path_factory.mktemp('bop_ds'))
+  kw = dict(driver_golden['dataset_kw'])
+  kw['scene_ids'], kw['obj_ids'] = tuple(kw['scene_ids']), tuple(kw['obj_ids'])
+  info = synth.write_bop_dataset(root, _oracle_render_fn, **kw)
+  assert _checksum(info) == driver_golden['dataset_sha256'], \
+    'the synthetic dataset did not regenerate byte-identically; goldens do not apply'
+  return info
+
+
+def _params(info, error_type, n_top, eval_path):
+  from bop_toolkit_b200 import eval_calc_errors as ece
+  return ece.parse_args([
+    '--error_type=' + error_type, '--n_top=%d' % n_top,
+    '--result_filenames=' + info['result_filename'], '--results_path=' + info['results_path'],
+    '--eval_path=' + eval_path, '--datasets_path=' + info['datasets_path']])
+
+
+def _golden_files(driver_golden, error_type, n_top):
+  pre = '%s|%d|' % (error_type, n_top)
+  return {k[len(pre):]: v for k, v in driver_golden['files'].items() if k.startswith(pre)}
+
+
+def _load_text(text):
+  return json.loads(text, parse_constant=lambda c: {'Infinity': float('inf'), '-Infinity': -float('inf'),
+                                                     'NaN': float('nan')}[c])
+
+
+def test_parse_args_quirks():
+  from bop_toolkit_b200 import eval_calc_errors as ece
+  p = ece.parse_args(['--skip_missing=False', '--vsd_normalized_by_diameter=', '--n_top=-1',
+                      '--vsd_deltas=lmo:7.5,xx:3', '--vsd_taus=0.1,0.3'])
+  assert p['skip_missing'] is True            # bool('False') -- eval_calc_errors.py:120
+  assert p['vsd_normalized_by_diameter'] is False
+  assert p['n_top'] == -1 and p['vsd_deltas'] == {'lmo': 7.5, 'xx': 3.0} and p['vsd_taus'] == [0.1, 0.3]
+  d = ece.default_params()
+  assert d['vsd_taus'][2] == 0.15000000000000002 and len(d['vsd_taus']) == 10
+  assert ece.parse_result_filename('a/b/meth-x_lmo-test-pbr.csv') == ('meth-x_lmo-test-pbr', 'meth-x', 'lmo', 'test', 'pbr')
+
+
+@pytest.mark.parametrize('n_top', [1, -1, 0])
+def test_flatten_matches_reference_records(dataset, driver_golden, n_top):
+  """Host logic only: record order, est_id, scores and GT ids equal the reference's."""
+  from bop_toolkit_b200 import dataset_params, eval_calc_errors as ece, inout
+  et = {1: 'mssd', -1: 'mspd', 0: 'mssd'}[n_top]
+  gold = _golden_files(driver_golden, et, n_top)
+  assert gold
+  p = _params(dataset, et, n_top, '/nonexistent')
+  dp = dataset_params.get_split_params(p['datasets_path'], 'lmo', 'test')
+  targets = inout.load_json(os.path.join(dp['base_path'], p['targets_filename']))
+  torg, eorg = {}, {}
+  for t in targets:
+    torg.setdefault(t['scene_id'], {}).setdefault(t['im_id'], {})[t['obj_id']] = t
+  for e in inout.load_bop_results(os.path.join(p['results_path'], p['result_filenames'][0])):
+    eorg.setdefault(e['scene_id'], {}).setdefault(e['im_id'], {}).setdefault(e['obj_id'], []).append(e)
+  for scene_id, st in torg.items():
+    gt = inout.load_scene_gt(dp['scene_gt_tpath'].format(scene_id=scene_id))
+    sp = ece.flatten_scene(p, scene_id, st, eorg.get(scene_id, {}), gt)
+    ref = _load_text(gold['synth_lmo-test/error=%s_ntop=%d/errors_%06d.json' % (et, n_top, scene_id)])
+    assert len(ref) == len(sp.records)
+    for a, b in zip(sp.records, ref):
+      assert (a['im_id'], a['obj_id'], a['est_id'], a['score']) == (b['im_id'], b['obj_id'], b['est_id'], b['score'])
+      assert [str(g) for g in a['errors']] == list(b['errors'])
+    assert len(sp.rec) == sum(len(r['errors']) for r in ref)
+
+
+def test_writer_layout_roundtrip(driver_golden):
+  """inout.save_json reproduces the reference's text byte for byte from parsed records."""
+  from bop_toolkit_b200 import inout
+  n = 0
+  for key, text in driver_golden['files'].items():
+    recs = _load_text(text)
+    for r in recs:
+      r['errors'] = {int(k): v for k, v in r['errors'].items()}
+    assert inout.dumps_errors_layout(recs) == text, key
+    n += 1
+  assert n >= 60
+
+
+TOL = {'vsd': (0.0, 1e-3), 'adi': (1e-5, 1e-6), 'ad': (1e-5, 1e-6), 're': (1e-5, 1e-6), 'rete': (1e-5, 1e-6)}
+
+
+@pytest.mark.gpu
+def test_driver_files_match_reference(dataset, driver_golden, tmp_path):
+  from bop_toolkit_b200 import eval_calc_errors as ece
+  identical = total = 0
+  for error_type, n_top in driver_golden['runs']:
+    gold = _golden_files(driver_golden, error_type, n_top)
+    eval_path = str(tmp_path / ('eval_%s_%d' % (error_type, n_top)))
+    ece.calc_errors(_params(dataset, error_type, n_top, eval_path), log=lambda s: None)
+    ours = {}
+    for dirpath, _, names in os.walk(eval_path):
+      for name in names:
+        full = os.path.join(dirpath, name)
+        ours[os.path.relpath(full, eval_path)] = open(full).read()
+    assert sorted(ours) == sorted(gold), (error_type, n_top)
+    rtol, atol = TOL.get(error_type, (1e-5, 1e-9))
+    for rel, text in gold.items():
+      total += 1
+      identical += int(ours[rel] == text)
+      a, b = _load_text(ours[rel]), _load_text(text)
+      assert len(a) == len(b)
+      for ra, rb in zip(a, b):
+        assert {k: ra[k] for k in ('im_id', 'obj_id', 'est_id', 'score')} == \
+               {k: rb[k] for k in ('im_id', 'obj_id', 'est_id', 'score')}
+        assert list(ra['errors']) == list(rb['errors'])
+        for g in rb['errors']:
+          ea, eb = np.array(ra['errors'][g], float), np.array(rb['errors'][g], float)
+          assert ea.shape == eb.shape
+          fin = np.isfinite(eb)
+          assert np.array_equal(np.isfinite(ea), fin) and np.array_equal(ea[~fin], eb[~fin])
+          assert np.all(np.abs(ea[fin] - eb[fin]) <= atol + rtol * np.abs(eb[fin])), \
+            (error_type, n_top, rel, ra, rb)
+  print('driver files: %d of %d byte-identical to the reference' % (identical, total))
