@@ -73,6 +73,10 @@ _SIGNATURES = {
                                    ctypes.c_size_t, _P]),
   'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
                        _P]),
+  'bop_mask_overlap_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P,
+                                ctypes.c_size_t, _P]),
+  'bop_mask_stats_workspace_bytes': (ctypes.c_size_t, [_I]),
+  'bop_mask_overlap_from_depth_dev': (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
   'bop_model_upload': (_I, [_P, _I, _P, _I, _P, _I, ctypes.c_double, _P, _P]),
   'bop_model_free': (_I, [_P, _P]),
   'bop_mssd_host': (_I, [_P, _I, _P, _P, _I, _I, _P]),

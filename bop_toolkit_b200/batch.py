@@ -432,6 +432,78 @@ def render_batch(models, obj, poses, cams, height, width):
   return out
 
 
+def _cams(K, n, dev):
+  """K: one 3x3 / [P,9] / [P,3,3] intrinsics -> [P,4] fx, fy, cx, cy float64 on `dev`."""
+  Kd = to_device(K, torch.float64, dev).reshape(-1, 9)
+  if Kd.shape[0] == 1 and n != 1:
+    Kd = Kd.expand(n, 9)
+  if Kd.shape[0] != n:
+    raise ValueError('K must be [P,9] or a single 3x3')
+  return Kd[:, [0, 4, 2, 5]].contiguous()
+
+
+def mask_overlap_batch(models, obj, pose_est, pose_gt, K, height, width, gate=False):
+  """pose_error.cus and pose_error.cou_bb_proj for P pairs (both silhouettes rasterised in
+  shared memory; only statistics leave the SM).  Returns a dict of device tensors:
+  'cus' [P], 'cou_bb' [P] (NaN where a silhouette is empty), 'counts' [P,4] int64 = union,
+  inter, est, gt pixels, 'bbox' [P,8] int32 = (x, y, w, h) of est then gt."""
+  pe, pg, n = _poses(models, pose_est, pose_gt)
+  dev = models.device
+  oi = _obj_idx(models, obj, n)
+  cams = _cams(K, n, dev)
+  out = {'cus': torch.empty(n, dtype=torch.float64, device=dev),
+         'cou_bb': torch.empty(n, dtype=torch.float64, device=dev),
+         'counts': torch.empty((n, 4), dtype=torch.int64, device=dev),
+         'bbox': torch.empty((n, 8), dtype=torch.int32, device=dev)}
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, int(height), int(width), models.max_pts)
+  ws = _workspace(dev, wsb)
+  with torch.cuda.device(dev):
+    rc = _lib.lib().bop_mask_overlap_dev(
+      models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), cams.data_ptr(), n,
+      models.max_pts, int(height), int(width), int(bool(gate)), out['cus'].data_ptr(),
+      out['cou_bb'].data_ptr(), out['counts'].data_ptr(), out['bbox'].data_ptr(), ws.data_ptr(),
+      wsb, _stream_ptr())
+  _lib.check(rc)
+  return out
+
+
+def cus_batch(models, obj, pose_est, pose_gt, K, height, width, gate=False):
+  """pose_error.cus for P pairs -> [P] float64 device tensor."""
+  return mask_overlap_batch(models, obj, pose_est, pose_gt, K, height, width, gate)['cus']
+
+
+def cou_bb_proj_batch(models, obj, pose_est, pose_gt, K, height, width):
+  """pose_error.cou_bb_proj for P pairs -> [P] float64 device tensor (NaN: empty silhouette)."""
+  return mask_overlap_batch(models, obj, pose_est, pose_gt, K, height, width, False)['cou_bb']
+
+
+def mask_overlap_from_depth_batch(depth_est, depth_gt, device=None):
+  """Same statistics as mask_overlap_batch for pre-rendered depth images / binary masks
+  ([P,H,W] or [H,W]; non-zero = inside)."""
+  _lib.require_cuda()
+  dev = _dev(device if device is not None else
+             (depth_est.device if isinstance(depth_est, torch.Tensor) and depth_est.is_cuda else None))
+  de = to_device(depth_est, torch.float32, dev)
+  dg = to_device(depth_gt, torch.float32, dev)
+  if de.shape != dg.shape:
+    raise ValueError('masks must have the same shape')
+  if de.dim() == 2:
+    de, dg = de.unsqueeze(0), dg.unsqueeze(0)
+  n, H, W = de.shape
+  out = {'cus': torch.empty(n, dtype=torch.float64, device=dev),
+         'cou_bb': torch.empty(n, dtype=torch.float64, device=dev),
+         'counts': torch.empty((n, 4), dtype=torch.int64, device=dev),
+         'bbox': torch.empty((n, 8), dtype=torch.int32, device=dev)}
+  wsb = _lib.lib().bop_mask_stats_workspace_bytes(n)
+  ws = _workspace(dev, wsb)
+  with torch.cuda.device(dev):
+    rc = _lib.lib().bop_mask_overlap_from_depth_dev(
+      de.data_ptr(), dg.data_ptr(), n, H, W, out['cus'].data_ptr(), out['cou_bb'].data_ptr(),
+      out['counts'].data_ptr(), out['bbox'].data_ptr(), ws.data_ptr(), wsb, _stream_ptr())
+  _lib.check(rc)
+  return out
+
+
 def depth_bytes_fetched(device, depth_dtype_code):
   """Bytes of depth_test the last vsd_batch pass on `device` fetched (synchronises)."""
   ws = _workspaces[(device.type, device.index)].buf

@@ -226,7 +226,7 @@ struct PixParams {
   int vec_ok;        // rows of depth_test are 16-byte (f32) / 8-byte (u16) aligned
 };
 
-constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2;
+constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2, MODE_MASK = 3;
 
 template <int MODE>
 struct Acc {
@@ -348,6 +348,7 @@ struct FusedArgs {
   unsigned long long* counts;   // VSD step: [n][2+BOP_MAX_TAUS] u64
   double* tl_sums;              // VSD tlinear: [n][BOP_MAX_TAUS] f64
   float* depth_out;             // RENDER: [n][H][W]
+  int* mask_bbox;               // MASK: [n][8] = xmin,ymin,xmax,ymax of the est mask, then of the gt mask
   unsigned max_items;
   int tile_px;
   int small_tri_px;
@@ -408,7 +409,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         uint4* z4 = (uint4*)(zt + (size_t)p * a.tile_px);
         for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = inf4;
       }
-      if (MODE != MODE_RENDER)
+      if (MODE == MODE_STEP || MODE == MODE_TLINEAR)
         for (int c = tid; c < w; c += nthr)
           xh[c] = __ddiv_rn(__dsub_rn((double)(cx0 + c), sD.kcx), sD.kfx);
     }
@@ -499,6 +500,35 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       continue;
     }
 
+    if (MODE == MODE_MASK) {
+      // pose_error.cus / cou_bb_proj (pose_error.py:256-286,300-330): mask = rendered depth > 0;
+      // counts of the est / gt / intersection / union masks and the pixel bbox of each mask.
+      int ne = 0, ng = 0, ni = 0, nu = 0;
+      int bb[8] = {INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MAX, INT_MAX, INT_MIN, INT_MIN};
+      for (int i = tid; i < npx; i += nthr) {
+        const bool e = zt[i] != BOP_INF_BITS_F32, g = zt[a.tile_px + i] != BOP_INF_BITS_F32;
+        if (!(e || g)) continue;
+        const int r = i / w, x = cx0 + (i - r * w), y = cy0 + r;
+        nu += 1; ni += (e && g) ? 1 : 0;
+        if (e) { ne += 1; bb[0] = min(bb[0], x); bb[1] = min(bb[1], y); bb[2] = max(bb[2], x); bb[3] = max(bb[3], y); }
+        if (g) { ng += 1; bb[4] = min(bb[4], x); bb[5] = min(bb[5], y); bb[6] = max(bb[6], x); bb[7] = max(bb[7], y); }
+      }
+      const int cnt[4] = {warp_sum(nu), warp_sum(ni), warp_sum(ne), warp_sum(ng)};
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        bb[k] = (k & 2) ? __reduce_max_sync(BOP_FULL_MASK, bb[k]) : __reduce_min_sync(BOP_FULL_MASK, bb[k]);
+      if (lane == 0) {
+        unsigned long long* c = a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (cnt[k]) atomicAdd(c + k, (unsigned long long)cnt[k]);
+        int* o = a.mask_bbox + (size_t)sW.pair * 8;
+        if (cnt[2]) { atomicMin(o + 0, bb[0]); atomicMin(o + 1, bb[1]); atomicMax(o + 2, bb[2]); atomicMax(o + 3, bb[3]); }
+        if (cnt[3]) { atomicMin(o + 4, bb[4]); atomicMin(o + 5, bb[5]); atomicMax(o + 6, bb[6]); atomicMax(o + 7, bb[7]); }
+      }
+      continue;
+    }
+
     // ---- pixel pass ------------------------------------------------------------------
     Acc<MODE> acc;
     int n_loaded = 0;
@@ -585,6 +615,53 @@ __global__ void vsd_finalize_kernel(const unsigned long long* __restrict__ count
     errors[(size_t)i * n_taus + k] = e;
     if (counts_out) counts_out[(size_t)i * (2 + n_taus) + 2 + k] = (long long)c[2 + k];
   }
+}
+
+// pose_error.cus (pose_error.py:279-285): 1 - inter / union, 1.0 when the union is empty;
+// pose_error.cou_bb_proj (:318-330) with misc.calc_2d_bbox (misc.py:202-218; w = xmax - xmin,
+// h = ymax - ymin) and misc.iou (misc.py:236-263) on integer pixel coordinates.  A pair with an
+// empty mask has no bbox (the reference raises on it): cou_bb is NaN there.
+__global__ void mask_finalize_kernel(const unsigned long long* __restrict__ counts,
+                                     const int* __restrict__ bbox, int n, double* __restrict__ cus,
+                                     double* __restrict__ cou_bb, long long* __restrict__ counts_out,
+                                     int* __restrict__ bbox_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long* c = counts + (size_t)i * (2 + BOP_MAX_TAUS);
+  const unsigned long long uni = c[0], inter = c[1];
+  if (cus) cus[i] = uni > 0 ? 1.0 - (double)inter / (double)uni : 1.0;
+  if (counts_out)
+    for (int k = 0; k < 4; ++k) counts_out[(size_t)i * 4 + k] = (long long)c[k];
+  const int* b = bbox + (size_t)i * 8;
+  if (bbox_out) {
+    for (int p = 0; p < 2; ++p) {
+      const bool has = c[2 + p] > 0;
+      bbox_out[i * 8 + 4 * p + 0] = has ? b[4 * p + 0] : 0;
+      bbox_out[i * 8 + 4 * p + 1] = has ? b[4 * p + 1] : 0;
+      bbox_out[i * 8 + 4 * p + 2] = has ? b[4 * p + 2] - b[4 * p + 0] : -1;
+      bbox_out[i * 8 + 4 * p + 3] = has ? b[4 * p + 3] - b[4 * p + 1] : -1;
+    }
+  }
+  if (cou_bb) {
+    if (c[2] == 0 || c[3] == 0) {
+      cou_bb[i] = __longlong_as_double(0x7ff8000000000000ll);
+    } else {
+      const long long ax0 = b[0], ay0 = b[1], ax1 = b[2], ay1 = b[3];
+      const long long bx0 = b[4], by0 = b[5], bx1 = b[6], by1 = b[7];
+      const long long wi = min(ax1, bx1) - max(ax0, bx0), hi = min(ay1, by1) - max(ay0, by0);
+      double iou = 0.0;
+      if (wi > 0 && hi > 0) {
+        const long long ai = wi * hi, aa = (ax1 - ax0) * (ay1 - ay0), ab = (bx1 - bx0) * (by1 - by0);
+        iou = (double)ai / (double)(aa + ab - ai);
+      }
+      cou_bb[i] = 1.0 - iou;
+    }
+  }
+}
+
+__global__ void fill_i32_pattern_kernel(int* __restrict__ p, int n8) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n8 * 8) p[i] = (i & 2) ? INT_MIN : INT_MAX;
 }
 
 }  // namespace
@@ -699,7 +776,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 constexpr size_t kPvBudgetBytes = (size_t)2 << 30;   // projected-vertex scratch per chunk
 
 struct WsLayout {
-  size_t ctr, counts, tl, bbox, desc, work, pv, total;
+  size_t ctr, counts, tl, bbox, mbox, desc, work, pv, total;
   unsigned max_items;
   int chunk;       // items processed per pass (the batch is split so that pv fits the budget)
   int pv_stride;   // PVert records per (item, pose)
@@ -725,6 +802,7 @@ WsLayout ws_layout(int n, int H, int W, int n_poses, int max_pts) {
   L.counts = off; off = align_up(off + (size_t)c * (2 + BOP_MAX_TAUS) * 8, 256);
   L.tl = off;     off = align_up(off + (size_t)c * BOP_MAX_TAUS * 8, 256);
   L.bbox = off;   off = align_up(off + (size_t)c * 2 * sizeof(int4), 256);
+  L.mbox = off;   off = align_up(off + (size_t)c * 8 * sizeof(int), 256);
   L.desc = off;   off = align_up(off + (size_t)c * sizeof(PairDesc), 256);
   L.work = off;   off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
   L.pv = off;     off = align_up(off + (size_t)c * per_item_pv, 256);
@@ -771,7 +849,7 @@ int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
   const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
   const int grid = sm_count() * g_tune.ctas_per_sm;
-  const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : BOP_PROF_VSD_FUSED;
+  const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : (MODE == MODE_MASK ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
   const bool dense = g_tune.threads * g_tune.ctas_per_sm > 512;
   if (dense)
     BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -982,6 +1060,125 @@ extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth
   vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, tl, n_pairs, pp.n_taus,
                                                             prm->cost_type, errors_out,
                                                             (long long*)counts_out);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+// pose_error.cus (pose_error.py:256-286) and pose_error.cou_bb_proj (:300-330) for a batch of
+// pose pairs: both poses are rasterised into shared-memory z-tiles and only mask statistics
+// leave the SM.  cam: [n][4] fx,fy,cx,cy per pair.
+extern "C" int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                                    const double* pose_est, const double* pose_gt,
+                                    const double* cam, int n_pairs, int max_pts, int height,
+                                    int width, int gate, double* cus_out, double* cou_bb_out,
+                                    int64_t* counts_out, int32_t* bbox_out, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && cam, "bop_mask_overlap_dev: null pointer");
+  BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_mask_overlap_dev: bad image size");
+  BOP_REQUIRE(max_pts >= 1, "bop_mask_overlap_dev: max_pts must be >= 1");
+  const WsLayout L = ws_layout(n_pairs, height, width, 2, max_pts);
+  BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_mask_overlap_dev: workspace too small");
+  BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_mask_overlap_dev: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  for (int c0 = 0; c0 < n_pairs; c0 += L.chunk) {
+    const int nc = n_pairs - c0 < L.chunk ? n_pairs - c0 : L.chunk;
+    if (int rc = launch_plan(models, obj_idx + c0, pose_est + 12 * (size_t)c0, pose_gt + 12 * (size_t)c0,
+                             nullptr, cam + 4 * (size_t)c0, nullptr, 1, nc, 2, height, width, gate, ws, L, s))
+      return rc;
+    fill_i32_pattern_kernel<<<(nc * 8 + 255) / 256, 256, 0, s>>>((int*)(ws + L.mbox), nc);
+    BOP_LAUNCH_CHECK();
+    FusedArgs a;
+    memset(&a, 0, sizeof(a));
+    a.models = models;
+    a.desc = (const PairDesc*)(ws + L.desc);
+    a.work = (const WorkItem*)(ws + L.work);
+    a.ctr = (PlanCounters*)(ws + L.ctr);
+    a.pv = (const PVert*)(ws + L.pv);
+    a.pv_stride = L.pv_stride;
+    a.counts = (unsigned long long*)(ws + L.counts);
+    a.mask_bbox = (int*)(ws + L.mbox);
+    a.max_items = L.max_items;
+    a.tile_px = g_tune.tile_px;
+    a.small_tri_px = g_tune.small_tri_px;
+    a.pp.H = height;
+    a.pp.W = width;
+    a.pp.n_taus = 1;
+    if (int rc = launch_fused<MODE_MASK>(a, width, s)) return rc;
+    mask_finalize_kernel<<<(nc + 127) / 128, 128, 0, s>>>(
+        a.counts, a.mask_bbox, nc, cus_out ? cus_out + c0 : nullptr, cou_bb_out ? cou_bb_out + c0 : nullptr,
+        counts_out ? (long long*)counts_out + (size_t)c0 * 4 : nullptr, bbox_out ? bbox_out + (size_t)c0 * 8 : nullptr);
+    BOP_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+// Mask statistics of pre-rendered depth images / binary masks (non-zero = inside): the part of
+// pose_error.cus / cou_bb_proj after the two render calls, and pose_error.cou_mask
+// (pose_error.py:235-253).  grid = (n_pairs, chunks); 128-bit loads when rows allow it.
+namespace {
+__global__ void __launch_bounds__(256)
+mask_stats_kernel(const float* __restrict__ de, const float* __restrict__ dg, int H, int W,
+                  unsigned long long* __restrict__ counts, int* __restrict__ mbox) {
+  const int pair = blockIdx.x;
+  const size_t base = (size_t)pair * H * W;
+  const int npx = H * W;
+  int ne = 0, ng = 0, ni = 0, nu = 0;
+  int bb[8] = {INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MAX, INT_MAX, INT_MIN, INT_MIN};
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < npx; i += gridDim.y * blockDim.x) {
+    const bool e = __ldg(de + base + i) != 0.f, g = __ldg(dg + base + i) != 0.f;
+    if (!(e || g)) continue;
+    const int y = i / W, x = i - y * W;
+    nu += 1; ni += (e && g) ? 1 : 0;
+    if (e) { ne += 1; bb[0] = min(bb[0], x); bb[1] = min(bb[1], y); bb[2] = max(bb[2], x); bb[3] = max(bb[3], y); }
+    if (g) { ng += 1; bb[4] = min(bb[4], x); bb[5] = min(bb[5], y); bb[6] = max(bb[6], x); bb[7] = max(bb[7], y); }
+  }
+  const int cnt[4] = {warp_sum(nu), warp_sum(ni), warp_sum(ne), warp_sum(ng)};
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    bb[k] = (k & 2) ? __reduce_max_sync(BOP_FULL_MASK, bb[k]) : __reduce_min_sync(BOP_FULL_MASK, bb[k]);
+  if ((threadIdx.x & 31) == 0) {
+    unsigned long long* c = counts + (size_t)pair * (2 + BOP_MAX_TAUS);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (cnt[k]) atomicAdd(c + k, (unsigned long long)cnt[k]);
+    int* o = mbox + (size_t)pair * 8;
+    if (cnt[2]) { atomicMin(o + 0, bb[0]); atomicMin(o + 1, bb[1]); atomicMax(o + 2, bb[2]); atomicMax(o + 3, bb[3]); }
+    if (cnt[3]) { atomicMin(o + 4, bb[4]); atomicMin(o + 5, bb[5]); atomicMax(o + 6, bb[6]); atomicMax(o + 7, bb[7]); }
+  }
+}
+}  // namespace
+
+extern "C" size_t bop_mask_stats_workspace_bytes(int n_pairs) {
+  return align_up((size_t)n_pairs * (2 + BOP_MAX_TAUS) * 8, 256) + align_up((size_t)n_pairs * 8 * sizeof(int), 256);
+}
+
+extern "C" int bop_mask_overlap_from_depth_dev(const float* depth_est, const float* depth_gt,
+                                               int n_pairs, int height, int width, double* cus_out,
+                                               double* cou_bb_out, int64_t* counts_out,
+                                               int32_t* bbox_out, void* workspace,
+                                               size_t workspace_bytes, void* stream) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(depth_est && depth_gt, "bop_mask_overlap_from_depth_dev: null pointer");
+  BOP_REQUIRE(height > 0 && width > 0, "bop_mask_overlap_from_depth_dev: bad image size");
+  BOP_REQUIRE(workspace && workspace_bytes >= bop_mask_stats_workspace_bytes(n_pairs),
+              "bop_mask_overlap_from_depth_dev: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  const size_t cbytes = align_up((size_t)n_pairs * (2 + BOP_MAX_TAUS) * 8, 256);
+  unsigned long long* counts = (unsigned long long*)ws;
+  int* mbox = (int*)(ws + cbytes);
+  BOP_CUDA(cudaMemsetAsync(ws, 0, cbytes, s));
+  fill_i32_pattern_kernel<<<(n_pairs * 8 + 255) / 256, 256, 0, s>>>(mbox, n_pairs);
+  BOP_LAUNCH_CHECK();
+  const int chunks = max(1, min(64, (height * width + 256 * 16 - 1) / (256 * 16)));
+  bop_prof_begin(BOP_PROF_MASK, s);
+  mask_stats_kernel<<<dim3(n_pairs, chunks), 256, 0, s>>>(depth_est, depth_gt, height, width, counts, mbox);
+  bop_prof_end(BOP_PROF_MASK, s);
+  BOP_LAUNCH_CHECK();
+  mask_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, mbox, n_pairs, cus_out, cou_bb_out,
+                                                             (long long*)counts_out, bbox_out);
   BOP_LAUNCH_CHECK();
   return 0;
 }

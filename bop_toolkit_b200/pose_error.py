@@ -1,4 +1,5 @@
-"""Drop-in replacement for bop_toolkit_lib.pose_error (vsd, mssd, mspd, add, adi, re, te, proj).
+"""Drop-in replacement for bop_toolkit_lib.pose_error (vsd, mssd, mspd, add, adi, re, te, proj,
+cus, cou_mask, cou_bb, cou_bb_proj).
 
 Same positional signatures, numpy in / Python float (or list of floats) out, same exceptions
 (bop_toolkit_lib/pose_error.py:17-232).  Each call is a batch-of-1 wrapper over the batched
@@ -146,3 +147,54 @@ def vsd(R_est, t_est, R_gt, t_gt, depth_test, K, delta, taus,
       np.asarray(depth_test), None, K.reshape(1, 9), float(diameter), delta, taus,
       normalized_by_diameter, cost_type, 'bop19', device=_device())
   return [float(e) for e in err.cpu()[0]]
+
+
+def _mask_stats(R_est, t_est, R_gt, t_gt, K, renderer, obj_id):
+  """Silhouette statistics of the two poses (the shared front half of cus / cou_bb_proj)."""
+  K = np.asarray(K, dtype=np.float64)
+  from .renderer import RendererCuda
+  if isinstance(renderer, RendererCuda):
+    ms = renderer.model_set
+    return batch.mask_overlap_batch(ms, ms.index_of(obj_id), _pose(R_est, t_est), _pose(R_gt, t_gt),
+                                    K.reshape(1, 9), renderer.height, renderer.width)
+  fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+  depth_est = renderer.render_object(obj_id, R_est, t_est, fx, fy, cx, cy)['depth']
+  depth_gt = renderer.render_object(obj_id, R_gt, t_gt, fx, fy, cx, cy)['depth']
+  return batch.mask_overlap_from_depth_batch(np.asarray(depth_est, np.float32) > 0,
+                                             np.asarray(depth_gt, np.float32) > 0, _device())
+
+
+def cus(R_est, t_est, R_gt, t_gt, K, renderer, obj_id):
+  """Complement over Union of projected 2D masks (pose_error.py:256-286)."""
+  return _scalar(_mask_stats(R_est, t_est, R_gt, t_gt, K, renderer, obj_id)['cus'])
+
+
+def cou_mask(mask_est, mask_gt):
+  """Complement over Union of 2D binary masks (pose_error.py:235-253)."""
+  st = batch.mask_overlap_from_depth_batch(np.asarray(mask_est).astype(bool),
+                                           np.asarray(mask_gt).astype(bool), _device())
+  return _scalar(st['cus'])
+
+
+def cou_bb(bb_est, bb_gt):
+  """Complement over Union of 2D bounding boxes (x, y, w, h) (pose_error.py:289-297 with
+  misc.iou, misc.py:236-263).  Four scalars per box: plain host arithmetic."""
+  ax0, ay0, ax1, ay1 = bb_est[0], bb_est[1], bb_est[0] + bb_est[2], bb_est[1] + bb_est[3]
+  bx0, by0, bx1, by1 = bb_gt[0], bb_gt[1], bb_gt[0] + bb_gt[2], bb_gt[1] + bb_gt[3]
+  w_inter = min(ax1, bx1) - max(ax0, bx0)
+  h_inter = min(ay1, by1) - max(ay0, by0)
+  iou = 0.0
+  if w_inter > 0 and h_inter > 0:
+    area_inter = w_inter * h_inter
+    iou = area_inter / float(bb_est[2] * bb_est[3] + bb_gt[2] * bb_gt[3] - area_inter)
+  return 1.0 - iou
+
+
+def cou_bb_proj(R_est, t_est, R_gt, t_gt, K, renderer, obj_id):
+  """Complement over Union of projected 2D bounding boxes (pose_error.py:300-330).  Like the
+  reference (`xs.min()` of an empty array), raises ValueError when a silhouette is empty."""
+  st = _mask_stats(R_est, t_est, R_gt, t_gt, K, renderer, obj_id)
+  counts = st['counts'].cpu()[0]
+  if int(counts[2]) == 0 or int(counts[3]) == 0:
+    raise ValueError('zero-size array to reduction operation minimum which has no identity')
+  return _scalar(st['cou_bb'])

@@ -90,7 +90,7 @@ uint64_t    bop_kernel_launch_count(void);
 
 /* Per-kernel device timing (CUDA events on the launching stream), used by bench.py for the
  * roofline figure.  Slots: 0 fused VSD kernel, 1 VSD bbox+plan, 2 MSSD, 3 MSPD, 4 K2 pixel pass,
- * 5 render, 6 ADI.  bop_profile_sum_ms synchronises on the recorded events and returns the summed
+ * 5 render, 6 ADI, 7 mask overlap.  bop_profile_sum_ms synchronises on the recorded events and returns the summed
  * duration of the last `last_n` timed launches of the slot (0 = all kept, ring of 256).        */
 int bop_profile_enable(int on);
 int bop_profile_reset(void);
@@ -181,6 +181,33 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
+
+/* ---- mask overlap: pose_error.cus / cou_bb_proj / cou_mask --------------------
+ * pose_error.cus (pose_error.py:256-286): 1 - |mask_est & mask_gt| / |mask_est | mask_gt| of the
+ * two rendered silhouettes (1.0 when the union is empty); pose_error.cou_bb_proj (:300-330):
+ * 1 - IoU of the pixel bounding boxes of the two silhouettes (misc.calc_2d_bbox misc.py:202-218,
+ * misc.iou misc.py:236-263; NaN when a silhouette is empty -- the reference raises there).
+ * cam: [n_pairs][4] fx,fy,cx,cy.  gate != 0 applies the driver's sphere-projection gate
+ * (scripts/eval_calc_errors.py:296-300,349-354) -> cus = 1.0.
+ * Outputs (each may be NULL): cus_out, cou_bb_out [n_pairs] float64; counts_out [n_pairs][4]
+ * int64 = union, inter, est, gt pixel counts; bbox_out [n_pairs][8] int32 = (x, y, w, h) of the
+ * est then of the gt silhouette (w = xmax - xmin; w = h = -1 when empty).
+ * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_pts) bytes.                      */
+int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                         const double* pose_est, const double* pose_gt, const double* cam,
+                         int n_pairs, int max_pts, int height, int width, int gate,
+                         double* cus_out, double* cou_bb_out, int64_t* counts_out,
+                         int32_t* bbox_out, void* workspace, size_t workspace_bytes,
+                         void* stream);
+/* Same statistics for pre-rendered depth images or binary masks ([n_pairs][H][W] float32,
+ * non-zero = inside): pose_error.cou_mask (pose_error.py:235-253) and the tail of cus /
+ * cou_bb_proj when a foreign Renderer produced the images.
+ * workspace: bop_mask_stats_workspace_bytes(n_pairs) bytes.                              */
+size_t bop_mask_stats_workspace_bytes(int n_pairs);
+int bop_mask_overlap_from_depth_dev(const float* depth_est, const float* depth_gt, int n_pairs,
+                                    int height, int width, double* cus_out, double* cou_bb_out,
+                                    int64_t* counts_out, int32_t* bbox_out, void* workspace,
+                                    size_t workspace_bytes, void* stream);
 
 /* depth_test may also be a pointer into PINNED HOST memory (cudaHostAlloc / cudaHostRegister;
  * with unified addressing the host pointer is valid on the device): the fused kernel then pulls

@@ -232,3 +232,51 @@ def te(t_est, t_gt):
   """bop_toolkit_lib/pose_error.py:205-214."""
   assert t_est.size == t_gt.size == 3
   return np.linalg.norm(t_gt - t_est)
+
+
+def calc_2d_bbox(xs, ys):
+  """misc.calc_2d_bbox without clipping (bop_toolkit_lib/misc.py:202-218): (x, y, w, h) with
+  w = xmax - xmin, h = ymax - ymin."""
+  return [xs.min(), ys.min(), xs.max() - xs.min(), ys.max() - ys.min()]
+
+
+def iou(bb_a, bb_b):
+  """misc.iou (bop_toolkit_lib/misc.py:236-263)."""
+  tl_a, br_a = (bb_a[0], bb_a[1]), (bb_a[0] + bb_a[2], bb_a[1] + bb_a[3])
+  tl_b, br_b = (bb_b[0], bb_b[1]), (bb_b[0] + bb_b[2], bb_b[1] + bb_b[3])
+  w_inter = min(br_a[0], br_b[0]) - max(tl_a[0], tl_b[0])
+  h_inter = min(br_a[1], br_b[1]) - max(tl_a[1], tl_b[1])
+  if w_inter > 0 and h_inter > 0:
+    area_inter = w_inter * h_inter
+    return area_inter / float(bb_a[2] * bb_a[3] + bb_b[2] * bb_b[3] - area_inter)
+  return 0.0
+
+
+def cou_mask(mask_est, mask_gt):
+  """pose_error.cou_mask (bop_toolkit_lib/pose_error.py:235-253)."""
+  me, mg = mask_est.astype(bool), mask_gt.astype(bool)
+  union_count = float(np.logical_or(mg, me).sum())
+  return 1.0 - np.logical_and(mg, me).sum() / union_count if union_count > 0 else 1.0
+
+
+def cus(R_est, t_est, R_gt, t_gt, K, renderer, obj_id):
+  """pose_error.cus (bop_toolkit_lib/pose_error.py:256-286)."""
+  fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+  depth_est = renderer.render_object(obj_id, R_est, t_est, fx, fy, cx, cy)['depth']
+  depth_gt = renderer.render_object(obj_id, R_gt, t_gt, fx, fy, cx, cy)['depth']
+  return cou_mask(depth_est > 0, depth_gt > 0)
+
+
+def cou_bb(bb_est, bb_gt):
+  """pose_error.cou_bb (bop_toolkit_lib/pose_error.py:289-297)."""
+  return 1.0 - iou(bb_est, bb_gt)
+
+
+def cou_bb_proj(R_est, t_est, R_gt, t_gt, K, renderer, obj_id):
+  """pose_error.cou_bb_proj (bop_toolkit_lib/pose_error.py:300-330)."""
+  fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+  depth_est = renderer.render_object(obj_id, R_est, t_est, fx, fy, cx, cy)['depth']
+  depth_gt = renderer.render_object(obj_id, R_gt, t_gt, fx, fy, cx, cy)['depth']
+  ys_est, xs_est = (depth_est > 0).nonzero()
+  ys_gt, xs_gt = (depth_gt > 0).nonzero()
+  return 1.0 - iou(calc_2d_bbox(xs_est, ys_est), calc_2d_bbox(xs_gt, ys_gt))

@@ -113,6 +113,20 @@ def main():
              vsd_render_est=np.array(ren_e), vsd_render_gt=np.array(ren_g),
              vsd_step=np.array(vsd_step), vsd_tlinear=np.array(vsd_tlin),
              vsd_unnorm=np.array(vsd_unnorm))
+  # ---- mask-overlap errors on the same renders (reference functions) -------------------
+  cam = (Kv[0, 0], Kv[1, 1], Kv[0, 2], Kv[1, 2])
+  out['cus'] = np.array([ref_pe.cus(Rv_e[i], tv_e[i].reshape(3, 1), Rv_g[i], tv_g[i].reshape(3, 1), Kv, ren, 7)
+                         for i in range(nv)])
+  out['cou_bb_proj'] = np.array([ref_pe.cou_bb_proj(Rv_e[i], tv_e[i].reshape(3, 1), Rv_g[i],
+                                                    tv_g[i].reshape(3, 1), Kv, ren, 7) for i in range(nv)])
+  out['cou_mask'] = np.array([ref_pe.cou_mask(ren_e[i] > 0, ren_g[i] > 0) for i in range(nv)])
+  bbs = rng.integers(0, 60, size=(12, 2, 4))
+  bbs[0, 1] = bbs[0, 0]                      # identical boxes
+  bbs[1, 1, :2] = bbs[1, 0, :2] + 500        # disjoint boxes
+  out['cou_bb_in'] = bbs
+  out['cou_bb'] = np.array([ref_pe.cou_bb(list(map(int, b[0])), list(map(int, b[1]))) for b in bbs])
+  out['bbox2d'] = np.array([ref_misc.calc_2d_bbox(*np.nonzero(ren_e[i] > 0)[::-1]) for i in range(nv)])
+
   # dist image + visibility masks of pair 1 (reference functions, called directly)
   d_test = ref_misc.depth_im_to_dist_im_fast(depth_tests[1], Kv)
   d_gt = ref_misc.depth_im_to_dist_im_fast(ren_g[1], Kv)

@@ -32,7 +32,7 @@ from oracle import renderer_oracle            # noqa: E402
 DATASET_KW = dict(dataset='lmo', split='test', scene_ids=(2, 3), n_images=3, obj_ids=(1, 5, 6, 8, 9, 10, 11, 12),
                   objs_per_image=4, ests_per_target=3, seed=7)
 RUNS = [('vsd', 1), ('vsd', -1), ('mssd', 1), ('mssd', 0), ('mspd', 1), ('mspd', -1), ('ad', 1),
-        ('add', 1), ('adi', 1), ('proj', 1), ('rete', 1), ('re', 1), ('te', 0)]
+        ('add', 1), ('adi', 1), ('proj', 1), ('cus', 1), ('rete', 1), ('re', 1), ('te', 0)]
 
 
 def oracle_render_fn(pts, faces, R, t, K):

@@ -124,7 +124,7 @@ def test_writer_layout_roundtrip(driver_golden):
   assert n >= 60
 
 
-TOL = {'vsd': (0.0, 1e-3), 'adi': (1e-5, 1e-6), 'ad': (1e-5, 1e-6), 're': (1e-5, 1e-6), 'rete': (1e-5, 1e-6)}
+TOL = {'vsd': (0.0, 1e-3), 'cus': (0.0, 2e-3), 'adi': (1e-5, 1e-6), 'ad': (1e-5, 1e-6), 're': (1e-5, 1e-6), 'rete': (1e-5, 1e-6)}
 
 
 @pytest.mark.gpu

@@ -485,3 +485,76 @@ def test_vsd_zero_copy_pinned_depth(B):
   assert torch.equal(c, d)
   with pytest.raises(ValueError):
     B.vsd_batch(ms, 0, pe, pg, torch.from_numpy(depth), im, Ks, 15, taus, zero_copy=True)
+
+
+# ------------------------------------------------------------------ mask-overlap errors
+def test_mask_overlap_bit_exact_given_reference_renders(B, golden):
+  """cus / cou_bb_proj / cou_mask from identical depth images: integer pixel statistics, so the
+  errors equal the reference's bit for bit."""
+  from bop_toolkit_b200 import pose_error as pe
+  g = golden
+  st = B.mask_overlap_from_depth_batch(g['vsd_render_est'], g['vsd_render_gt'])
+  assert np.array_equal(st['cus'].cpu().numpy(), g['cus'])
+  assert np.array_equal(st['cus'].cpu().numpy(), g['cou_mask'])
+  assert np.array_equal(st['cou_bb'].cpu().numpy(), g['cou_bb_proj'])
+  assert np.array_equal(st['bbox'].cpu().numpy()[:, :4], g['bbox2d'])
+  n = g['cus'].shape[0]
+  for i in range(n):
+    assert pe.cou_mask(g['vsd_render_est'][i] > 0, g['vsd_render_gt'][i] > 0) == g['cou_mask'][i]
+  for b, e in zip(g['cou_bb_in'], g['cou_bb']):
+    assert pe.cou_bb(list(map(int, b[0])), list(map(int, b[1]))) == e
+  # empty masks: union == 0 -> 1.0 (pose_error.py:250-252)
+  z = np.zeros((1, 8, 12), np.float32)
+  st = B.mask_overlap_from_depth_batch(z, z)
+  assert float(st['cus'].cpu()[0]) == 1.0 and np.isnan(float(st['cou_bb'].cpu()[0]))
+
+  class Foreign(object):   # duck-typed renderer handing back the reference's renders
+    def __init__(self):
+      self.k = 0
+    def render_object(self, obj_id, R, t, fx, fy, cx, cy):
+      i, which = divmod(self.k, 2)
+      self.k += 1
+      return {'depth': (g['vsd_render_est'] if which == 0 else g['vsd_render_gt'])[i % n]}
+  ren = Foreign()
+  for i in range(n):
+    a = (g['vsd_R_e'][i], g['vsd_t_e'][i].reshape(3, 1), g['vsd_R_g'][i], g['vsd_t_g'][i].reshape(3, 1), g['vsd_K'], ren, 7)
+    assert pe.cus(*a) == g['cus'][i]
+  ren.k = 0
+  for i in range(n):
+    a = (g['vsd_R_e'][i], g['vsd_t_e'][i].reshape(3, 1), g['vsd_R_g'][i], g['vsd_t_g'][i].reshape(3, 1), g['vsd_K'], ren, 7)
+    assert pe.cou_bb_proj(*a) == g['cou_bb_proj'][i]
+
+
+def test_cus_fused_vs_reference_golden(B, golden):
+  """cus / cou_bb_proj with the library's own rasteriser (fused, nothing leaves the SM but
+  counts) against the reference run on the oracle's renders.  Budget: the silhouettes may differ
+  in <= 0.5 % of their edge pixels (1/256-px snapping), i.e. a few pixels of some thousands."""
+  from bop_toolkit_b200 import pose_error as pe, renderer
+  g = golden
+  H, W = g['vsd_depth_test'].shape[1:]
+  ren = renderer.create_renderer(W, H, 'cuda', mode='depth')
+  ren.add_object(7, pts=g['vsd_pts'], faces=g['vsd_faces'], diameter=180.0)
+  n = g['cus'].shape[0]
+  pe_, pg_ = _poses(B, g['vsd_R_e'], g['vsd_t_e']), _poses(B, g['vsd_R_g'], g['vsd_t_g'])
+  st = B.mask_overlap_batch(ren.model_set, 0, pe_, pg_, g['vsd_K'], H, W)
+  ref = B.mask_overlap_from_depth_batch(g['vsd_render_est'], g['vsd_render_gt'])
+  cnt, cnt_ref = st['counts'].cpu().numpy(), ref['counts'].cpu().numpy()
+  assert np.all(np.abs(cnt - cnt_ref) <= 3), (cnt, cnt_ref)
+  assert np.allclose(st['cus'].cpu().numpy(), g['cus'], rtol=0, atol=2e-3)
+  assert np.all(np.abs(st['bbox'].cpu().numpy() - ref['bbox'].cpu().numpy()) <= 1)
+  assert np.allclose(st['cou_bb'].cpu().numpy(), g['cou_bb_proj'], rtol=0, atol=2e-2)
+  # fused == (render -> stats), bit for bit
+  de = B.render_batch(ren.model_set, 0, pe_, np.tile(g['vsd_K'].reshape(9)[[0, 4, 2, 5]], (n, 1)), H, W)
+  dg = B.render_batch(ren.model_set, 0, pg_, np.tile(g['vsd_K'].reshape(9)[[0, 4, 2, 5]], (n, 1)), H, W)
+  two = B.mask_overlap_from_depth_batch(de, dg)
+  for k in ('cus', 'cou_bb', 'counts', 'bbox'):
+    assert np.array_equal(st[k].cpu().numpy(), two[k].cpu().numpy(), equal_nan=True), k
+  for i in range(3):
+    a = (g['vsd_R_e'][i], g['vsd_t_e'][i].reshape(3, 1), g['vsd_R_g'][i], g['vsd_t_g'][i].reshape(3, 1), g['vsd_K'], ren, 7)
+    assert pe.cus(*a) == float(st['cus'].cpu()[i])
+    assert pe.cou_bb_proj(*a) == float(st['cou_bb'].cpu()[i])
+  # sphere gate of the driver: a far-away estimate -> 1.0
+  far = pe_.copy()
+  far[:, 9] += 5000.0
+  gated = B.cus_batch(ren.model_set, 0, far, pg_, g['vsd_K'], H, W, gate=True).cpu().numpy()
+  assert np.all(gated == 1.0)

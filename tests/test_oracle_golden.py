@@ -128,3 +128,23 @@ def test_oracle_raster_known_answer(oracle_built):
   # reversed winding gives the same image (no culling)
   d2 = renderer_oracle.render_depth(pts, faces[:, ::-1].copy(), np.eye(3), [0, 0, 100.0], 100.0, 100.0, 20.5, 20.5, 40, 40)
   assert np.array_equal(d, d2)
+
+
+def test_mask_overlap_errors(golden, oracle_built):
+  """cus / cou_mask / cou_bb / cou_bb_proj of the oracle == the reference's, bit for bit."""
+  g = golden
+  H, W = g['vsd_depth_test'].shape[1:]
+  ren = renderer_oracle.RendererOracle(W, H)
+  ren.add_object(7, pts=g['vsd_pts'], faces=g['vsd_faces'])
+  Kv = g['vsd_K']
+  n = g['vsd_R_e'].shape[0]
+  for i in range(n):
+    a = (g['vsd_R_e'][i], g['vsd_t_e'][i].reshape(3, 1), g['vsd_R_g'][i], g['vsd_t_g'][i].reshape(3, 1), Kv, ren, 7)
+    assert po.cus(*a) == g['cus'][i]
+    assert po.cou_bb_proj(*a) == g['cou_bb_proj'][i]
+    assert po.cou_mask(g['vsd_render_est'][i] > 0, g['vsd_render_gt'][i] > 0) == g['cou_mask'][i]
+    ys, xs = np.nonzero(g['vsd_render_est'][i] > 0)
+    assert list(po.calc_2d_bbox(xs, ys)) == list(g['bbox2d'][i])
+  for b, e in zip(g['cou_bb_in'], g['cou_bb']):
+    assert po.cou_bb(list(map(int, b[0])), list(map(int, b[1]))) == e
+  assert g['cus'][0] == 0.0 and g['cou_bb'][0] == 0.0 and g['cou_bb'][1] == 1.0
