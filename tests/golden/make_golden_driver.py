@@ -6,7 +6,10 @@ A small synthetic dataset in BOP layout is written with bop_toolkit_b200.synth.w
 (deterministic: seeded numpy + the float64 C oracle rasteriser for the depth images), then the
 REAL reference script is executed unmodified (runpy) for every error type, with the usual shim
 (stub pytz / imageio / png, numpy.float) and `renderer.create_renderer` patched to return the
-oracle rasteriser -- the reference's GL renderers cannot run here.  The text of every errors_*.json
+oracle rasteriser -- the reference's GL renderers cannot run here.  The oracle renders with
+window positions snapped to 1/256 px, as OpenGL implementations do (GL_SUBPIXEL_BITS = 8 on the
+GPUs the reference ran on): with ~400-pixel silhouettes of the small test models a single edge
+pixel moves VSD by 2.5e-3, so the comparison needs the same snapping rule on both sides.  The text of every errors_*.json
 it writes is stored in tests/golden/driver_golden.json together with a checksum of the dataset,
 so the tests can regenerate the same dataset on the GPU box and compare file by file.
 """
@@ -76,7 +79,7 @@ def install_reference_shim():
       self.models[obj_id] = (m['pts'], m['faces'].astype(np.int32))
 
   ref_renderer.create_renderer = lambda w, h, renderer_type='cpp', mode='rgb+depth', **kw: \
-    RefOracleRenderer(w, h, mode)
+    RefOracleRenderer(w, h, mode, subpixel_bits=8)
 
 
 def main():
