@@ -384,7 +384,8 @@ def gpu_arm(args):
   achieved = n_active * alg_pair / (fused_ms * 1e-3) / 1e9
   traffic = None
   try:
-    traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['fused_kernel_dram_bytes_per_launch']
+    # measured DRAM bytes per evaluated pair (one ncu --set full capture) x pairs in this launch
+    traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['fused_kernel_dram_bytes_per_pair'] * n_active
   except Exception:
     pass
   small = sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_im, h_K, h_scale)) + \
