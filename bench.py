@@ -298,7 +298,7 @@ def gpu_arm(args):
     mspd = batch.mspd_batch(ms, d_obj, d_pe, d_pg, d_K)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
     if world > 1:   # the path's one exchange step: all-gather of fixed-width error records
-      return sharding.gather_records(ids, errs)[1]
+      return sharding.gather_records(ids, errs, counts=[P] * world)[1]
     return errs
 
   def step_e2e(zero_copy=True):
@@ -312,7 +312,7 @@ def gpu_arm(args):
     mspd = batch.mspd_batch(ms, o, a, b, h_K)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
     if world > 1:
-      sharding.gather_records(ids, errs)
+      sharding.gather_records(ids, errs, counts=[P] * world)
     h_out.copy_(errs, non_blocking=True)
     return errs
 

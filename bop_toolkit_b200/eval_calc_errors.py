@@ -322,14 +322,21 @@ def _shard_pairs(sp, rank, world):
   return np.nonzero(owner[sp.im_pos] == rank)[0]
 
 
-def _gather_errors(errs, sel, n_pairs, device):
-  """All-gathers (pair index, error row) from every rank -> float64 [n_pairs, T] on every rank."""
+def _gather_errors(errs, sel, n_pairs, device, sp=None, world=None):
+  """All-gathers (pair index, error row) from every rank -> float64 [n_pairs, T] on every rank.
+  With `sp` the per-rank row counts follow from the (deterministic) image assignment, so the
+  gather is a single collective."""
   import torch
   from . import sharding
+  counts = None
+  if sp is not None and world:
+    cost = np.bincount(sp.im_pos, minlength=len(sp.im_ids))
+    owner = sharding.assign_images(cost, world)
+    counts = np.bincount(owner[sp.im_pos], minlength=world).tolist()
   ids = torch.zeros((len(sel), 5), dtype=torch.int32, device=device)
   ids[:, 0] = torch.from_numpy(sel.astype(np.int32)).to(device)
   e = torch.from_numpy(np.ascontiguousarray(errs)).to(device)
-  ids_all, e_all = sharding.gather_records(ids, e)
+  ids_all, e_all = sharding.gather_records(ids, e, counts=counts)
   out = np.full((n_pairs, errs.shape[1]), np.nan)
   out[ids_all[:, 0].cpu().numpy().astype(np.int64)] = e_all.cpu().numpy()
   return out
@@ -403,7 +410,7 @@ def calc_errors(p, device=None, log=misc.log, write=True):
       sel = _shard_pairs(sp, rank, world)
       errs = engine.compute(scene_id, sp, scene_camera, sel)
       if world > 1:
-        errs = _gather_errors(errs, sel, len(sp.rec), engine.device)
+        errs = _gather_errors(errs, sel, len(sp.rec), engine.device, sp=sp, world=world)
       records = fill_records(sp, errs)
       scenes[scene_id] = records
       if write and rank == 0:

@@ -27,39 +27,45 @@ def round_robin(n_images, world_size):
   return (np.arange(n_images) % world_size).astype(np.int32)
 
 
-def gather_records(ids, errs, group=None):
-  """All-gathers per-rank error records.
+def gather_records(ids, errs, group=None, counts=None):
+  """All-gathers per-rank error records in ONE collective.
   ids: int32 [n, 5] = scene_id, im_id, obj_id, est_id, gt_id; errs: float64 [n, T] (score may be
-  carried as an extra column).  Shards differ in size: counts are exchanged first, payloads are
-  padded to the maximum.  Returns (ids_all [N,5], errs_all [N,T]) ordered by rank."""
+  carried as an extra column).  The ids are bit-cast into three float64 lanes in front of the
+  errors, so a record is one fixed-width row of (3 + T) float64 and a single
+  all_gather_into_tensor moves everything (NCCL copies bytes; no arithmetic touches the lanes).
+  Shards differ in size: `counts` (rows per rank, known to every rank when the image assignment
+  is deterministic) skips the count exchange; otherwise counts are all-gathered first.
+  Payloads are padded to the maximum.  Returns (ids_all [N,5], errs_all [N,T]) ordered by rank."""
   if not dist.is_initialized() or dist.get_world_size(group) == 1:
     return ids, errs
   ws = dist.get_world_size(group)
   dev = ids.device
-  n = torch.tensor([ids.shape[0]], dtype=torch.int64, device=dev)
-  counts = [torch.zeros_like(n) for _ in range(ws)]
-  dist.all_gather(counts, n, group=group)
-  counts = [int(c.item()) for c in counts]
-  m = max(counts)
-  T = errs.shape[1]
-  # one payload: ids bit-cast into float64 lanes would lose nothing, but two gathers keep dtypes
-  ids_p = torch.zeros((m, ids.shape[1]), dtype=ids.dtype, device=dev)
-  err_p = torch.zeros((m, T), dtype=errs.dtype, device=dev)
-  ids_p[:ids.shape[0]] = ids
-  err_p[:errs.shape[0]] = errs
-  ids_all = torch.empty((ws * m, ids.shape[1]), dtype=ids.dtype, device=dev)
-  err_all = torch.empty((ws * m, T), dtype=errs.dtype, device=dev)
-  if dev.type == 'cuda':
-    dist.all_gather_into_tensor(ids_all, ids_p, group=group)
-    dist.all_gather_into_tensor(err_all, err_p, group=group)
+  n, T = ids.shape[0], errs.shape[1]
+  if counts is None:
+    c = torch.tensor([n], dtype=torch.int64, device=dev)
+    cl = [torch.zeros_like(c) for _ in range(ws)]
+    dist.all_gather(cl, c, group=group)
+    counts = [int(x.item()) for x in cl]
   else:
-    l1 = [torch.empty_like(ids_p) for _ in range(ws)]
-    l2 = [torch.empty_like(err_p) for _ in range(ws)]
-    dist.all_gather(l1, ids_p, group=group)
-    dist.all_gather(l2, err_p, group=group)
-    ids_all, err_all = torch.cat(l1), torch.cat(l2)
-  keep = torch.cat([torch.arange(c, device=dev) + r * m for r, c in enumerate(counts)])
-  return ids_all[keep], err_all[keep]
+    counts = [int(x) for x in counts]
+    assert counts[dist.get_rank(group)] == n
+  m = max(counts)
+  row = torch.zeros((m, 3 + T), dtype=torch.float64, device=dev)
+  if n:
+    row[:n, :3].view(torch.int32)[:, :5] = ids
+    row[:n, 3:] = errs
+  out = torch.empty((ws * m, 3 + T), dtype=torch.float64, device=dev)
+  if dev.type == 'cuda':
+    dist.all_gather_into_tensor(out, row, group=group)
+  else:
+    parts = [torch.empty_like(row) for _ in range(ws)]
+    dist.all_gather(parts, row, group=group)
+    out = torch.cat(parts)
+  if any(c != m for c in counts):
+    keep = torch.cat([torch.arange(c, device=dev) + r * m for r, c in enumerate(counts)])
+    out = out[keep]
+  ids_all = out[:, :3].contiguous().view(torch.int32)[:, :5]
+  return ids_all, out[:, 3:]
 
 
 def allreduce_counts(counts, group=None):

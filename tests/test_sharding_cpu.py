@@ -37,6 +37,20 @@ def _worker(rank, ws, port, out_dir):
   errs = torch.tensor(errs, dtype=torch.float64).reshape(-1, 2)
   ids_all, errs_all = sharding.gather_records(ids, errs)
   cnt = sharding.allreduce_counts(torch.tensor([ids.shape[0]], dtype=torch.int64))
+  # counts known up front (deterministic assignment): same result without the count exchange
+  known = [int(pairs_per_im[owner == r].sum()) for r in range(ws)]
+  ids_k, errs_k = sharding.gather_records(ids, errs, counts=known)
+  assert torch.equal(ids_k, ids_all) and torch.equal(errs_k, errs_all)
+  # the driver's shard / gather helpers (eval_calc_errors.py) on the same data
+  from bop_toolkit_b200 import eval_calc_errors as ece
+  sp = ece.ScenePairs()
+  sp.im_ids = list(range(n_im))
+  sp.im_pos = np.repeat(np.arange(n_im), pairs_per_im).astype(np.int32)
+  sp.rec = np.arange(len(sp.im_pos))
+  sel = ece._shard_pairs(sp, rank, ws)
+  mine = np.stack([sel.astype(np.float64), 2.0 * sel], axis=1)
+  full = ece._gather_errors(mine, sel, len(sp.rec), torch.device('cpu'), sp=sp, world=ws)
+  assert np.array_equal(full[:, 0], np.arange(len(sp.rec))) and np.array_equal(full[:, 1], 2.0 * full[:, 0])
   np.savez(os.path.join(out_dir, 'r%d.npz' % rank), ids=ids_all.numpy(), errs=errs_all.numpy(),
            cnt=cnt.numpy(), own=owner)
   dist.destroy_process_group()
