@@ -77,6 +77,9 @@ _SIGNATURES = {
                                 ctypes.c_size_t, _P]),
   'bop_mask_stats_workspace_bytes': (ctypes.c_size_t, [_I]),
   'bop_mask_overlap_from_depth_dev': (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
+  'bop_gt_info_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I, _I, _I, _I]),
+  'bop_gt_info_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, ctypes.c_double, _I, _I,
+                           _P, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
   'bop_model_upload': (_I, [_P, _I, _P, _I, _P, _I, ctypes.c_double, _P, _P]),
   'bop_model_free': (_I, [_P, _P]),
   'bop_mssd_host': (_I, [_P, _I, _P, _P, _I, _I, _P]),

@@ -504,6 +504,49 @@ def mask_overlap_from_depth_batch(depth_est, depth_gt, device=None):
   return out
 
 
+def gt_info_batch(models, obj, pose_gt, depth_test, im_idx, K, delta=15, depth_scale=None,
+                  margin=None, want_masks=False, zero_copy=False):
+  """The per-instance body of scripts/calc_gt_info.py / calc_gt_masks.py for B GT instances.
+  depth_test: [n_im,H,W] float32 mm or uint16 raw + depth_scale[n_im]; im_idx: [B]; K: [n_im,9].
+  margin: (mx, my) canvas margin around the image; None = (W, H), the 3x canvas of calc_gt_info;
+  (0, 0) = calc_gt_masks.  Returns a dict of device tensors: 'counts' [B,3] int64 =
+  px_count_all / valid / visib, 'visib_fract' [B], 'bbox' [B,8] int32 = bbox_obj, bbox_visib
+  (x, y, w, h), and with want_masks 'mask' / 'mask_visib' [B,H,W] uint8 (0 / 255)."""
+  dev = models.device
+  p = to_device(pose_gt, torch.float64, dev)
+  n = p.numel() // 12
+  oi = _obj_idx(models, obj, n)
+  dd, code = _depth_input(depth_test, dev, zero_copy)
+  n_im, H, W = dd.shape
+  Kd = to_device(K, torch.float64, dev).reshape(-1, 9)
+  if Kd.shape[0] == 1 and n_im > 1:
+    Kd = Kd.expand(n_im, 9).contiguous()
+  ii = to_device(im_idx, torch.int32, dev, (n,)) if im_idx is not None else \
+    (torch.zeros(n, dtype=torch.int32, device=dev) if n_im == 1 else torch.arange(n, dtype=torch.int32, device=dev))
+  sc = None
+  if code == _lib.DEPTH_U16:
+    sc = to_device(depth_scale if depth_scale is not None else np.ones(n_im, np.float32),
+                   torch.float32, dev, (n_im,))
+  mx, my = (W, H) if margin is None else (int(margin[0]), int(margin[1]))
+  out = {'counts': torch.empty((n, 3), dtype=torch.int64, device=dev),
+         'visib_fract': torch.empty(n, dtype=torch.float64, device=dev),
+         'bbox': torch.empty((n, 8), dtype=torch.int32, device=dev)}
+  if want_masks:
+    out['mask'] = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
+    out['mask_visib'] = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
+  wsb = _lib.lib().bop_gt_info_workspace_bytes(n, H, W, mx, my, models.max_pts)
+  ws = _workspace(dev, wsb)
+  with torch.cuda.device(dev):
+    rc = _lib.lib().bop_gt_info_dev(
+      models.table.data_ptr(), oi.data_ptr(), p.data_ptr(), dd.data_ptr(),
+      sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(), n, models.max_pts,
+      H, W, code, float(delta), mx, my, out['counts'].data_ptr(), out['visib_fract'].data_ptr(),
+      out['bbox'].data_ptr(), out['mask'].data_ptr() if want_masks else None,
+      out['mask_visib'].data_ptr() if want_masks else None, ws.data_ptr(), wsb, _stream_ptr())
+  _lib.check(rc)
+  return out
+
+
 def depth_bytes_fetched(device, depth_dtype_code):
   """Bytes of depth_test the last vsd_batch pass on `device` fetched (synchronises)."""
   ws = _workspaces[(device.type, device.index)].buf

@@ -88,7 +88,7 @@ project_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restri
                const int32_t* __restrict__ im_idx, const double* __restrict__ K,
                const double* __restrict__ diameters, int cam_mode, int n,
                int n_poses, int H, int W, int gate, int pv_stride, PVert* __restrict__ pv,
-               int4* __restrict__ bbox) {
+               int4* __restrict__ bbox, int cx_off, int cy_off) {
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (gw >= n * n_poses) return;
@@ -113,7 +113,7 @@ project_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restri
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
   PoseCamF P;
-  make_posecam(pose, fx, fy, cx, cy, P);
+  make_posecam(pose, fx, fy, cx + cx_off, cy + cy_off, P);
   const float4* __restrict__ verts = (const float4*)M.verts4;
   PVert* __restrict__ out = pv + (size_t)gw * pv_stride;
   int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
@@ -151,7 +151,8 @@ __global__ void plan_kernel(const bop_model_dev* __restrict__ models,
                             int cam_mode, int n, int n_poses, int H,
                             int W, int tile_px, const int4* __restrict__ bbox,
                             PairDesc* __restrict__ desc, WorkItem* __restrict__ work,
-                            PlanCounters* __restrict__ ctr, unsigned max_items) {
+                            PlanCounters* __restrict__ ctr, unsigned max_items, int cx_off,
+                            int cy_off) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   PairDesc D;
@@ -171,8 +172,8 @@ __global__ void plan_kernel(const bop_model_dev* __restrict__ models,
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
   D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
-  make_posecam(pose_a + 12 * (size_t)i, fx, fy, cx, cy, D.pose[0]);
-  if (n_poses == 2) make_posecam(pose_b + 12 * (size_t)i, fx, fy, cx, cy, D.pose[1]);
+  make_posecam(pose_a + 12 * (size_t)i, fx, fy, cx + cx_off, cy + cy_off, D.pose[0]);
+  if (n_poses == 2) make_posecam(pose_b + 12 * (size_t)i, fx, fy, cx + cx_off, cy + cy_off, D.pose[1]);
   else D.pose[1] = D.pose[0];
   int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
   for (int p = 0; p < n_poses; ++p) {
@@ -226,7 +227,7 @@ struct PixParams {
   int vec_ok;        // rows of depth_test are 16-byte (f32) / 8-byte (u16) aligned
 };
 
-constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2, MODE_MASK = 3;
+constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2, MODE_MASK = 3, MODE_GTINFO = 4;
 
 template <int MODE>
 struct Acc {
@@ -349,6 +350,10 @@ struct FusedArgs {
   double* tl_sums;              // VSD tlinear: [n][BOP_MAX_TAUS] f64
   float* depth_out;             // RENDER: [n][H][W]
   int* mask_bbox;               // MASK: [n][8] = xmin,ymin,xmax,ymax of the est mask, then of the gt mask
+  unsigned char* mask_full;     // GTINFO (optional): [n][H][W] 255 where the object projects
+  unsigned char* mask_visib;    // GTINFO (optional): [n][H][W] 255 where it is visible
+  int canvas_w;                 // clip width of the raster canvas (= pp.W except GTINFO)
+  int mx, my;                   // GTINFO: margin of the canvas around the image (canvas = image + 2 margins)
   unsigned max_items;
   int tile_px;
   int small_tri_px;
@@ -398,7 +403,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
     __syncthreads();
     const int w = sD.w, nrows = sW.nrows;
-    const int cx0 = sD.x0, cx1 = min(sD.x0 + w - 1, a.pp.W - 1);
+    const int cx0 = sD.x0, cx1 = min(sD.x0 + w - 1, a.canvas_w - 1);
     const int cy0 = sD.y0 + sW.row0, cy1 = cy0 + nrows - 1;
     const int npx = nrows * w;
     const int n_poses = sD.n_poses;
@@ -525,6 +530,55 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         int* o = a.mask_bbox + (size_t)sW.pair * 8;
         if (cnt[2]) { atomicMin(o + 0, bb[0]); atomicMin(o + 1, bb[1]); atomicMax(o + 2, bb[2]); atomicMax(o + 3, bb[3]); }
         if (cnt[3]) { atomicMin(o + 4, bb[4]); atomicMin(o + 5, bb[5]); atomicMax(o + 6, bb[6]); atomicMax(o + 7, bb[7]); }
+      }
+      continue;
+    }
+
+    if (MODE == MODE_GTINFO) {
+      // scripts/calc_gt_info.py:113-175 / calc_gt_masks.py:110-133 for one GT instance: the pose
+      // is rendered on a canvas larger than the image (margins mx, my); px_count_all counts the
+      // whole silhouette, the visibility test (visibility.estimate_visib_mask_gt, bop19) runs on
+      // the pixels inside the image.  Boxes are in IMAGE coordinates (may leave the image).
+      int n_all = 0, n_valid = 0, n_vis = 0;
+      int bb[8] = {INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MAX, INT_MAX, INT_MIN, INT_MIN};
+      const float scale = (a.pp.depth_dtype == BOP_DEPTH_U16 && a.depth_scale) ? a.depth_scale[sD.im] : 1.f;
+      const size_t im_base = (size_t)sD.im * a.pp.H * (size_t)a.pp.W;
+      const size_t out_base = (size_t)sW.pair * a.pp.H * (size_t)a.pp.W;
+      for (int i = tid; i < npx; i += nthr) {
+        const unsigned zb = zt[i];
+        if (zb == BOP_INF_BITS_F32) continue;
+        const int r = i / w, x = cx0 + (i - r * w) - a.mx, y = cy0 + r - a.my;
+        n_all += 1;
+        bb[0] = min(bb[0], x); bb[1] = min(bb[1], y); bb[2] = max(bb[2], x); bb[3] = max(bb[3], y);
+        if (x < 0 || y < 0 || x >= a.pp.W || y >= a.pp.H) continue;
+        const size_t off = (size_t)y * a.pp.W + x;
+        float dt;
+        if (a.pp.depth_dtype == BOP_DEPTH_F32) dt = __ldg((const float*)a.depth_test + im_base + off);
+        else dt = __fmul_rn((float)__ldg((const unsigned short*)a.depth_test + im_base + off), scale);
+        const double X = __ddiv_rn(__dsub_rn((double)x, sD.kcx), sD.kfx);
+        const double Y = __ddiv_rn(__dsub_rn((double)y, sD.kcy), sD.kfy);
+        const double Dt = dist_of(X, Y, dt), Dg = dist_of(X, Y, __uint_as_float(zb));
+        if (Dt > 0.0) n_valid += 1;
+        const bool vis = (__fsub_rn((float)Dg, (float)Dt) <= a.pp.delta_f32) || Dt == 0.0;
+        if (a.mask_full) a.mask_full[out_base + off] = 255;
+        if (vis) {
+          n_vis += 1;
+          bb[4] = min(bb[4], x); bb[5] = min(bb[5], y); bb[6] = max(bb[6], x); bb[7] = max(bb[7], y);
+          if (a.mask_visib) a.mask_visib[out_base + off] = 255;
+        }
+      }
+      const int cnt[3] = {warp_sum(n_all), warp_sum(n_valid), warp_sum(n_vis)};
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        bb[k] = (k & 2) ? __reduce_max_sync(BOP_FULL_MASK, bb[k]) : __reduce_min_sync(BOP_FULL_MASK, bb[k]);
+      if (lane == 0) {
+        unsigned long long* c = a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS);
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          if (cnt[k]) atomicAdd(c + k, (unsigned long long)cnt[k]);
+        int* o = a.mask_bbox + (size_t)sW.pair * 8;
+        if (cnt[0]) { atomicMin(o + 0, bb[0]); atomicMin(o + 1, bb[1]); atomicMax(o + 2, bb[2]); atomicMax(o + 3, bb[3]); }
+        if (cnt[2]) { atomicMin(o + 4, bb[4]); atomicMin(o + 5, bb[5]); atomicMax(o + 6, bb[6]); atomicMax(o + 7, bb[7]); }
       }
       continue;
     }
@@ -656,6 +710,28 @@ __global__ void mask_finalize_kernel(const unsigned long long* __restrict__ coun
       }
       cou_bb[i] = 1.0 - iou;
     }
+  }
+}
+
+// Record fields of scripts/calc_gt_info.py:146-175: px_count_all / valid / visib, visib_fract,
+// bbox_obj and bbox_visib as (x, y, w, h) = misc.calc_2d_bbox; both boxes are [-1,-1,-1,-1]
+// unless px_count_visib > 0 (:158-169).
+__global__ void gt_info_finalize_kernel(const unsigned long long* __restrict__ counts,
+                                        const int* __restrict__ bbox, int n,
+                                        long long* __restrict__ counts_out,
+                                        double* __restrict__ visib_fract, int* __restrict__ bbox_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long* c = counts + (size_t)i * (2 + BOP_MAX_TAUS);
+  for (int k = 0; k < 3; ++k) counts_out[(size_t)i * 3 + k] = (long long)c[k];
+  visib_fract[i] = c[0] > 0 ? (double)c[2] / (double)c[0] : 0.0;
+  const int* b = bbox + (size_t)i * 8;
+  for (int p = 0; p < 2; ++p) {
+    const bool has = c[2] > 0;
+    bbox_out[i * 8 + 4 * p + 0] = has ? b[4 * p + 0] : -1;
+    bbox_out[i * 8 + 4 * p + 1] = has ? b[4 * p + 1] : -1;
+    bbox_out[i * 8 + 4 * p + 2] = has ? b[4 * p + 2] - b[4 * p + 0] : -1;
+    bbox_out[i * 8 + 4 * p + 3] = has ? b[4 * p + 3] - b[4 * p + 1] : -1;
   }
 }
 
@@ -849,7 +925,7 @@ int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
   const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
   const int grid = sm_count() * g_tune.ctas_per_sm;
-  const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : (MODE == MODE_MASK ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
+  const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : ((MODE == MODE_MASK || MODE == MODE_GTINFO) ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
   const bool dense = g_tune.threads * g_tune.ctas_per_sm > 512;
   if (dense)
     BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -870,7 +946,7 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
                 const double* pose_b, const int32_t* im_idx, const double* K,
                 const double* diameters, int cam_mode, int n,
                 int n_poses, int H, int W, int gate, unsigned char* ws, const WsLayout& L,
-                cudaStream_t s) {
+                cudaStream_t s, int cx_off = 0, int cy_off = 0) {
   // counters + counts + tl sums are contiguous at the head of the workspace.
   BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
   int4* bbox = (int4*)(ws + L.bbox);
@@ -878,12 +954,12 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
   bop_prof_begin(BOP_PROF_VSD_PLAN, s);
   project_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
                                                           diameters, cam_mode, n, n_poses, H, W, gate,
-                                                          L.pv_stride, (PVert*)(ws + L.pv), bbox);
+                                                          L.pv_stride, (PVert*)(ws + L.pv), bbox, cx_off, cy_off);
   BOP_LAUNCH_CHECK();
   plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
                                               n, n_poses, H, W, g_tune.tile_px, bbox,
                                               (PairDesc*)(ws + L.desc), (WorkItem*)(ws + L.work),
-                                              (PlanCounters*)(ws + L.ctr), L.max_items);
+                                              (PlanCounters*)(ws + L.ctr), L.max_items, cx_off, cy_off);
   bop_prof_end(BOP_PROF_VSD_PLAN, s);
   BOP_LAUNCH_CHECK();
   return 0;
@@ -967,6 +1043,10 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
     a.tile_px = g_tune.tile_px;
     a.small_tri_px = g_tune.small_tri_px;
     a.pp = pp;
+    a.canvas_w = pp.W;
+    a.mx = a.my = 0;
+    a.mask_full = a.mask_visib = nullptr;
+    a.mask_bbox = nullptr;
     int rc = prm->cost_type == BOP_COST_TLINEAR ? launch_fused<MODE_TLINEAR>(a, pp.W, s)
                                                 : launch_fused<MODE_STEP>(a, pp.W, s);
     if (rc) return rc;
@@ -1011,6 +1091,7 @@ extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* 
     a.small_tri_px = g_tune.small_tri_px;
     a.pp.H = height;
     a.pp.W = width;
+    a.canvas_w = width;
     a.pp.n_taus = 1;
     if (int rc = launch_fused<MODE_RENDER>(a, width, s)) return rc;
   }
@@ -1104,6 +1185,7 @@ extern "C" int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* 
     a.small_tri_px = g_tune.small_tri_px;
     a.pp.H = height;
     a.pp.W = width;
+    a.canvas_w = width;
     a.pp.n_taus = 1;
     if (int rc = launch_fused<MODE_MASK>(a, width, s)) return rc;
     mask_finalize_kernel<<<(nc + 127) / 128, 128, 0, s>>>(
@@ -1180,5 +1262,78 @@ extern "C" int bop_mask_overlap_from_depth_dev(const float* depth_est, const flo
   mask_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, mbox, n_pairs, cus_out, cou_bb_out,
                                                              (long long*)counts_out, bbox_out);
   BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+// scripts/calc_gt_info.py:113-175 and scripts/calc_gt_masks.py:110-133 for a batch of GT
+// instances.  margin_x / margin_y: the reference renders calc_gt_info on a 3x canvas (margins =
+// image size, :76-79,121-128) so that px_count_all and bbox_obj include the part of the object
+// outside the image; calc_gt_masks uses no margin.
+extern "C" size_t bop_gt_info_workspace_bytes(int n, int height, int width, int margin_x,
+                                              int margin_y, int max_pts) {
+  return ws_layout(n, height + 2 * margin_y, width + 2 * margin_x, 1, max_pts).total;
+}
+
+extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                               const double* pose_gt, const void* depth_test,
+                               const float* depth_scale, const int32_t* im_idx, const double* K,
+                               int n, int max_pts, int height, int width, int depth_dtype,
+                               double delta, int margin_x, int margin_y, int64_t* counts_out,
+                               double* visib_fract_out, int32_t* bbox_out,
+                               unsigned char* mask_out, unsigned char* mask_visib_out,
+                               void* workspace, size_t workspace_bytes, void* stream) {
+  if (n <= 0) return 0;
+  BOP_REQUIRE(models && obj_idx && pose_gt && depth_test && im_idx && K && counts_out &&
+              visib_fract_out && bbox_out, "bop_gt_info_dev: null pointer");
+  BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_gt_info_dev: bad image size");
+  BOP_REQUIRE(margin_x >= 0 && margin_y >= 0, "bop_gt_info_dev: negative margin");
+  BOP_REQUIRE(depth_dtype == BOP_DEPTH_F32 || depth_dtype == BOP_DEPTH_U16, "bop_gt_info_dev: unknown depth dtype");
+  const int cw = width + 2 * margin_x, ch = height + 2 * margin_y;
+  BOP_REQUIRE(((cw + 3) & ~3) <= g_tune.tile_px, "bop_gt_info_dev: canvas wider than the z-tile");
+  const WsLayout L = ws_layout(n, ch, cw, 1, max_pts);
+  BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_gt_info_dev: workspace too small");
+  BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_gt_info_dev: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned char* ws = (unsigned char*)workspace;
+  if (mask_out) BOP_CUDA(cudaMemsetAsync(mask_out, 0, (size_t)n * height * width, s));
+  if (mask_visib_out) BOP_CUDA(cudaMemsetAsync(mask_visib_out, 0, (size_t)n * height * width, s));
+  for (int c0 = 0; c0 < n; c0 += L.chunk) {
+    const int nc = n - c0 < L.chunk ? n - c0 : L.chunk;
+    if (int rc = launch_plan(models, obj_idx + c0, pose_gt + 12 * (size_t)c0, pose_gt + 12 * (size_t)c0,
+                             im_idx + c0, K, nullptr, 0, nc, 1, ch, cw, 0, ws, L, s, margin_x, margin_y))
+      return rc;
+    fill_i32_pattern_kernel<<<(nc * 8 + 255) / 256, 256, 0, s>>>((int*)(ws + L.mbox), nc);
+    BOP_LAUNCH_CHECK();
+    FusedArgs a;
+    memset(&a, 0, sizeof(a));
+    a.models = models;
+    a.desc = (const PairDesc*)(ws + L.desc);
+    a.work = (const WorkItem*)(ws + L.work);
+    a.ctr = (PlanCounters*)(ws + L.ctr);
+    a.pv = (const PVert*)(ws + L.pv);
+    a.pv_stride = L.pv_stride;
+    a.depth_test = depth_test;
+    a.depth_scale = depth_scale;
+    a.counts = (unsigned long long*)(ws + L.counts);
+    a.mask_bbox = (int*)(ws + L.mbox);
+    a.mask_full = mask_out ? mask_out + (size_t)c0 * height * width : nullptr;
+    a.mask_visib = mask_visib_out ? mask_visib_out + (size_t)c0 * height * width : nullptr;
+    a.max_items = L.max_items;
+    a.tile_px = g_tune.tile_px;
+    a.small_tri_px = g_tune.small_tri_px;
+    a.pp.H = height;
+    a.pp.W = width;
+    a.pp.n_taus = 1;
+    a.pp.delta_f32 = (float)delta;
+    a.pp.depth_dtype = depth_dtype;
+    a.canvas_w = cw;
+    a.mx = margin_x;
+    a.my = margin_y;
+    if (int rc = launch_fused<MODE_GTINFO>(a, width, s)) return rc;
+    gt_info_finalize_kernel<<<(nc + 127) / 128, 128, 0, s>>>(
+        a.counts, a.mask_bbox, nc, (long long*)counts_out + (size_t)c0 * 3, visib_fract_out + c0,
+        bbox_out + (size_t)c0 * 8);
+    BOP_LAUNCH_CHECK();
+  }
   return 0;
 }

@@ -48,6 +48,48 @@ _TLESS_SIZE = {
 _HB_SIZE = {'pbr': (640, 480), 'primesense': (640, 480), 'kinect': (1920, 1080)}
 
 
+def _scene_ids(name, split, split_type):
+  """Scene ids per dataset / split (dataset_params.py:336-584); `pbr` splits have 50 scenes."""
+  if split_type == 'pbr':
+    return list(range(50))
+  by_split = lambda d: d[split]
+  if name == 'lm':
+    return _R(1, 16)
+  if name == 'lmo':
+    return by_split({'train': [1, 5, 6, 8, 9, 10, 11, 12], 'test': [2]})
+  if name == 'tless':
+    if split == 'train':
+      return [1] if split_type == 'synthetless' else _R(1, 31)
+    return _R(1, 21)
+  if name == 'tudl':
+    return _R(1, 4)
+  if name == 'tyol':
+    return _R(1, 22)
+  if name == 'ruapc':
+    return _R(1, 15)
+  if name == 'icmi':
+    return _R(1, 7)
+  if name == 'icbin':
+    return by_split({'train': _R(1, 3), 'test': _R(1, 4)})
+  if name == 'itodd':
+    return by_split({'train': [], 'val': [1], 'test': [1]})
+  if name == 'hbs':
+    return by_split({'train': [], 'val': [3, 5, 13], 'test': [3, 5, 13]})
+  if name == 'hb':
+    return by_split({'train': [], 'val': _R(1, 14), 'test': _R(1, 14)})
+  if name == 'ycbv':
+    if split == 'train':
+      return {'real': _R(0, 48) + _R(60, 92), 'synt': _R(0, 80)}[split_type]
+    return _R(48, 60)
+  if name == 'hope':
+    return by_split({'train': [], 'val': _R(1, 11), 'test': _R(1, 41)})
+  if name == 'kit':
+    return _R(1, 121)
+  if name in ('bigbird', 'gist', 'data2_source'):
+    return _R(1, 111)
+  raise ValueError('Unknown BOP dataset ({}).'.format(name))
+
+
 def get_model_params(datasets_path, dataset_name, model_type=None):
   """Object-model parameters of a dataset (dataset_params.py:66-165)."""
   if dataset_name not in _MODELS:
@@ -68,7 +110,10 @@ def get_model_params(datasets_path, dataset_name, model_type=None):
 
 
 def get_split_params(datasets_path, dataset_name, split, split_type=None):
-  """Split parameters (paths, image size) of a dataset (dataset_params.py:315-646)."""
+  """Split parameters (paths, image size) of a dataset (dataset_params.py:315-646).  As in the
+  reference, 'name', 'split_type' and 'base_path' echo the arguments (so 'hbs' keeps its own
+  base folder for the targets file) while the split folder uses the resolved names."""
+  name_arg, type_arg = dataset_name, split_type
   depth_ext = '.tif' if (dataset_name == 'itodd' and split_type != 'pbr') else '.png'
   if dataset_name == 'tless':
     if split_type is None:
@@ -86,14 +131,17 @@ def get_split_params(datasets_path, dataset_name, split, split_type=None):
       split_type = 'real'
   else:
     raise ValueError('Unknown BOP dataset ({}).'.format(dataset_name))
-  base_path = join(datasets_path, dataset_name)
-  split_path = join(base_path, split)
+  ids = _scene_ids(dataset_name, split, split_type)
+  if dataset_name == 'hbs':
+    dataset_name = 'hb'     # both versions share one directory
+  base_path = join(datasets_path, name_arg)
+  split_path = join(datasets_path, dataset_name, split)
   if split_type is not None:
     split_path += '_' + split_type
   scene = join(split_path, '{scene_id:06d}')
   return {
-    'name': dataset_name, 'split': split, 'split_type': split_type,
-    'base_path': base_path, 'split_path': split_path, 'im_size': im_size,
+    'name': name_arg, 'split': split, 'split_type': type_arg,
+    'base_path': base_path, 'split_path': split_path, 'im_size': im_size, 'scene_ids': ids,
     'scene_camera_tpath': join(scene, 'scene_camera.json'),
     'scene_gt_tpath': join(scene, 'scene_gt.json'),
     'scene_gt_info_tpath': join(scene, 'scene_gt_info.json'),

@@ -84,3 +84,9 @@ def get_error_signature(error_type, n_top, **kwargs):
     tau_str = 'inf' if tau == float('inf') else '{:.3f}'.format(tau)
     sign += '_delta={:.3f}_tau={}'.format(kwargs['vsd_delta'], tau_str)
   return sign
+
+
+def get_score_signature(correct_th, visib_gt_min):
+  """File-name signature of a score setting (contract of misc.py:353-361)."""
+  return 'th=' + '-'.join('{:.3f}'.format(t) for t in correct_th) + \
+    '_min-visib={:.3f}'.format(visib_gt_min)

@@ -163,6 +163,7 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
   rng = np.random.default_rng(seed)
   ds = os.path.join(root, 'datasets', dataset)
   os.makedirs(os.path.join(ds, 'models_eval'), exist_ok=True)
+  os.makedirs(os.path.join(ds, 'models'), exist_ok=True)     # calc_gt_info / calc_gt_masks use these
   os.makedirs(os.path.join(root, 'results'), exist_ok=True)
   models, info = {}, {}
   for k, oid in enumerate(obj_ids):
@@ -170,6 +171,7 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
     pts, faces = make_mesh(mesh_res[0], mesh_res[1], diameter, seed=seed * 100 + oid)
     models[oid] = (pts, faces)
     inout.save_ply(os.path.join(ds, 'models_eval', 'obj_%06d.ply' % oid), pts, faces)
+    inout.save_ply(os.path.join(ds, 'models', 'obj_%06d.ply' % oid), pts, faces)
     mi = {'diameter': diameter, 'min_x': float(pts[:, 0].min()), 'min_y': float(pts[:, 1].min()),
           'min_z': float(pts[:, 2].min()), 'size_x': float(np.ptp(pts[:, 0])),
           'size_y': float(np.ptp(pts[:, 1])), 'size_z': float(np.ptp(pts[:, 2]))}
@@ -178,8 +180,9 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
     if k % 4 == 3:
       mi['symmetries_continuous'] = [{'axis': [0, 0, 1], 'offset': [0, 0, 0]}]
     info[str(oid)] = mi
-  with open(os.path.join(ds, 'models_eval', 'models_info.json'), 'w') as f:
-    json.dump(info, f)
+  for folder in ('models_eval', 'models'):
+    with open(os.path.join(ds, folder, 'models_info.json'), 'w') as f:
+      json.dump(info, f)
   targets, lines = [], ['scene_id,im_id,obj_id,score,R,t,time']
   fmt = lambda a: ' '.join(repr(float(x)) for x in np.asarray(a).reshape(-1))
   for si, scene_id in enumerate(scene_ids):

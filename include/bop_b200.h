@@ -209,6 +209,27 @@ int bop_mask_overlap_from_depth_dev(const float* depth_est, const float* depth_g
                                     int64_t* counts_out, int32_t* bbox_out, void* workspace,
                                     size_t workspace_bytes, void* stream);
 
+/* ---- GT info / GT masks -----------------------------------------------------------
+ * The per-instance body of scripts/calc_gt_info.py:113-175 and scripts/calc_gt_masks.py:110-133:
+ * render the GT pose, visibility.estimate_visib_mask_gt (visibility.py:45-57, 'bop19') against
+ * the sensor depth, pixel counts and boxes.  margin_x/margin_y: calc_gt_info renders on a 3x
+ * canvas (margins = image width/height, calc_gt_info.py:76-79) so px_count_all / bbox_obj cover
+ * the part of the object outside the image; calc_gt_masks uses margins 0.
+ * depth_test [n_im][H][W] (depth_dtype), depth_scale [n_im] or NULL, im_idx [n], K [n_im][9].
+ * counts_out [n][3] int64 = px_count_all, px_count_valid, px_count_visib; visib_fract_out [n];
+ * bbox_out [n][8] int32 = bbox_obj (x,y,w,h) then bbox_visib, all -1 unless px_count_visib > 0;
+ * mask_out / mask_visib_out (optional) [n][H][W] uint8, 255 inside (the PNG payloads).
+ * workspace: bop_gt_info_workspace_bytes(...) bytes, 256-byte aligned.                     */
+size_t bop_gt_info_workspace_bytes(int n, int height, int width, int margin_x, int margin_y,
+                                   int max_pts);
+int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_idx, const double* pose_gt,
+                    const void* depth_test, const float* depth_scale, const int32_t* im_idx,
+                    const double* K, int n, int max_pts, int height, int width, int depth_dtype,
+                    double delta, int margin_x, int margin_y, int64_t* counts_out,
+                    double* visib_fract_out, int32_t* bbox_out, unsigned char* mask_out,
+                    unsigned char* mask_visib_out, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
 /* depth_test may also be a pointer into PINNED HOST memory (cudaHostAlloc / cudaHostRegister;
  * with unified addressing the host pointer is valid on the device): the fused kernel then pulls
  * only the depth samples it needs (the pixels under the two rendered silhouettes) across PCIe

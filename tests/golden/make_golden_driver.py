@@ -32,8 +32,13 @@ sys.path.insert(0, ROOT)
 from bop_toolkit_b200 import synth            # noqa: E402
 from oracle import renderer_oracle            # noqa: E402
 
-DATASET_KW = dict(dataset='lmo', split='test', scene_ids=(2, 3), n_images=3, obj_ids=(1, 5, 6, 8, 9, 10, 11, 12),
+DATASET_KW = dict(dataset='lm', split='test', scene_ids=(2, 3), n_images=3, obj_ids=tuple(range(1, 16)),
                   objs_per_image=4, ests_per_target=3, seed=7)
+# (error type, n_top) whose error files are also scored; score settings = extra flags
+SCORE_RUNS = [('vsd', 1), ('vsd', -1), ('mssd', 1), ('mssd', 0), ('mspd', -1), ('ad', 1), ('rete', 1), ('cus', 1)]
+SCORE_SETTINGS = [[], ['--visib_gt_min=0.3'], ['--correct_th_vsd=0.15', '--correct_th_mssd=0.1',
+                                               '--correct_th_mspd=5', '--correct_th_ad=0.05',
+                                               '--correct_th_rete=10,3', '--correct_th_cus=0.3']]
 RUNS = [('vsd', 1), ('vsd', -1), ('mssd', 1), ('mssd', 0), ('mspd', 1), ('mspd', -1), ('ad', 1),
         ('add', 1), ('adi', 1), ('proj', 1), ('cus', 1), ('rete', 1), ('re', 1), ('te', 0)]
 
@@ -47,7 +52,7 @@ def dataset_checksum(info):
   """sha256 over the decoded depth images, the results CSV and the targets (byte-exact inputs)."""
   import cv2
   h = hashlib.sha256()
-  base = os.path.join(info['datasets_path'], 'lmo')
+  base = os.path.join(info['datasets_path'], DATASET_KW['dataset'])
   for scene_id in info['scene_ids']:
     ddir = os.path.join(base, 'test', '%06d' % scene_id, 'depth')
     for name in sorted(os.listdir(ddir)):
@@ -82,36 +87,120 @@ def install_reference_shim():
     RefOracleRenderer(w, h, mode, subpixel_bits=8)
 
 
+def run_script(script, argv):
+  old = sys.argv
+  sys.argv = [script] + argv
+  try:
+    runpy.run_path(script, run_name='__main__')
+  finally:
+    sys.argv = old
+
+
+def collect(root):
+  out = {}
+  for dirpath, _, names in os.walk(root):
+    for name in names:
+      full = os.path.join(dirpath, name)
+      out[os.path.relpath(full, root)] = open(full).read()
+  return out
+
+
+def patch_dataset_params(info):
+  """calc_gt_info.py / calc_gt_masks.py have no flags (dataset and paths are edited in their `p`
+  dict): route their dataset_params calls to the synthetic dataset instead."""
+  from bop_toolkit_lib import dataset_params as ref_dp
+  orig_split, orig_model = ref_dp.get_split_params, ref_dp.get_model_params
+  ds, split = DATASET_KW['dataset'], DATASET_KW['split']
+  ref_dp.get_split_params = lambda path, name, sp, st=None: orig_split(info['datasets_path'], ds, split, None)
+  ref_dp.get_model_params = lambda path, name, mt=None: orig_model(info['datasets_path'], ds, mt)
+  return lambda: (setattr(ref_dp, 'get_split_params', orig_split), setattr(ref_dp, 'get_model_params', orig_model))
+
+
 def main():
+  import cv2
   renderer_oracle.build()
   tmp = tempfile.mkdtemp(prefix='bop_golden_')
   try:
     info = synth.write_bop_dataset(tmp, oracle_render_fn, **DATASET_KW)
     install_reference_shim()
-    script = '/root/reference/scripts/eval_calc_errors.py'
+    sys.modules['imageio'].imwrite = lambda path, im, **kw: cv2.imwrite(path, im)
+    ds_dir = os.path.join(info['datasets_path'], DATASET_KW['dataset'])
+    split_dir = os.path.join(ds_dir, DATASET_KW['split'])
+
+    # ---- scene_gt_info.json by the reference's calc_gt_info.py ---------------------------
+    undo = patch_dataset_params(info)
+    run_script('/root/reference/scripts/calc_gt_info.py', [])
+    gt_info = {str(s): open(os.path.join(split_dir, '%06d' % s, 'scene_gt_info.json')).read()
+               for s in info['scene_ids']}
+    # ---- masks by the reference's calc_gt_masks.py (it only visits scene 0: link it) --------
+    first = info['scene_ids'][0]
+    os.symlink(os.path.join(split_dir, '%06d' % first), os.path.join(split_dir, '000000'))
+    run_script('/root/reference/scripts/calc_gt_masks.py', [])
+    os.unlink(os.path.join(split_dir, '000000'))
+    undo()
+    masks = {}
+    for kind in ('mask', 'mask_visib'):
+      mdir = os.path.join(split_dir, '%06d' % first, kind)
+      for name in sorted(os.listdir(mdir)):
+        m = cv2.imread(os.path.join(mdir, name), cv2.IMREAD_UNCHANGED)
+        assert m.dtype == np.uint8 and set(np.unique(m)) <= {0, 255}
+        masks['%s/%s' % (kind, name)] = np.packbits(m > 0)
+    np.savez_compressed(os.path.join(HERE, 'gt_masks_golden.npz'), scene_id=first, **masks)
+
+    # ---- error files by the reference's eval_calc_errors.py ------------------------------
     files = {}
+    eval_paths = {}
     for error_type, n_top in RUNS:
       eval_path = os.path.join(tmp, 'eval_%s_%d' % (error_type, n_top))
-      argv = [script, '--error_type=' + error_type, '--n_top=%d' % n_top,
-              '--result_filenames=' + info['result_filename'],
-              '--results_path=' + info['results_path'], '--eval_path=' + eval_path,
-              '--datasets_path=' + info['datasets_path'], '--renderer_type=vispy']
-      old = sys.argv
-      sys.argv = argv
-      try:
-        runpy.run_path(script, run_name='__main__')
-      finally:
-        sys.argv = old
-      for dirpath, _, names in os.walk(eval_path):
-        for name in names:
-          full = os.path.join(dirpath, name)
-          rel = os.path.relpath(full, eval_path)
-          files['%s|%d|%s' % (error_type, n_top, rel)] = open(full).read()
-    out = {'dataset_kw': {k: (list(v) if isinstance(v, tuple) else v) for k, v in DATASET_KW.items()},
-           'dataset_sha256': dataset_checksum(info), 'runs': [list(r) for r in RUNS], 'files': files}
+      eval_paths[(error_type, n_top)] = eval_path
+      run_script('/root/reference/scripts/eval_calc_errors.py', [
+        '--error_type=' + error_type, '--n_top=%d' % n_top,
+        '--result_filenames=' + info['result_filename'], '--results_path=' + info['results_path'],
+        '--eval_path=' + eval_path, '--datasets_path=' + info['datasets_path'],
+        '--renderer_type=vispy'])
+      for rel, text in collect(eval_path).items():
+        files['%s|%d|%s' % (error_type, n_top, rel)] = text
+
+    # ---- scores / matches by the reference's eval_calc_scores.py -------------------------
+    scores = {}
+    for error_type, n_top in SCORE_RUNS:
+      eval_path = eval_paths[(error_type, n_top)]
+      result_dir = os.path.join(eval_path, os.listdir(eval_path)[0])
+      dirs = sorted(os.listdir(result_dir))
+      if error_type == 'vsd':
+        dirs = [d for d in dirs if d.endswith('tau=0.200') or d.endswith('tau=0.500')]
+      for si, extra in enumerate(SCORE_SETTINGS):
+        before = set(collect(eval_path))
+        run_script('/root/reference/scripts/eval_calc_scores.py', [
+          '--error_dir_paths=' + ','.join(os.path.join(os.path.basename(result_dir), d) for d in dirs),
+          '--eval_path=' + eval_path, '--datasets_path=' + info['datasets_path']] + extra)
+        after = collect(eval_path)
+        for rel in sorted(set(after) - before):
+          scores['%s|%d|%d|%s' % (error_type, n_top, si, rel)] = after[rel]
+    # ---- the reference's dataset tables (fields the drivers read) ------------------------
+    from bop_toolkit_lib import dataset_params as ref_dp
+    tables = {}
+    for ds in ['lm', 'lmo', 'tless', 'tudl', 'tyol', 'ruapc', 'icmi', 'icbin', 'itodd', 'hbs', 'hb', 'ycbv', 'hope']:
+      tables['model|%s' % ds] = ref_dp.get_model_params('/d', ds, 'eval')
+      for split in ['train', 'val', 'test']:
+        for st in [None, 'pbr', 'primesense', 'kinect', 'real', 'synt', 'render']:
+          try:
+            r = ref_dp.get_split_params('/d', ds, split, st)
+          except Exception:
+            continue
+          tables['split|%s|%s|%s' % (ds, split, st)] = {
+            k: (list(r[k]) if isinstance(r[k], tuple) else r[k]) for k in r if k in
+            ('name', 'split', 'split_type', 'base_path', 'split_path', 'im_size', 'scene_ids',
+             'scene_camera_tpath', 'scene_gt_tpath', 'scene_gt_info_tpath', 'depth_tpath',
+             'mask_tpath', 'mask_visib_tpath')}
+    out = {'tables': tables, 'dataset_kw': {k: (list(v) if isinstance(v, tuple) else v) for k, v in DATASET_KW.items()},
+           'dataset_sha256': dataset_checksum(info), 'runs': [list(r) for r in RUNS], 'files': files,
+           'gt_info': gt_info, 'score_runs': [list(r) for r in SCORE_RUNS],
+           'score_settings': SCORE_SETTINGS, 'scores': scores}
     with open(os.path.join(HERE, 'driver_golden.json'), 'w') as f:
       json.dump(out, f, indent=0, sort_keys=True)
-    print('wrote %d files, dataset sha256 %s' % (len(files), out['dataset_sha256']))
+    print('wrote %d error files, %d score files, %d masks, dataset sha256 %s'
+          % (len(files), len(scores), len(masks), out['dataset_sha256']))
   finally:
     shutil.rmtree(tmp, ignore_errors=True)
 

@@ -27,7 +27,7 @@ def _oracle_render_fn(pts, faces, R, t, K):
 def _checksum(info):
   import cv2
   h = hashlib.sha256()
-  base = os.path.join(info['datasets_path'], 'lmo')
+  base = os.path.join(info['datasets_path'], 'lm')
   for scene_id in info['scene_ids']:
     ddir = os.path.join(base, 'test', '%06d' % scene_id, 'depth')
     for name in sorted(os.listdir(ddir)):
@@ -93,7 +93,7 @@ def test_flatten_matches_reference_records(dataset, driver_golden, n_top):
   gold = _golden_files(driver_golden, et, n_top)
   assert gold
   p = _params(dataset, et, n_top, '/nonexistent')
-  dp = dataset_params.get_split_params(p['datasets_path'], 'lmo', 'test')
+  dp = dataset_params.get_split_params(p['datasets_path'], 'lm', 'test')
   targets = inout.load_json(os.path.join(dp['base_path'], p['targets_filename']))
   torg, eorg = {}, {}
   for t in targets:
@@ -103,7 +103,7 @@ def test_flatten_matches_reference_records(dataset, driver_golden, n_top):
   for scene_id, st in torg.items():
     gt = inout.load_scene_gt(dp['scene_gt_tpath'].format(scene_id=scene_id))
     sp = ece.flatten_scene(p, scene_id, st, eorg.get(scene_id, {}), gt)
-    ref = _load_text(gold['synth_lmo-test/error=%s_ntop=%d/errors_%06d.json' % (et, n_top, scene_id)])
+    ref = _load_text(gold['synth_lm-test/error=%s_ntop=%d/errors_%06d.json' % (et, n_top, scene_id)])
     assert len(ref) == len(sp.records)
     for a, b in zip(sp.records, ref):
       assert (a['im_id'], a['obj_id'], a['est_id'], a['score']) == (b['im_id'], b['obj_id'], b['est_id'], b['score'])
