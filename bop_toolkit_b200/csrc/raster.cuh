@@ -62,10 +62,26 @@ __device__ __forceinline__ PVert project_vertex(const PoseCamF& P, const float4 
 struct TriSetup {
   int A[3], B[3], C[3];   // C already carries the top-left bias
   int bias[3];            // 0 or 1: added back to get the true edge value for interpolation
-  float iz[3];
-  float inv_area;         // 1 / (E_0 + E_1 + E_2) (true values) = 1 / |2 * area|
+  // 1/Z is affine in screen space: izp(x, y) = iz0 + pa * (256 x - vx) + pb * (256 y - vy), with
+  // (vx, vy) the snapped sub-pixel position of vertex 0.  The expression depends only on the
+  // triangle and the pixel -- not on the tile, band or path that draws it -- so a pixel's depth
+  // is the same bit pattern wherever it is rasterised.
+  float pa, pb, iz0;
+  int vx, vy;
   int bx0, by0, bx1, by1; // candidate pixel rectangle (inclusive), already clipped
 };
+
+// Depth plane of a triangle from its (oriented) edge steps.  A[k] = dE_k/dx, B[k] = dE_k/dy per
+// PIXEL (256 sub-pixel units); sum_k A[k] = sum_k B[k] = 0, so the gradient only needs the
+// differences of 1/Z, which are exact-ish in float (no cancellation against 1/Z itself).
+__device__ __forceinline__ void tri_plane(float A1, float A2, float B1, float B2, float area,
+                                          const PVert& v0, const PVert& v1, const PVert& v2,
+                                          float& pa, float& pb) {
+  const float d1 = __fsub_rn(v1.iz, v0.iz), d2 = __fsub_rn(v2.iz, v0.iz);
+  const float k = __frcp_rn(area) * (1.0f / (float)kSubOne);
+  pa = __fmul_rn(__fmaf_rn(A1, d1, __fmul_rn(A2, d2)), k);
+  pb = __fmul_rn(__fmaf_rn(B1, d1, __fmul_rn(B2, d2)), k);
+}
 
 // Returns the number of candidate pixels (0: nothing to draw; < 0: -count, the triangle is too
 // large for 32-bit edge functions and must take the 64-bit path).
@@ -102,8 +118,9 @@ __device__ __forceinline__ int tri_setup(const PVert& v0, const PVert& v1, const
     T.B[k] = dx * kSubOne;
     T.C[k] = e0 - (1 - own);
   }
-  T.iz[0] = v0.iz; T.iz[1] = v1.iz; T.iz[2] = v2.iz;
-  T.inv_area = __frcp_rn((float)(s * area2));
+  tri_plane((float)T.A[1], (float)T.A[2], (float)T.B[1], (float)T.B[2], (float)(s * area2), v0, v1, v2,
+            T.pa, T.pb);
+  T.iz0 = v0.iz; T.vx = v0.x; T.vy = v0.y;
   return n;
 }
 
@@ -115,35 +132,41 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return r;
 }
 
-// Depth at a covered sample from the three (true) edge values: 1/Z is affine in screen space.
-__device__ __forceinline__ float tri_depth(float w0, float w1, float w2, const float* iz, float inv_area) {
-  const float izp = __fmaf_rn(w0, iz[0], __fmaf_rn(w1, iz[1], __fmul_rn(w2, iz[2]))) * inv_area;
-  return rcp_fast(izp);
+// Depth at pixel (x, y) of a triangle's plane (see TriSetup).  256 x - vx is an exact float.
+__device__ __forceinline__ float plane_row(float pb, float iz0, int y, int vy) {
+  return __fmaf_rn(pb, (float)((y << kSubBits) - vy), iz0);
+}
+__device__ __forceinline__ float plane_depth(float pa, float rowbase, float fdx) {
+  return rcp_fast(__fmaf_rn(pa, fdx, rowbase));
 }
 
+// z-test + merge.  The tile starts at +inf bits (0x7f800000): negative, NaN and +inf candidates
+// compare >= that as unsigned integers, so no range check is needed.
 __device__ __forceinline__ void z_merge(unsigned* __restrict__ p, float Z) {
-  if (Z > 0.f && Z < 3.0e38f) {
-    const unsigned zb = __float_as_uint(Z);
-    if (zb < *p) atomicMin(p, zb);
-  }
+  const unsigned zb = __float_as_uint(Z);
+  if (zb < *p) atomicMin(p, zb);
 }
 
-// Rasterises a small triangle (32-bit path) into the z-tile.  One thread.
+// Rasterises a small triangle (32-bit path) into the z-tile.  One thread; incremental edge
+// stepping; the depth plane is evaluated only at covered pixels (1 FFMA + 1 MUFU.RCP).
 __device__ __forceinline__ void tri_raster_small(const TriSetup& T, unsigned* __restrict__ z, int zx0,
                                                  int zy0, int zstride) {
   int r0 = T.C[0], r1 = T.C[1], r2 = T.C[2];
+  const float fdx0 = (float)((T.bx0 << kSubBits) - T.vx);
+  float fdy = (float)((T.by0 << kSubBits) - T.vy);
+  unsigned* zrow = z + (T.by0 - zy0) * zstride - zx0;
   for (int y = T.by0; y <= T.by1; ++y) {
     int e0 = r0, e1 = r1, e2 = r2;
-    unsigned* zrow = z + (y - zy0) * zstride - zx0;
+    const float rowbase = __fmaf_rn(T.pb, fdy, T.iz0);
+    float fdx = fdx0;
     for (int x = T.bx0; x <= T.bx1; ++x) {
-      if ((e0 | e1 | e2) >= 0) {
-        const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]),
-                    w2 = (float)(e2 + T.bias[2]);
-        z_merge(zrow + x, tri_depth(w0, w1, w2, T.iz, T.inv_area));
-      }
+      if ((e0 | e1 | e2) >= 0) z_merge(zrow + x, plane_depth(T.pa, rowbase, fdx));
       e0 += T.A[0]; e1 += T.A[1]; e2 += T.A[2];
+      fdx += (float)kSubOne;
     }
     r0 += T.B[0]; r1 += T.B[1]; r2 += T.B[2];
+    fdy += (float)kSubOne;
+    zrow += zstride;
   }
 }
 
@@ -157,16 +180,15 @@ __device__ __forceinline__ void tri_raster_warp(const TriSetup& T, int lane, uns
   const int sx = 1 << lw_log, sy = 32 >> lw_log;
   for (int y = T.by0 + ly; y <= T.by1; y += sy) {
     const int dy = y - T.by0;
+    const float rowbase = plane_row(T.pb, T.iz0, y, T.vy);
     for (int x = T.bx0 + lx; x <= T.bx1; x += sx) {
       const int dx = x - T.bx0;
       const int e0 = T.C[0] + T.A[0] * dx + T.B[0] * dy;
       const int e1 = T.C[1] + T.A[1] * dx + T.B[1] * dy;
       const int e2 = T.C[2] + T.A[2] * dx + T.B[2] * dy;
-      if ((e0 | e1 | e2) >= 0) {
-        const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]),
-                    w2 = (float)(e2 + T.bias[2]);
-        z_merge(z + (y - zy0) * zstride + (x - zx0), tri_depth(w0, w1, w2, T.iz, T.inv_area));
-      }
+      if ((e0 | e1 | e2) >= 0)
+        z_merge(z + (y - zy0) * zstride + (x - zx0),
+                plane_depth(T.pa, rowbase, (float)((x << kSubBits) - T.vx)));
     }
   }
 }
@@ -175,8 +197,8 @@ __device__ __forceinline__ void tri_raster_warp(const TriSetup& T, int lane, uns
 struct TriSetup64 {
   long long A[3], B[3], C[3];
   int bias[3];
-  float iz[3];
-  float inv_area;
+  float pa, pb, iz0;
+  int vx, vy;
   int bx0, by0, bx1, by1;
 };
 
@@ -199,8 +221,9 @@ __device__ __forceinline__ bool tri_setup64(const PVert& v0, const PVert& v1, co
     T.B[k] = dx * kSubOne;
     T.C[k] = e0 - (1 - own);
   }
-  T.iz[0] = v0.iz; T.iz[1] = v1.iz; T.iz[2] = v2.iz;
-  T.inv_area = __frcp_rn((float)(s * area2));
+  tri_plane((float)T.A[1], (float)T.A[2], (float)T.B[1], (float)T.B[2], (float)(s * area2), v0, v1, v2,
+            T.pa, T.pb);
+  T.iz0 = v0.iz; T.vx = v0.x; T.vy = v0.y;
   return true;
 }
 
@@ -215,9 +238,10 @@ __device__ __forceinline__ void tri_raster_large(const TriSetup64& T, int lane, 
     const long long e1 = T.C[1] + T.A[1] * xx + T.B[1] * yy;
     const long long e2 = T.C[2] + T.A[2] * xx + T.B[2] * yy;
     if ((e0 | e1 | e2) >= 0) {
-      // Same expression as the 32-bit path, so a pixel's depth does not depend on which path drew it.
-      const float w0 = (float)(e0 + T.bias[0]), w1 = (float)(e1 + T.bias[1]), w2 = (float)(e2 + T.bias[2]);
-      z_merge(z + (T.by0 + yy - zy0) * zstride + (T.bx0 + xx - zx0), tri_depth(w0, w1, w2, T.iz, T.inv_area));
+      // Same plane expression as the 32-bit paths.
+      const int x = T.bx0 + xx, y = T.by0 + yy;
+      z_merge(z + (y - zy0) * zstride + (x - zx0),
+              plane_depth(T.pa, plane_row(T.pb, T.iz0, y, T.vy), (float)((x << kSubBits) - T.vx)));
     }
   }
 }

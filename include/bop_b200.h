@@ -270,6 +270,7 @@ int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_est,
  * threads: CTA size; ctas_per_sm: persistent CTAs per SM.  0 keeps the current value. */
 int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_px);
 
+
 #ifdef __cplusplus
 }
 #endif
