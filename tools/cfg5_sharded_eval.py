@@ -1,0 +1,147 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4] in miniature: a synthetic YCB-V-layout test set evaluated end to end
+by the drop-in drivers, sharded over the GPUs of one node.
+
+  python tools/cfg5_sharded_eval.py --images 40                       (1 GPU)
+  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 \
+      tools/cfg5_sharded_eval.py --images 40                          (2 GPUs)
+
+Stages (all through the package's public drivers): write the dataset (depth rendered with the
+CUDA rasteriser), calc_gt_info -> scene_gt_info.json, eval_calc_errors for vsd / mssd / mspd with
+n_top = -1 (images sharded over the ranks, error records all-gathered over NCCL), then the BOP19
+average recalls with the in-process score stage.  With more than one rank, rank 0 also evaluates
+everything unsharded and checks that the gathered records are bit-identical.  Prints one JSON line.
+"""
+import argparse
+import json
+import os
+import shutil
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--images', type=int, default=20, help='images per scene (12 scenes)')
+  ap.add_argument('--root', default=None)
+  ap.add_argument('--keep', action='store_true')
+  args = ap.parse_args()
+
+  import torch
+  import torch.distributed as dist
+  from bop_toolkit_b200 import batch, calc_gt_info, eval_calc_errors as ece, eval_calc_scores as ecs, synth
+
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  torch.cuda.set_device(local)
+  if world > 1:
+    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+  root = args.root or os.path.join(tempfile.gettempdir(), 'bop_cfg5_%d' % args.images)
+  quiet = lambda s: None
+  t = {}
+
+  # ---- dataset (rank 0) ----------------------------------------------------------------
+  if rank == 0:
+    t0 = time.time()
+    if os.path.exists(root):
+      shutil.rmtree(root)
+    cache = {}
+
+    def render_fn(pts, faces, R, t_, K):
+      key = id(pts)
+      if key not in cache:
+        ms = batch.ModelSet('cuda:%d' % local)
+        ms.add(0, pts, faces)
+        cache[key] = ms
+      cam = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]])
+      return batch.render_batch(cache[key], 0, batch.pack_poses(R[None], t_[None]), cam,
+                                synth.IM_H, synth.IM_W)[0].cpu().numpy()
+    info = synth.write_bop_dataset(root, render_fn, dataset='ycbv', split='test',
+                                   scene_ids=tuple(range(48, 60)), n_images=args.images,
+                                   obj_ids=tuple(range(1, 22)), objs_per_image=5, ests_per_target=2,
+                                   seed=3, mesh_res=(50, 100))
+    t['write_dataset_s'] = time.time() - t0
+    t0 = time.time()
+    p = calc_gt_info.parse_args(['--dataset=ycbv', '--dataset_split=test',
+                                 '--datasets_path=' + info['datasets_path']])
+    p['device'] = 'cuda:%d' % local
+    calc_gt_info.calc_gt_info(p, log=quiet)
+    t['calc_gt_info_s'] = time.time() - t0
+    with open(os.path.join(root, 'info.json'), 'w') as f:
+      json.dump(info, f)
+  if world > 1:
+    dist.barrier()
+  info = json.load(open(os.path.join(root, 'info.json')))
+
+  # ---- errors: sharded over the ranks ------------------------------------------------------
+  def params(error_type):
+    return ece.parse_args(['--error_type=' + error_type, '--n_top=-1',
+                           '--result_filenames=' + info['result_filename'],
+                           '--results_path=' + info['results_path'], '--eval_path=' + info['eval_path'],
+                           '--datasets_path=' + info['datasets_path']])
+  records, n_pairs = {}, {}
+  for et in ('vsd', 'mssd', 'mspd'):
+    torch.cuda.synchronize()
+    t0 = time.time()
+    records[et] = ece.calc_errors(params(et), log=quiet, write=(rank == 0))['synth_ycbv-test']
+    torch.cuda.synchronize()
+    t['errors_%s_s' % et] = time.time() - t0
+    n_pairs[et] = sum(len(r['errors']) for recs in records[et].values() for r in recs)
+
+  out = None
+  if rank == 0:
+    # ---- sharded == unsharded (bit-identical records) ----------------------------------
+    identical = None
+    if world > 1:
+      identical = True
+      real_info = ece._dist_info
+      ece._dist_info = lambda: (0, 1)
+      try:
+        for et in ('vsd', 'mssd', 'mspd'):
+          single = ece.calc_errors(params(et), log=quiet, write=False)['synth_ycbv-test']
+          identical = identical and (single == records[et])
+      finally:
+        ece._dist_info = real_info
+    # ---- BOP19 average recalls (eval_bop19_pose.py:47-66): in-process score stage --------
+    t0 = time.time()
+    ths = {'vsd': [round(x, 2) for x in np.arange(0.05, 0.51, 0.05)],
+           'mssd': [round(x, 2) for x in np.arange(0.05, 0.51, 0.05)],
+           'mspd': [float(x) for x in np.arange(5, 51, 5)]}
+    ar, n_scores, ctx = {}, 0, {}
+    p_vsd = params('vsd')
+    for et in ('vsd', 'mssd', 'mspd'):
+      recalls = []
+      taus = range(len(p_vsd['vsd_taus'])) if et == 'vsd' else [None]
+      for tau_id in taus:
+        recs = {s: (ece.records_for_tau(r, tau_id) if et == 'vsd' else r) for s, r in records[et].items()}
+        for th in ths[et]:
+          ps = ecs.parse_args(['--datasets_path=' + info['datasets_path'], '--correct_th_%s=%s' % (et, th)])
+          sc, _ = ecs.score_errors(ps, et, -1, 'ycbv', 'test', None, recs, do_print=False, ctx=ctx)
+          recalls.append(sc['recall'])
+          n_scores += 1
+      ar[et] = float(np.mean(recalls))
+    t['scores_s'] = time.time() - t0
+    out = {'config': 'synthetic ycbv-test layout: 12 scenes x %d images, 6 GT instances / image, 21 models of 4902 verts'
+                     % args.images,
+           'n_gpus': world, 'pairs': n_pairs, 'seconds': {k: round(v, 3) for k, v in t.items()},
+           'pairs_per_s_driver': {et: round(n_pairs[et] / t['errors_%s_s' % et], 1) for et in n_pairs},
+           'AR': ar, 'AR_mean': float(np.mean(list(ar.values()))), 'score_settings_evaluated': n_scores,
+           'sharded_equals_unsharded': identical}
+    print(json.dumps(out))
+    if not args.keep:
+      shutil.rmtree(root, ignore_errors=True)
+  if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+  main()
