@@ -90,25 +90,32 @@ def gt_valid_mask(im_gt, im_gt_info, im_targets, visib_gt_min):
 
 
 def normalize_errors(scene_errs, err_type, p, models_info, im_width):
-  """Per-object diameter / image-width normalisation before thresholding (:235-247).  Mutates
-  the records like the reference does."""
-  if err_type in p['normalized_by_diameter']:
-    for err in scene_errs:
+  """Per-object diameter / image-width normalisation before thresholding (:235-247).  Same
+  arithmetic as the reference (e / diameter, then factor * e) but into NEW records: the input
+  (e.g. the records calc_errors returned) is left untouched and nothing is deep-copied."""
+  by_diam = err_type in p['normalized_by_diameter']
+  by_width = err_type in p['normalized_by_im_width']
+  if not (by_diam or by_width):
+    return scene_errs
+  factor = 640.0 / float(im_width)
+  out = []
+  for err in scene_errs:
+    errors = err['errors']
+    if by_diam:
       diameter = float(models_info[err['obj_id']]['diameter'])
-      for g in err['errors']:
-        err['errors'][g] = [e / diameter for e in err['errors'][g]]
-  if err_type in p['normalized_by_im_width']:
-    factor = 640.0 / float(im_width)
-    for err in scene_errs:
-      for g in err['errors']:
-        err['errors'][g] = [factor * e for e in err['errors'][g]]
-  return scene_errs
+      errors = {g: [e / diameter for e in es] for g, es in errors.items()}
+    if by_width:
+      errors = {g: [factor * e for e in es] for g, es in errors.items()}
+    rec = dict(err)
+    rec['errors'] = errors
+    out.append(rec)
+  return out
 
 
 def score_errors(p, err_type, n_top, dataset, split, split_type, scene_errs_by_scene,
                  do_print=True, ctx=None):
   """Matches + scores for one error setting from in-memory records.
-  scene_errs_by_scene: {scene_id: records} (records are deep-copied before normalisation).
+  scene_errs_by_scene: {scene_id: records} (never mutated).
   ctx: optional cache dict shared between calls (targets, GT, GT info, models info).
   Returns (scores, matches)."""
   ctx = {} if ctx is None else ctx
@@ -137,8 +144,8 @@ def score_errors(p, err_type, n_top, dataset, split, split_type, scene_errs_by_s
     for im_id, im_targets in scene_targets.items():
       gt_curr[im_id] = scene_gt[im_id]
       valid[im_id] = gt_valid_mask(scene_gt[im_id], scene_gt_info[im_id], im_targets, p['visib_gt_min'])
-    errs = normalize_errors(copy.deepcopy(scene_errs_by_scene[scene_id]), err_type, p,
-                            ctx['models_info'], dp_split['im_size'][0])
+    errs = normalize_errors(scene_errs_by_scene[scene_id], err_type, p, ctx['models_info'],
+                            dp_split['im_size'][0])
     matches += pose_matching.match_poses_scene(scene_id, gt_curr, valid, errs,
                                                p['correct_th'][err_type], n_top)
   scores = score.calc_localization_scores(dp_split['scene_ids'], dp_model['obj_ids'],

@@ -31,6 +31,7 @@ def main():
   ap.add_argument('--images', type=int, default=20, help='images per scene (12 scenes)')
   ap.add_argument('--root', default=None)
   ap.add_argument('--keep', action='store_true')
+  ap.add_argument('--profile', action='store_true', help='cProfile of the error + score stages (rank 0)')
   args = ap.parse_args()
 
   import torch
@@ -88,6 +89,11 @@ def main():
                            '--results_path=' + info['results_path'], '--eval_path=' + info['eval_path'],
                            '--datasets_path=' + info['datasets_path']])
   records, n_pairs = {}, {}
+  prof = None
+  if args.profile and rank == 0:
+    import cProfile
+    prof = cProfile.Profile()
+    prof.enable()
   for et in ('vsd', 'mssd', 'mspd'):
     torch.cuda.synchronize()
     t0 = time.time()
@@ -129,6 +135,10 @@ def main():
           n_scores += 1
       ar[et] = float(np.mean(recalls))
     t['scores_s'] = time.time() - t0
+    if prof is not None:
+      import pstats
+      prof.disable()
+      pstats.Stats(prof, stream=sys.stderr).sort_stats('cumulative').print_stats(45)
     out = {'config': 'synthetic ycbv-test layout: 12 scenes x %d images, 6 GT instances / image, 21 models of 4902 verts'
                      % args.images,
            'n_gpus': world, 'pairs': n_pairs, 'seconds': {k: round(v, 3) for k, v in t.items()},
