@@ -143,7 +143,51 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
   const int N = M.n_pts;
   const int nchunks = (N + kChunk - 1) / kChunk;
   const int warp = tid >> 5, lane = tid & 31;
-  const int nitems = nchunks * ns;
+  if (MODE == 1) {
+    // MSPD: the projection of the ESTIMATED pose does not depend on the symmetry, and float64
+    // division is the expensive instruction here.  A warp takes 128 points (4 per lane), projects
+    // them with P_e once, then sweeps the symmetries: 9 DFMA + ONE reciprocal per (point, symmetry).
+    constexpr int kPerLane = 4;
+    const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
+    for (int pass = warp; pass < npass; pass += kWarps) {
+      double px[kPerLane], py[kPerLane], pz[kPerLane], eu[kPerLane], ev[kPerLane];
+      bool ok[kPerLane];
+#pragma unroll
+      for (int k = 0; k < kPerLane; ++k) {
+        const int i = (pass * kPerLane + k) * 32 + lane;
+        ok[k] = i < N;
+        px[k] = py[k] = pz[k] = eu[k] = ev[k] = 0.0;
+        if (ok[k]) {
+          load_pt(pts, i, px[k], py[k], pz[k]);
+          const double ex = Pe[0] * px[k] + Pe[1] * py[k] + Pe[2] * pz[k] + Pe[3];
+          const double ey = Pe[4] * px[k] + Pe[5] * py[k] + Pe[6] * pz[k] + Pe[7];
+          const double ew = Pe[8] * px[k] + Pe[9] * py[k] + Pe[10] * pz[k] + Pe[11];
+          eu[k] = ex / ew;                   // pts_im /= pts_im[2, :]  (misc.py:106)
+          ev[k] = ey / ew;
+        }
+      }
+      for (int sy = 0; sy < ns; ++sy) {
+        double T[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) T[k] = xf[sy][k];
+        double m2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < kPerLane; ++k) {
+          if (ok[k]) {
+            const double gx = T[0] * px[k] + T[1] * py[k] + T[2] * pz[k] + T[3];
+            const double gy = T[4] * px[k] + T[5] * py[k] + T[6] * pz[k] + T[7];
+            const double gw = T[8] * px[k] + T[9] * py[k] + T[10] * pz[k] + T[11];
+            const double inv = 1.0 / gw;
+            const double du = eu[k] - gx * inv, dv = ev[k] - gy * inv;
+            m2 = fmax(m2, du * du + dv * dv);
+          }
+        }
+        m2 = warp_max(m2);
+        if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m2));
+      }
+    }
+  }
+  const int nitems = MODE == 1 ? 0 : nchunks * ns;
   for (int item = warp; item < nitems; item += kWarps) {
     const int chunk = item / ns;
     const int s = item - chunk * ns;
