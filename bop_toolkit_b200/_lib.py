@@ -24,7 +24,8 @@ class ModelDev(ctypes.Structure):
   _fields_ = [
     ('pts', ctypes.c_void_p), ('verts4', ctypes.c_void_p), ('faces4', ctypes.c_void_p),
     ('syms', ctypes.c_void_p), ('diameter', ctypes.c_double), ('n_pts', ctypes.c_int32),
-    ('n_faces', ctypes.c_int32), ('n_syms', ctypes.c_int32), ('pts_f64', ctypes.c_int32)]
+    ('n_faces', ctypes.c_int32), ('n_syms', ctypes.c_int32), ('pts_f64', ctypes.c_int32),
+    ('cull', ctypes.c_int32), ('reserved', ctypes.c_int32)]
 
 
 class VsdParams(ctypes.Structure):

@@ -52,6 +52,39 @@ def pack_syms(syms):
   return out
 
 
+def closed_and_oriented(faces, n_pts):
+  """True iff every directed edge of the triangle list occurs exactly once and its reverse occurs
+  too: a closed surface whose faces are wound consistently (necessary for back-face culling to
+  leave the depth image unchanged)."""
+  f = np.asarray(faces, dtype=np.int64).reshape(-1, 3)
+  if f.shape[0] == 0:
+    return False
+  a = np.concatenate([f[:, 0], f[:, 1], f[:, 2]])
+  b = np.concatenate([f[:, 1], f[:, 2], f[:, 0]])
+  if np.any(a == b):
+    return False
+  fwd = a * int(n_pts) + b
+  if np.unique(fwd).size != fwd.size:
+    return False
+  return bool(np.isin(b * int(n_pts) + a, fwd).all())
+
+
+def _cull_probe_poses(diameter, n=24, seed=12345):
+  """Poses around the object for the culling verification: random rotations at distances from
+  1.2 to 8 diameters, on and off the optical axis."""
+  rng = np.random.default_rng(seed)
+  q = rng.normal(size=(n, 4))
+  q /= np.linalg.norm(q, axis=1, keepdims=True)
+  w, x, y, z = q.T
+  R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], axis=1)
+  d = max(float(diameter), 1e-3)
+  tz = d * rng.uniform(1.2, 8.0, size=n)
+  t = np.stack([tz * rng.uniform(-0.3, 0.3, size=n), tz * rng.uniform(-0.25, 0.25, size=n), tz], axis=1)
+  return np.ascontiguousarray(np.hstack([R, t]))
+
+
 class ModelSet(object):
   """Object models resident in HBM: the device-side counterpart of the reference's
   `models[obj_id]` (inout.load_ply), `models_sym[obj_id]` (misc.get_symmetry_transformations),
@@ -69,9 +102,15 @@ class ModelSet(object):
     self.max_syms = 1
     self.info = {}       # obj_id -> dict(n_pts, n_faces, n_syms, diameter)
 
-  def add(self, obj_id, pts, faces=None, syms=None, diameter=0.0):
+  def add(self, obj_id, pts, faces=None, syms=None, diameter=0.0, cull='auto'):
     """pts: Nx3 float64 as pose_error.* receives them; faces: Fx3 ints (needed for VSD /
-    rendering); syms: list of {'R','t'} or [S,12]; diameter: models_info 'diameter'."""
+    rendering); syms: list of {'R','t'} or [S,12]; diameter: models_info 'diameter'.
+    cull: 'auto' enables back-face culling in the rasteriser only when the mesh is closed and
+    consistently oriented (closed_and_oriented) AND renders of probe poses with culling have the
+    same silhouettes and depths within 1e-5 relative of renders without (_verify_cull); False
+    never culls (the reference's GL state).  Culling halves the triangle work; on such a mesh the
+    nearest surface along every ray is front-facing, so the depth image can only differ by float
+    rounding where a front and a back face nearly coincide at a silhouette."""
     pts = np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 3))
     n = pts.shape[0]
     if n == 0:
@@ -122,9 +161,32 @@ class ModelSet(object):
     self._keep.append(keep)
     self.max_pts = max(self.max_pts, n)
     self.max_syms = max(self.max_syms, ns)
-    self.info[obj_id] = dict(n_pts=n, n_faces=nf, n_syms=ns, diameter=float(diameter))
+    self.info[obj_id] = dict(n_pts=n, n_faces=nf, n_syms=ns, diameter=float(diameter), cull=0)
     self._table = None
+    if cull == 'auto' and nf > 0 and closed_and_oriented(faces, n):
+      self._verify_cull(obj_id, float(diameter) if diameter else float(np.linalg.norm(np.ptp(pts, axis=0))))
     return self._index[obj_id]
+
+  def _verify_cull(self, obj_id, size):
+    """Renders probe poses without culling and with either sign; keeps a sign only if every
+    silhouette is identical and every depth agrees to 1e-5 relative.  (Depths are not always
+    bit-identical: where a front and a back face nearly coincide at a silhouette pixel, the
+    unculled z-test keeps whichever of the two float roundings is smaller.)"""
+    row = self._rows[self._index[obj_id]]
+    poses = _cull_probe_poses(size)
+    cam = np.array([572.4114, 573.57043, 325.2611, 242.04899])
+    ref = render_batch(self, self._index[obj_id], poses, cam, 480, 640)
+    if not bool((ref > 0).any()):
+      return
+    for sign in (1, -1):
+      row.cull = sign
+      self._table = None
+      got = render_batch(self, self._index[obj_id], poses, cam, 480, 640)
+      if torch.equal(got > 0, ref > 0) and bool(((got - ref).abs() <= 1e-5 * ref).all()):
+        self.info[obj_id]['cull'] = sign
+        return
+    row.cull = 0
+    self._table = None
 
   def index_of(self, obj_id):
     return self._index[obj_id]

@@ -85,8 +85,9 @@ __device__ __forceinline__ void tri_plane(float A1, float A2, float B1, float B2
 
 // Returns the number of candidate pixels (0: nothing to draw; < 0: -count, the triangle is too
 // large for 32-bit edge functions and must take the 64-bit path).
+// cull: 0 = none, +1 / -1 = drop triangles with negative / positive signed area (bop_model_dev.cull).
 __device__ __forceinline__ int tri_setup(const PVert& v0, const PVert& v1, const PVert& v2, int cx0,
-                                         int cy0, int cx1, int cy1, TriSetup& T) {
+                                         int cy0, int cx1, int cy1, TriSetup& T, int cull = 0) {
   if (!(v0.valid & v1.valid & v2.valid)) return 0;
   const int minx = min(v0.x, min(v1.x, v2.x)), maxx = max(v0.x, max(v1.x, v2.x));
   const int miny = min(v0.y, min(v1.y, v2.y)), maxy = max(v0.y, max(v1.y, v2.y));
@@ -104,6 +105,7 @@ __device__ __forceinline__ int tri_setup(const PVert& v0, const PVert& v1, const
   const int area2 = (v1.x - v0.x) * (v2.y - v0.y) - (v1.y - v0.y) * (v2.x - v0.x);
   if (area2 == 0) return 0;
   const int s = area2 > 0 ? 1 : -1;
+  if (cull == -s) return 0;
   const int px0 = bx0 << kSubBits, py0 = by0 << kSubBits;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
@@ -203,13 +205,14 @@ struct TriSetup64 {
 };
 
 __device__ __forceinline__ bool tri_setup64(const PVert& v0, const PVert& v1, const PVert& v2,
-                                            const TriSetup& Tb, TriSetup64& T) {
+                                            const TriSetup& Tb, TriSetup64& T, int cull = 0) {
   T.bx0 = Tb.bx0; T.bx1 = Tb.bx1; T.by0 = Tb.by0; T.by1 = Tb.by1;
   const long long ax[3] = {v1.x, v2.x, v0.x}, ay[3] = {v1.y, v2.y, v0.y};
   const long long bx[3] = {v2.x, v0.x, v1.x}, by[3] = {v2.y, v0.y, v1.y};
   const long long area2 = (long long)(v1.x - v0.x) * (v2.y - v0.y) - (long long)(v1.y - v0.y) * (v2.x - v0.x);
   if (area2 == 0) return false;
   const long long s = area2 > 0 ? 1 : -1;
+  if (cull == -(int)s) return false;
   const long long px0 = (long long)T.bx0 << kSubBits, py0 = (long long)T.by0 << kSubBits;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {

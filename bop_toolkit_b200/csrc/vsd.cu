@@ -423,6 +423,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const bop_model_dev M = a.models[sD.obj];
     const int4* __restrict__ faces = (const int4*)M.faces4;
     const int F = M.n_faces;
+    const int cull = M.cull;
 
     // One loop over the triangles of BOTH poses (they draw into different z-tiles, so no barrier
     // is needed between them).  Triangles with many candidate pixels are deferred to a queue and
@@ -448,7 +449,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
         const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
         TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T, cull);
         if (n != 0) {
           unsigned* const z = zt + (size_t)p * a.tile_px;
           if (n > 0 && n <= a.small_tri_px) {
@@ -461,7 +462,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
               tri_raster_small(T, z, cx0, cy0, w);
             } else {
               TriSetup64 T64;
-              if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+              if (tri_setup64(v0, v1, v2, T, T64, cull)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
             }
           }
         }
@@ -482,12 +483,12 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
         unsigned* const z = zt + (size_t)p * a.tile_px;
         TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T, cull);
         if (n > 0) {
           tri_raster_warp(T, lane, z, cx0, cy0, w);
         } else if (n < 0) {
           TriSetup64 T64;
-          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
+          if (tri_setup64(v0, v1, v2, T, T64, cull)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
         }
       }
     }

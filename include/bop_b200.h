@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BOP_B200_ABI_VERSION 1
+#define BOP_B200_ABI_VERSION 2
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
 #define BOP_MAX_SYMS_PER_CTA 32
 
@@ -63,6 +63,12 @@ typedef struct bop_model_dev {
   int32_t        n_faces;
   int32_t        n_syms;
   int32_t        pts_f64;
+  int32_t        cull;      /* 0: draw every triangle (the reference's GL state: no face culling,
+                               renderer_vispy.py:470).  +1 / -1: skip triangles whose projected
+                               signed area is negative / positive.  Only set for meshes verified to
+                               be closed and consistently oriented, where the nearest surface along
+                               every ray is front-facing and the depth image is unchanged.        */
+  int32_t        reserved;
 } bop_model_dev;
 
 /* Parameters of pose_error.vsd (bop_toolkit_lib/pose_error.py:17-18). */

@@ -26,11 +26,11 @@ def test_library_exports_every_declared_symbol():
   for name in declared:
     assert hasattr(lib, name), 'missing export: ' + name
   assert sorted(_lib.EXPORTED_SYMBOLS) == declared     # the ctypes table covers the header
-  assert _lib.lib().bop_abi_version() == 1
+  assert _lib.lib().bop_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
-  assert ctypes.sizeof(_lib.ModelDev) == 56
+  assert ctypes.sizeof(_lib.ModelDev) == 64
   assert ctypes.sizeof(_lib.VsdParams) == 8 * _lib.BOP_MAX_TAUS + 8 + 8 * 4
 
 
@@ -78,3 +78,19 @@ def test_overlap_gate_host_twin(golden):
   g = golden
   got = [misc.overlapping_sphere_projections(75.0, g['t_e'][i], g['t_g'][i]) for i in range(len(g['t_e']))]
   assert np.array_equal(np.array(got), g['sphere_proj_overlap'])
+
+
+def test_closed_and_oriented_mesh_check():
+  """Host-side gate of the rasteriser's back-face culling."""
+  import numpy as np
+  from bop_toolkit_b200 import batch, synth
+  pts, f = synth.make_mesh(12, 24, 100.0, seed=1)
+  n = len(pts)
+  assert batch.closed_and_oriented(f, n)
+  assert batch.closed_and_oriented(f[:, ::-1], n)                   # inside-out is still consistent
+  assert not batch.closed_and_oriented(f[:-1], n)                   # hole
+  assert not batch.closed_and_oriented(np.vstack([f[:5], f[5:, ::-1]]), n)   # mixed winding
+  assert not batch.closed_and_oriented(np.vstack([f, f[:1]]), n)    # duplicate face
+  assert not batch.closed_and_oriented(np.zeros((0, 3), int), n)
+  tet = np.array([[0, 1, 2], [0, 3, 1], [1, 3, 2], [0, 2, 3]])
+  assert batch.closed_and_oriented(tet, 4)

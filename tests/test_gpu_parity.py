@@ -558,3 +558,47 @@ def test_cus_fused_vs_reference_golden(B, golden):
   far[:, 9] += 5000.0
   gated = B.cus_batch(ren.model_set, 0, far, pg_, g['vsd_K'], H, W, gate=True).cpu().numpy()
   assert np.all(gated == 1.0)
+
+
+# ------------------------------------------------------------------ verified back-face culling
+def test_backface_culling_is_output_preserving(B):
+  """ModelSet.add culls back faces only for closed, consistently oriented meshes and only after
+  probe renders agreed; silhouettes must be identical, depths equal up to float rounding."""
+  from bop_toolkit_b200 import synth
+  pts, faces = synth.make_mesh(30, 60, 180.0, seed=4)
+  n = 48
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=9, z_range=(300.0, 1400.0))
+  pe, pg = _poses(B, R_e, t_e), _poses(B, R_g, t_g)
+  cam = synth.LM_K.reshape(9)[[0, 4, 2, 5]]
+  plain, culled, flipped, opened = B.ModelSet(), B.ModelSet(), B.ModelSet(), B.ModelSet()
+  plain.add(1, pts, faces, None, 180.0, cull=False)
+  culled.add(1, pts, faces, None, 180.0)
+  flipped.add(1, pts, faces[:, ::-1].copy(), None, 180.0)       # inside-out winding
+  opened.add(1, pts, faces[:-7], None, 180.0)                   # a hole: not closed
+  assert plain.info[1]['cull'] == 0 and opened.info[1]['cull'] == 0
+  assert culled.info[1]['cull'] in (1, -1) and flipped.info[1]['cull'] == -culled.info[1]['cull']
+  ref = B.render_batch(plain, 0, pg, cam, 480, 640)
+  n_diff = 0
+  for ms in (culled, flipped):
+    got = B.render_batch(ms, 0, pg, cam, 480, 640)
+    assert torch_equal(got > 0, ref > 0)                          # identical silhouettes
+    assert bool(((got - ref).abs() <= 1e-5 * ref).all())          # depth: float rounding only
+    n_diff += int((got != ref).sum())
+  print('culled vs unculled renders: %d of %d covered pixels differ in the last bits'
+        % (n_diff // 2, int((ref > 0).sum())))
+  depth = ref.clone()
+  depth[depth == 0] = 1500.0
+  taus = list(np.arange(0.05, 0.51, 0.05))
+  Ks = np.tile(synth.LM_K.reshape(1, 9), (n, 1))
+  args = (0, pe, pg, depth, np.arange(n, dtype=np.int32), Ks, 15, taus, True, 'step')
+  v0, c0 = B.vsd_batch(plain, *args, return_counts=True)
+  v1, c1 = B.vsd_batch(culled, *args, return_counts=True)
+  assert int((c0 - c1).abs().max()) <= 2 and float((v0 - v1).abs().max()) <= 1e-3
+  m0 = B.mask_overlap_batch(plain, 0, pe, pg, synth.LM_K, 480, 640)
+  m1 = B.mask_overlap_batch(culled, 0, pe, pg, synth.LM_K, 480, 640)
+  assert torch_equal(m0['counts'], m1['counts']) and torch_equal(m0['bbox'], m1['bbox'])
+
+
+def torch_equal(a, b):
+  import torch
+  return bool(torch.equal(a, b))
