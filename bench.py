@@ -249,6 +249,8 @@ def gpu_arm(args):
     dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
   assert torch.cuda.is_available(), 'bench.py needs a GPU (there is no CPU fallback)'
   torch.cuda.set_device(local_rank)
+  from bop_toolkit_b200 import affinity
+  bound = None if os.environ.get('BOP_NO_BIND') else affinity.bind_to_gpu(local_rank)
   device = torch.device('cuda', local_rank)
   _lib.require_cuda()
   lib = _lib.lib()
@@ -401,7 +403,8 @@ def gpu_arm(args):
     'config': {'workload': WORKLOAD % P, 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
                'l2': 'inputs larger than L2 (12.3 GB of depth per pass)',
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
-               'exchange': 'all-gather of error records per step' if world > 1 else 'none'},
+               'exchange': 'all-gather of error records per step' if world > 1 else 'none',
+               'cpu_affinity': bound},
     'e2e': {'value': e2e_v, 'unit': 'pairs/s', 'ms_per_step': ms_e2e / args.steps,
             'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(h_out.numel() * 8),
             'matches_resident': same,
