@@ -401,7 +401,9 @@ def gpu_arm(args):
     'ms_per_step': ms_res / args.steps, 'higher_is_better': True, 'scaling': 'weak',
     'vs_baseline': None, 'dtype': 'f32 raster + f64 pixel/vertex arithmetic', 'data': 'synthetic',
     'config': {'workload': WORKLOAD % P, 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
-               'l2': 'inputs larger than L2 (12.3 GB of depth per pass)',
+               'l2': 'inputs larger than L2: resident pass reads its model pixels out of %.1f GB of depth; '
+                     'e2e pass fetches ~0.28 GB of host depth and streams %.1f GB of projected-vertex '
+                     'scratch per step (L2 = 126 MB)' % (P * H * W * 4 / 1e9, P * 2 * n_verts * 32 / 1e9),
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
                'exchange': 'all-gather of error records per step' if world > 1 else 'none',
                'cpu_affinity': bound},

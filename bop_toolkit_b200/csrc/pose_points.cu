@@ -19,7 +19,6 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kChunk = 256;  // points per (symmetry, chunk) warp work item
 
 template <typename PT>
 __device__ __forceinline__ void load_pt(const PT* __restrict__ pts, int i, double& x, double& y,
@@ -70,8 +69,8 @@ __global__ void re_te_kernel(const double* __restrict__ pe, const double* __rest
 // ---------------------------------------------------------------------------------
 // K3: symmetric max errors (MSSD / MSPD)
 // grid = (n_pairs, sym_groups); each CTA owns up to BOP_MAX_SYMS_PER_CTA symmetries of
-// one pair and all points.  Warp work item = (symmetry, 256-point chunk), chunk-major so
-// that warps running together read the same points (L1 reuse).  Per-symmetry maxima are
+// one pair and all points.  A warp keeps 128 points (4 per lane) in registers and sweeps the
+// CTA's symmetries over them, so points are loaded once.  Per-symmetry maxima are
 // kept in shared memory as uint64 bit patterns (non-negative doubles order like
 // integers); the CTA's min over symmetries goes to out[] with one atomicMin.
 // ---------------------------------------------------------------------------------
@@ -141,7 +140,6 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
 
   const PT* __restrict__ pts = (const PT*)M.pts;
   const int N = M.n_pts;
-  const int nchunks = (N + kChunk - 1) / kChunk;
   const int warp = tid >> 5, lane = tid & 31;
   if (MODE == 1) {
     // MSPD: the projection of the ESTIMATED pose does not depend on the symmetry, and float64
@@ -187,44 +185,39 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
   }
-  const int nitems = MODE == 1 ? 0 : nchunks * ns;
-  for (int item = warp; item < nitems; item += kWarps) {
-    const int chunk = item / ns;
-    const int s = item - chunk * ns;
-    double T[12];
+  if (MODE == 0) {
+    // MSSD: same sweep -- a warp keeps 128 points in registers and visits every symmetry, so the
+    // points are loaded (and converted to float64) once instead of once per symmetry.
+    constexpr int kPerLane = 4;
+    const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
+    for (int pass = warp; pass < npass; pass += kWarps) {
+      double px[kPerLane], py[kPerLane], pz[kPerLane];
+      bool ok[kPerLane];
 #pragma unroll
-    for (int k = 0; k < 12; ++k) T[k] = xf[s][k];
-    double m2 = 0.0;
-    const int base = chunk * kChunk;
-#pragma unroll 4
-    for (int k = 0; k < kChunk / 32; ++k) {
-      const int i = base + k * 32 + lane;
-      if (i < N) {
-        double x, y, z;
-        load_pt(pts, i, x, y, z);
-        double d2;
-        if (MODE == 0) {
-          const double dx = T[0] * x + T[1] * y + T[2] * z + T[9];
-          const double dy = T[3] * x + T[4] * y + T[5] * z + T[10];
-          const double dz = T[6] * x + T[7] * y + T[8] * z + T[11];
-          d2 = dx * dx + dy * dy + dz * dz;
-        } else {
-          const double ex = Pe[0] * x + Pe[1] * y + Pe[2] * z + Pe[3];
-          const double ey = Pe[4] * x + Pe[5] * y + Pe[6] * z + Pe[7];
-          const double ew = Pe[8] * x + Pe[9] * y + Pe[10] * z + Pe[11];
-          const double gx = T[0] * x + T[1] * y + T[2] * z + T[3];
-          const double gy = T[4] * x + T[5] * y + T[6] * z + T[7];
-          const double gw = T[8] * x + T[9] * y + T[10] * z + T[11];
-          const double du = ex / ew - gx / gw;   // pts_im /= pts_im[2, :]  (misc.py:106)
-          const double dv = ey / ew - gy / gw;
-          d2 = du * du + dv * dv;
+      for (int k = 0; k < kPerLane; ++k) {
+        const int i = (pass * kPerLane + k) * 32 + lane;
+        ok[k] = i < N;
+        px[k] = py[k] = pz[k] = 0.0;
+        if (ok[k]) load_pt(pts, i, px[k], py[k], pz[k]);
+      }
+      for (int sy = 0; sy < ns; ++sy) {
+        double T[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) T[k] = xf[sy][k];
+        double m2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < kPerLane; ++k) {
+          if (ok[k]) {
+            const double dx = T[0] * px[k] + T[1] * py[k] + T[2] * pz[k] + T[9];
+            const double dy = T[3] * px[k] + T[4] * py[k] + T[5] * pz[k] + T[10];
+            const double dz = T[6] * px[k] + T[7] * py[k] + T[8] * pz[k] + T[11];
+            m2 = fmax(m2, dx * dx + dy * dy + dz * dz);
+          }
         }
-        // NaN-propagating max would differ from numpy only for NaN inputs (outside the domain).
-        m2 = fmax(m2, d2);
+        m2 = warp_max(m2);
+        if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m2));
       }
     }
-    m2 = warp_max(m2);
-    if (lane == 0) atomicMax(&symmax[s], (unsigned long long)__double_as_longlong(m2));
   }
   __syncthreads();
   if (tid == 0) {
