@@ -419,7 +419,12 @@ def gpu_arm(args):
                  'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                  'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback 6650',
                  'traffic': traffic, 'kernel_ms': fused_ms, 'algorithmic_bytes_per_pair': alg_pair,
-                 'other_kernels_ms': parts},
+                 'other_kernels_ms': parts,
+                 'note': 'achieved = algorithmic bytes of a NON-fused pipeline (SURVEY 8d: 3 reads + 2 z-buffer '
+                         'writes of H*W*4 B + mesh) / kernel time, so frac > 1 means the fusion removed that '
+                         'traffic: `traffic` is the DRAM bytes ncu measured (3-4 % of DRAM bandwidth). The '
+                         'kernel is bound by instruction issue (ncu: issue slots 64-69 % busy, 19 of 32 lanes '
+                         'active); see DESIGN.md section 4.'},
   }
   if world == 1 and not args.no_cpu_baseline:
     v, ms_step, _ = cpu_arm(P, args.cpu_sample, 1, 1, 0)

@@ -12,7 +12,7 @@ tail -c 3000 $OUT/bench.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref rc=$?"
 cat $OUT/bench_ref.json
 if [ -z "$SKIP_NCU" ]; then
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $OUT/launches.csv \
   python bench.py --pairs 2000 --steps 2 --warmup 3 --no-cpu-baseline > $OUT/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:fused_kernel<\(int\)0' --launch-skip 3 -c 1 -f -o $OUT/fused \
   python bench.py --pairs 2000 --steps 2 --warmup 3 --no-cpu-baseline > $OUT/ncu_full.log 2>&1; echo "ncu full rc=$?"
