@@ -177,6 +177,37 @@ def main():
         after = collect(eval_path)
         for rel in sorted(set(after) - before):
           scores['%s|%d|%d|%s' % (error_type, n_top, si, rel)] = after[rel]
+    # ---- the whole BOP19 evaluation by the reference's eval_bop19_pose.py -----------------
+    # It shells out to eval_calc_errors.py / eval_calc_scores.py 123 times; the children need
+    # the same shim, so subprocess.call is routed to runpy in this process.  The children take
+    # the dataset folder from config.datasets_path (BOP_PATH), patched here.
+    import subprocess
+    from bop_toolkit_lib import config as ref_config
+    ref_config.datasets_path = info['datasets_path']
+    real_call = subprocess.call
+
+    def call_in_process(cmd):
+      assert cmd[0] == 'python'
+      run_script(cmd[1], list(cmd[2:]))
+      return 0
+    subprocess.call = call_in_process
+    bop19_eval = os.path.join(tmp, 'eval_bop19')
+    try:
+      run_script('/root/reference/scripts/eval_bop19_pose.py', [
+        '--result_filenames=' + info['result_filename'], '--results_path=' + info['results_path'],
+        '--eval_path=' + bop19_eval, '--renderer_type=vispy'])
+    finally:
+      subprocess.call = real_call
+    bop19 = {'scores': {}, 'matches_sha256': {}, 'n_error_files': 0}
+    for rel, text in collect(bop19_eval).items():
+      name = os.path.basename(rel)
+      if name.startswith('scores_'):
+        bop19['scores'][rel] = text
+      elif name.startswith('matches_'):
+        bop19['matches_sha256'][rel] = hashlib.sha256(text.encode()).hexdigest()
+      else:
+        bop19['n_error_files'] += 1
+
     # ---- the reference's dataset tables (fields the drivers read) ------------------------
     from bop_toolkit_lib import dataset_params as ref_dp
     tables = {}
@@ -196,11 +227,11 @@ def main():
     out = {'tables': tables, 'dataset_kw': {k: (list(v) if isinstance(v, tuple) else v) for k, v in DATASET_KW.items()},
            'dataset_sha256': dataset_checksum(info), 'runs': [list(r) for r in RUNS], 'files': files,
            'gt_info': gt_info, 'score_runs': [list(r) for r in SCORE_RUNS],
-           'score_settings': SCORE_SETTINGS, 'scores': scores}
+           'score_settings': SCORE_SETTINGS, 'scores': scores, 'bop19': bop19}
     with open(os.path.join(HERE, 'driver_golden.json'), 'w') as f:
       json.dump(out, f, indent=0, sort_keys=True)
-    print('wrote %d error files, %d score files, %d masks, dataset sha256 %s'
-          % (len(files), len(scores), len(masks), out['dataset_sha256']))
+    print('wrote %d error files, %d score files, %d masks, %d bop19 score files, dataset sha256 %s'
+          % (len(files), len(scores), len(masks), len(bop19['scores']), out['dataset_sha256']))
   finally:
     shutil.rmtree(tmp, ignore_errors=True)
 

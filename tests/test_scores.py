@@ -164,3 +164,38 @@ def test_calc_gt_masks_match_reference(dataset, driver_golden):
     assert diff <= 3, (key, diff)
   print('gt masks: %d files, %d differing bytes in total' % (n, bad))
   assert n == 30
+
+
+@pytest.mark.gpu
+def test_eval_bop19_pose_matches_reference(dataset, driver_golden, tmp_path):
+  """The whole BOP19 evaluation in one process (3 error types, 120 score settings) against the
+  files the reference's eval_bop19_pose.py + 123 child scripts left behind."""
+  import hashlib
+  from bop_toolkit_b200 import eval_bop19_pose as e19
+  _install_gt_info(dataset, driver_golden)
+  eval_path = str(tmp_path / 'eval_bop19')
+  p = e19.parse_args(['--result_filenames=' + dataset['result_filename'],
+                      '--results_path=' + dataset['results_path'], '--eval_path=' + eval_path,
+                      '--datasets_path=' + dataset['datasets_path']])
+  final = e19.evaluate(p, log=lambda s: None)['synth_lm-test']
+  gold = driver_golden['bop19']
+  ref_final = json.loads(gold['scores']['synth_lm-test/scores_bop19.json'])
+  for k, v in ref_final.items():
+    assert abs(float(final[k]) - v) <= 1e-3, (k, final[k], v)          # 0.1 pp
+  same_scores = same_matches = 0
+  for rel, text in gold['scores'].items():
+    ours = open(os.path.join(eval_path, rel)).read()
+    same_scores += int(ours == text)
+    a, b = json.loads(ours), json.loads(text)
+    assert set(a) == set(b)
+    if 'recall' in b:
+      assert abs(a['recall'] - b['recall']) <= 1e-3, rel
+      assert a['targets_count'] == b['targets_count'] and a['gt_count'] == b['gt_count']
+  for rel, sha in gold['matches_sha256'].items():
+    ours = open(os.path.join(eval_path, rel)).read()
+    same_matches += int(hashlib.sha256(ours.encode()).hexdigest() == sha)
+  n_err = sum(1 for d, _, names in os.walk(eval_path) for n in names if n.startswith('errors_'))
+  assert n_err == gold['n_error_files']
+  print('bop19: %d of %d score files and %d of %d match files byte-identical to the reference; AR %s'
+        % (same_scores, len(gold['scores']), same_matches, len(gold['matches_sha256']),
+           {k: round(float(v), 4) for k, v in final.items()}))
