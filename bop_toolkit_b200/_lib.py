@@ -25,7 +25,7 @@ class ModelDev(ctypes.Structure):
     ('pts', ctypes.c_void_p), ('verts4', ctypes.c_void_p), ('faces4', ctypes.c_void_p),
     ('syms', ctypes.c_void_p), ('diameter', ctypes.c_double), ('n_pts', ctypes.c_int32),
     ('n_faces', ctypes.c_int32), ('n_syms', ctypes.c_int32), ('pts_f64', ctypes.c_int32),
-    ('cull', ctypes.c_int32), ('reserved', ctypes.c_int32)]
+    ('cull', ctypes.c_int32), ('cull_min_dist', ctypes.c_float)]
 
 
 class VsdParams(ctypes.Structure):

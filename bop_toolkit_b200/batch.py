@@ -131,6 +131,8 @@ class ModelSet(object):
       row.pts_f64 = 0 if f32_exact else 1
       row.n_pts = n
       row.diameter = float(diameter)
+      # camera centres within this distance of the model origin may be inside the mesh: no culling
+      row.cull_min_dist = float(np.sqrt((p32.astype(np.float64) ** 2).sum(axis=1).max())) * 1.001
       keep = [d_pts, d_v4]
       nf = 0
       if faces is not None and len(faces):

@@ -129,7 +129,7 @@ extern "C" int bop_model_upload(const double* pts, int n_pts, const int32_t* fac
   d.pts = p;
   d.pts_f64 = f32_exact ? 0 : 1;
   d.cull = 0;       /* the convenience layer never culls; see batch.ModelSet for the verified path */
-  d.reserved = 0;
+  d.cull_min_dist = 0.f;
   BOP_CUDA(cudaMalloc(&p, v4.size() * sizeof(float)));
   BOP_CUDA(cudaMemcpy(p, v4.data(), v4.size() * sizeof(float), cudaMemcpyHostToDevice));
   d.verts4 = (const float*)p;

@@ -37,7 +37,8 @@ struct PairDesc {
   double diameter;
   int x0, y0, w, h;       // union ROI; x0 and w are multiples of 4
   int obj, im;
-  int n_poses, pad;
+  int n_poses;
+  int cull_ok;            // bit p: back-face culling may be applied to pose p (camera outside the model)
 };
 
 struct WorkItem {
@@ -160,7 +161,17 @@ __global__ void plan_kernel(const bop_model_dev* __restrict__ models,
   D.obj = obj;
   D.diameter = diameters ? diameters[i] : models[obj].diameter;
   D.n_poses = n_poses;
-  D.pad = 0;
+  {
+    // Culling is only output-preserving while the camera centre is outside the mesh: require it
+    // outside the model's bounding sphere (|t| = distance of the camera from the model origin).
+    const double r = (double)models[obj].cull_min_dist;
+    int ok = 0;
+    for (int p = 0; p < n_poses; ++p) {
+      const double* t = (p == 0 ? pose_a : pose_b) + 12 * (size_t)i + 9;
+      if (t[0] * t[0] + t[1] * t[1] + t[2] * t[2] > r * r) ok |= 1 << p;
+    }
+    D.cull_ok = ok;
+  }
   double fx, fy, cx, cy;
   if (cam_mode == 0) {
     D.im = im_idx[i];
@@ -423,7 +434,8 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const bop_model_dev M = a.models[sD.obj];
     const int4* __restrict__ faces = (const int4*)M.faces4;
     const int F = M.n_faces;
-    const int cull = M.cull;
+    const int cull_ok = sD.cull_ok;
+    const int cull_m = M.cull;
 
     // One loop over the triangles of BOTH poses (they draw into different z-tiles, so no barrier
     // is needed between them).  Triangles with many candidate pixels are deferred to a queue and
@@ -441,6 +453,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       if (g < nF) {
         const int p = g >= F ? 1 : 0;
         const int f = g - p * F;
+        const int cull = ((cull_ok >> p) & 1) ? cull_m : 0;
         const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
         const int4 fi = __ldg(faces + f);
         const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
@@ -474,6 +487,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       for (int qi = warp; qi < nq; qi += nwarps) {
         const int g = queue[qi];
         const int p = g >= F ? 1 : 0;
+        const int cull = ((cull_ok >> p) & 1) ? cull_m : 0;
         const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
         const int4 fi = __ldg(faces + (g - p * F));
         const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),

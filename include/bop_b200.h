@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BOP_B200_ABI_VERSION 2
+#define BOP_B200_ABI_VERSION 3
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
 #define BOP_MAX_SYMS_PER_CTA 32
 
@@ -68,7 +68,10 @@ typedef struct bop_model_dev {
                                signed area is negative / positive.  Only set for meshes verified to
                                be closed and consistently oriented, where the nearest surface along
                                every ray is front-facing and the depth image is unchanged.        */
-  int32_t        reserved;
+  float          cull_min_dist; /* culling is applied to a pose only if |t| > cull_min_dist, i.e. the
+                               camera centre lies outside the model's bounding sphere around its
+                               origin (inside a mesh the visible faces ARE the back faces); set it
+                               to max |pts| or more.  0 with cull != 0 culls every pose.          */
 } bop_model_dev;
 
 /* Parameters of pose_error.vsd (bop_toolkit_lib/pose_error.py:17-18). */

@@ -1,0 +1,277 @@
+"""GPU edge cases and size-independent properties of the CUDA path (through the C ABI).
+
+  * empty batches for every batched entry point;
+  * close-up poses (image-filling object, large triangles) against the oracle rasteriser and
+    under different kernel tunings -- tile size, the small/large triangle split and the
+    deferred-triangle queue (overflow included) must not change a single bit of any depth image
+    or VSD count (raster.cuh: the depth of a pixel depends on the triangle and the pixel only);
+  * objects behind / straddling the camera plane (outside the parity domain: triangles touching
+    Z <= 1e-6 are dropped, same rule as the oracle), fully outside the image, all-zero depth;
+  * the tau limit of one launch (BOP_MAX_TAUS) and chunking above it;
+  * at BASELINE.json's full size (10,000 pairs): results do not depend on batch composition
+    (shuffled batch == shuffled results, bit for bit), VSD(gt, gt) is 0 wherever something is
+    visible and 1 otherwise, MSSD / MSPD of a GT pose composed with a model symmetry is ~0.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+DEFAULT_TUNING = (18432, 1024, 1, 256)
+
+
+@pytest.fixture(scope='module')
+def B():
+  import torch
+  from bop_toolkit_b200 import _lib, batch
+  assert torch.cuda.is_available(), 'GPU tests need a CUDA device'
+  _lib.require_cuda()
+  return batch
+
+
+def _tune(*t):
+  from bop_toolkit_b200 import _lib
+  _lib.check(_lib.lib().bop_vsd_set_tuning(*t))
+
+
+def _cams(K, n):
+  return np.tile([K[0, 0], K[1, 1], K[0, 2], K[1, 2]], (n, 1))
+
+
+def test_empty_batches(B):
+  from bop_toolkit_b200 import synth
+  pts, faces = synth.make_mesh(10, 20, 100.0, seed=1)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 100.0)
+  z = np.zeros((0, 12))
+  K = synth.LM_K
+  assert B.mssd_batch(ms, 0, z, z).shape == (0,)
+  assert B.mspd_batch(ms, 0, z, z, K).shape == (0,)
+  assert B.add_batch(ms, 0, z, z).shape == (0,)
+  assert B.adi_batch(ms, 0, z, z).shape == (0,)
+  re, te = B.re_te_batch(z, z)
+  assert re.shape == (0,) and te.shape == (0,)
+  depth = np.ones((1, 480, 640), np.float32)
+  assert B.vsd_batch(ms, 0, z, z, depth, None, K.reshape(1, 9), 15, [0.1, 0.2]).shape == (0, 2)
+  assert B.render_batch(ms, 0, z, np.zeros((0, 4)), 480, 640).shape == (0, 480, 640)
+
+
+def _closeup_case(n=10, seed=3):
+  from bop_toolkit_b200 import synth
+  pts, faces = synth.make_mesh(24, 48, 220.0, seed=seed)     # coarse mesh: big triangles up close
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=seed + 1, z_range=(140.0, 320.0), outlier_frac=0.0)
+  t_g[0] = [0.0, 0.0, 125.0]          # surface ~15 mm from the camera plane: fills the whole image
+  t_e[0] = [3.0, -2.0, 128.0]
+  t_g[1] = [250.0, 150.0, 160.0]      # mostly outside
+  t_e[1] = [245.0, 155.0, 165.0]
+  return pts, faces, R_e, t_e, R_g, t_g
+
+
+def test_closeup_render_vs_oracle(B, oracle_built):
+  from bop_toolkit_b200 import synth
+  from oracle import renderer_oracle
+  from test_gpu_parity import _render_compare
+  pts, faces, _, _, R_g, t_g = _closeup_case()
+  K = synth.LM_K
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 220.0)
+  d = B.render_batch(ms, 0, B.pack_poses(R_g, t_g), _cams(K, len(R_g)), 480, 640).cpu().numpy()
+  tot_sil = tot_mis = tot_far = n_bad = n_px = 0
+  for i in range(len(R_g)):
+    ref = renderer_oracle.render_depth(pts, faces, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], 480, 640, 8)
+    sil, mis, far, rel, bad = _render_compare(d[i], ref)
+    tot_sil += sil; tot_mis += mis; tot_far += far
+    n_bad += int(bad.sum()); n_px += rel.size
+  assert (d[0] > 0).mean() > 0.95                      # the first pose really fills the image
+  assert tot_far == 0
+  assert tot_mis <= 0.0005 * tot_sil + 2, (tot_mis, tot_sil)
+  assert n_bad <= 1e-4 * n_px + 2, (n_bad, n_px)
+  print('close-up render: %d covered px, %d silhouette px, %d coverage mismatches, %d depth outliers'
+        % (n_px, tot_sil, tot_mis, n_bad))
+
+
+def test_results_do_not_depend_on_tuning(B):
+  """Tile height, CTA shape, the small/large triangle threshold and the deferred queue
+  (small_tri_px = 1 sends every triangle through it and overflows its 2048 slots) are
+  scheduling choices: depth images and VSD counts stay bit-identical."""
+  from bop_toolkit_b200 import synth
+  K = synth.LM_K
+  pts, faces, R_e, t_e, R_g, t_g = _closeup_case()
+  fine_pts, fine_faces = synth.make_mesh(50, 100, 200.0, seed=9)
+  R2e, t2e, R2g, t2g = synth.make_pose_pairs(12, seed=10, z_range=(300.0, 900.0), outlier_frac=0.1)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 220.0)
+  ms.add(2, fine_pts, fine_faces, None, 200.0)
+  obj = np.array([0] * len(R_e) + [1] * len(R2e), np.int32)
+  pe = B.pack_poses(np.concatenate([R_e, R2e]), np.concatenate([t_e, t2e]))
+  pg = B.pack_poses(np.concatenate([R_g, R2g]), np.concatenate([t_g, t2g]))
+  n = len(obj)
+  rng = np.random.default_rng(0)
+  taus = [0.05, 0.2, 0.5]
+
+  def run():
+    dg = B.render_batch(ms, obj, pg, _cams(K, n), 480, 640)
+    depth = dg.clone()
+    depth[depth == 0] = 1500.0
+    out = [dg.cpu().numpy()]
+    for cost in ('step', 'tlinear'):
+      e, c = B.vsd_batch(ms, obj, pe, pg, depth, np.arange(n, dtype=np.int32), np.tile(K.reshape(1, 9), (n, 1)),
+                         15, taus, True, cost, return_counts=True)
+      out += [e.cpu().numpy(), c.cpu().numpy()]
+    st = B.mask_overlap_batch(ms, obj, pe, pg, K, 480, 640)
+    out += [st[k].cpu().numpy() for k in sorted(st)]
+    return out
+
+  try:
+    base = run()
+    assert (base[0][0] > 0).mean() > 0.95
+    for tuning in ((4096, 256, 2, 4), (18432, 1024, 1, 1), (4096, 128, 4, 1 << 20), (9216, 512, 2, 64)):
+      _tune(*tuning)
+      for a, b in zip(base, run()):
+        if a.dtype.kind == 'f' and a.ndim == 2 and a.shape[1] == len(taus):
+          # tlinear sums float64 costs in a tiling-dependent order: 1e-11 (step costs are exact)
+          assert np.allclose(a, b, rtol=0, atol=1e-11, equal_nan=True), tuning
+        else:
+          assert np.array_equal(a, b, equal_nan=True), tuning
+  finally:
+    _tune(*DEFAULT_TUNING)
+
+
+def test_behind_camera_outside_image_and_zero_depth(B, oracle_built):
+  from bop_toolkit_b200 import synth
+  from oracle import pose_error_oracle as po, renderer_oracle
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(24, 48, 200.0, seed=5)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, [{'R': np.eye(3), 't': np.zeros((3, 1))}], 200.0)
+  assert ms.info[1]['cull'] != 0                     # culled model: the inside view must survive
+  R = np.tile(np.eye(3), (5, 1, 1))
+  t_g = np.array([[0, 0, 60.0],        # camera INSIDE the object: triangles straddle Z = 0
+                  [0, 0, -500.0],      # entirely behind the camera
+                  [9000.0, 0, 600.0],  # far outside the image
+                  [0, 0, 600.0],       # normal pose
+                  [0, 0, 600.0]])      # normal pose, all-zero depth image (pair 4)
+  t_e = t_g + np.array([2.0, 1.0, 5.0])
+  n = len(t_g)
+  d = B.render_batch(ms, 0, B.pack_poses(R, t_g), _cams(K, n), 480, 640).cpu().numpy()
+  assert np.isfinite(d).all() and (d >= 0).all()
+  assert not d[1].any() and not d[2].any() and d[3].any()
+  for i in (0, 3):
+    ref = renderer_oracle.render_depth(pts, faces, R[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], 480, 640, 8)
+    cov = (d[i] > 0) != (ref > 0)
+    assert cov.sum() <= 0.002 * max(1, (ref > 0).sum()) + 2, (i, int(cov.sum()))
+  depth = np.full((n, 480, 640), 1500.0, np.float32)
+  depth[4] = 0.0
+  taus = [0.05, 0.5]
+  err = B.vsd_batch(ms, 0, B.pack_poses(R, t_e), B.pack_poses(R, t_g), depth, None,
+                    np.tile(K.reshape(1, 9), (n, 1)), 15, taus).cpu().numpy()
+  assert np.isfinite(err).all()
+  assert np.array_equal(err[1], [1.0, 1.0]) and np.array_equal(err[2], [1.0, 1.0])   # empty union
+  # all-zero depth: bop19 visibility keeps every model pixel (visibility.py:44-47)
+  ren = renderer_oracle.RendererOracle(640, 480)
+  ren.add_object(1, pts=pts, faces=faces)
+  for i in (3, 4):
+    ref = po.vsd(R[i], t_e[i].reshape(3, 1), R[i], t_g[i].reshape(3, 1), depth[i], K, 15, taus, True, 200.0,
+                 ren, 1, 'step')
+    assert np.all(np.abs(err[i] - np.array(ref)) <= 1e-3), (i, err[i], ref)
+  # point errors are plain arithmetic behind the camera too
+  mssd = B.mssd_batch(ms, 0, B.pack_poses(R, t_e), B.pack_poses(R, t_g)).cpu().numpy()
+  assert np.allclose(mssd, np.linalg.norm([2.0, 1.0, 5.0]), rtol=1e-6)
+
+
+def test_tau_limit_and_chunking(B):
+  from bop_toolkit_b200 import _lib, synth
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(24, 48, 200.0, seed=6)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(6, seed=7, z_range=(400.0, 900.0), outlier_frac=0.0)
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  dg = B.render_batch(ms, 0, pg, _cams(K, 6), 480, 640)
+  depth = dg.clone()
+  depth[depth == 0] = 1400.0
+  taus = [0.01 * (k + 1) for k in range(2 * _lib.BOP_MAX_TAUS + 3)]     # three launches
+  Ks = np.tile(K.reshape(1, 9), (6, 1))
+  full = B.vsd_batch(ms, 0, pe, pg, depth, None, Ks, 15, taus).cpu().numpy()
+  assert full.shape == (6, len(taus))
+  for k in (0, _lib.BOP_MAX_TAUS - 1, _lib.BOP_MAX_TAUS, len(taus) - 1):
+    one = B.vsd_batch(ms, 0, pe, pg, depth, None, Ks, 15, [taus[k]]).cpu().numpy()
+    assert np.array_equal(one[:, 0], full[:, k])
+  assert np.all(np.diff(full, axis=1) <= 0)          # step cost is monotone in tau
+  prm = B.make_vsd_params(480, 640, 15, taus[:_lib.BOP_MAX_TAUS])
+  prm.n_taus = _lib.BOP_MAX_TAUS + 1                  # one launch refuses more than its limit
+  import ctypes
+  import torch
+  out = torch.empty((6, _lib.BOP_MAX_TAUS + 1), dtype=torch.float64, device='cuda')
+  wsb = _lib.lib().bop_vsd_workspace_bytes(6, 480, 640, ms.max_pts)
+  ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
+  oi = torch.zeros(6, dtype=torch.int32, device='cuda')
+  ii = torch.arange(6, dtype=torch.int32, device='cuda')
+  rc = _lib.lib().bop_vsd_dev(ms.table.data_ptr(), oi.data_ptr(), torch.from_numpy(pe).cuda().data_ptr(),
+                              torch.from_numpy(pg).cuda().data_ptr(), depth.data_ptr(), None, ii.data_ptr(),
+                              torch.from_numpy(Ks).cuda().data_ptr(), None, 6, ms.max_pts, ctypes.byref(prm),
+                              out.data_ptr(), None, ws.data_ptr(), wsb, None)
+  assert rc != 0 and _lib.lib().bop_last_error()
+
+
+def test_full_size_properties(B):
+  """BASELINE.json configs[1] size: 10,000 pairs, 8 models of 4,902 vertices."""
+  import torch
+  from bop_toolkit_b200 import misc, synth
+  K = synth.LM_K
+  P, n_im = 10000, 48
+  ms = B.ModelSet()
+  syms = []
+  for k in range(8):
+    pts, faces = synth.make_mesh(50, 100, 120.0 + 20 * k, seed=20 + k)
+    info = {'diameter': 120.0 + 20 * k}
+    if k < 3:
+      info['symmetries_discrete'] = synth.discrete_z_symmetries(4)
+    s = misc.get_symmetry_transformations(info, 0.01)
+    syms.append(s)
+    ms.add(k + 1, pts, faces, s, info['diameter'])
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(P, seed=77, z_range=(450.0, 1400.0), outlier_frac=0.05)
+  obj = (np.arange(P) % 8).astype(np.int32)
+  im = (np.arange(P) % n_im).astype(np.int32)
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  Ks = np.tile(K.reshape(1, 9), (n_im, 1))
+  # test images: the GT render of the first pair that uses the image over a far background
+  first = np.array([np.flatnonzero(im == i)[0] for i in range(n_im)])
+  depth = B.render_batch(ms, obj[first], pg[first], _cams(K, n_im), 480, 640)
+  depth[depth == 0] = 1800.0
+  taus = [0.05 * (k + 1) for k in range(10)]
+
+  def run(order):
+    v, c = B.vsd_batch(ms, obj[order], pe[order], pg[order], depth, im[order], Ks, 15, taus, True, 'step',
+                       gate=True, return_counts=True)
+    return (v, c, B.mssd_batch(ms, obj[order], pe[order], pg[order], gate=True),
+            B.mspd_batch(ms, obj[order], pe[order], pg[order], K),
+            B.add_batch(ms, obj[order], pe[order], pg[order]))
+
+  ident = np.arange(P)
+  perm = np.random.default_rng(5).permutation(P)
+  a, b = run(ident), run(perm)
+  pt = torch.from_numpy(perm).cuda()
+  for x, y in zip(a, b):
+    assert torch.equal(x[pt], y)                       # batch composition does not matter
+  # VSD of the GT pose against itself: 0 where anything is visible, 1 where the union is empty
+  v, c = B.vsd_batch(ms, obj, pg, pg, depth, im, Ks, 15, taus, True, 'step', return_counts=True)
+  v, c = v.cpu().numpy(), c.cpu().numpy()
+  vis = c[:, 0] > 0
+  assert vis.sum() > 0.5 * P
+  assert np.all(v[vis] == 0.0) and np.all(v[~vis] == 1.0) and np.all(c[:, 2:] == 0)
+  assert np.array_equal(c[:, 0], c[:, 1])              # union == intersection
+  # GT composed with a model symmetry: MSSD / MSPD see the same pose (float rounding only)
+  R_s, t_s = R_g.copy(), t_g.copy()
+  for i in range(P):
+    s = syms[obj[i]][i % len(syms[obj[i]])]
+    R_s[i] = R_g[i] @ s['R']
+    t_s[i] = R_g[i] @ s['t'][:, 0] + t_g[i]
+  ps = B.pack_poses(R_s, t_s)
+  assert float(B.mssd_batch(ms, obj, ps, pg).max()) < 1e-3       # mm, at |t| ~ 1e3 mm
+  assert float(B.mspd_batch(ms, obj, ps, pg, K).max()) < 1e-3    # px
+  # ADD >= MSSD-without-symmetry is not a theorem, but max >= mean is: max over points (MSSD of
+  # the identity symmetry alone) bounds the mean (ADD) from above for the 5 asymmetric models
+  add, mssd = a[4].cpu().numpy(), a[2].cpu().numpy()
+  asym = (obj >= 3) & np.isfinite(mssd)
+  assert np.all(mssd[asym] >= add[asym] * (1 - 1e-6))
