@@ -99,6 +99,7 @@ class ModelSet(object):
     self._index = {}     # obj_id -> row
     self._table = None
     self.max_pts = 1
+    self.max_geom = 1      # max(n_pts, ceil(n_faces / 2)): sizes the rasteriser's geometry scratch
     self.max_syms = 1
     self.info = {}       # obj_id -> dict(n_pts, n_faces, n_syms, diameter)
 
@@ -162,6 +163,7 @@ class ModelSet(object):
       self._rows.append(row)
     self._keep.append(keep)
     self.max_pts = max(self.max_pts, n)
+    self.max_geom = max(self.max_geom, n, (nf + 1) // 2)
     self.max_syms = max(self.max_syms, ns)
     self.info[obj_id] = dict(n_pts=n, n_faces=nf, n_syms=ns, diameter=float(diameter), cull=0)
     self._table = None
@@ -399,7 +401,7 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
       diam = to_device(np.ascontiguousarray(np.broadcast_to(
         np.asarray(diameter_override, dtype=np.float64), (n,))), torch.float64, dev, (n,))
   outs, cnts = [], []
-  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W, models.max_pts)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, H, W, models.max_geom)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     for chunk in _tau_chunks(taus):
@@ -410,7 +412,7 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
       rc = _lib.lib().bop_vsd_dev(
         models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
         sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
-        diam.data_ptr() if diam is not None else None, n, models.max_pts,
+        diam.data_ptr() if diam is not None else None, n, models.max_geom,
         ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
         ws.data_ptr(), wsb, _stream_ptr())
       _lib.check(rc)
@@ -485,11 +487,11 @@ def render_batch(models, obj, poses, cams, height, width):
   if c.numel() == 4:
     c = c.reshape(1, 4).expand(n, 4).contiguous()
   out = torch.empty((n, int(height), int(width)), dtype=torch.float32, device=dev)
-  wsb = _lib.lib().bop_render_workspace_bytes(n, int(height), int(width), models.max_pts)
+  wsb = _lib.lib().bop_render_workspace_bytes(n, int(height), int(width), models.max_geom)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     rc = _lib.lib().bop_render_depth_dev(models.table.data_ptr(), oi.data_ptr(), p.data_ptr(),
-                                         c.data_ptr(), n, models.max_pts, int(height), int(width),
+                                         c.data_ptr(), n, models.max_geom, int(height), int(width),
                                          out.data_ptr(),
                                          ws.data_ptr(), wsb, _stream_ptr())
   _lib.check(rc)
@@ -519,12 +521,12 @@ def mask_overlap_batch(models, obj, pose_est, pose_gt, K, height, width, gate=Fa
          'cou_bb': torch.empty(n, dtype=torch.float64, device=dev),
          'counts': torch.empty((n, 4), dtype=torch.int64, device=dev),
          'bbox': torch.empty((n, 8), dtype=torch.int32, device=dev)}
-  wsb = _lib.lib().bop_vsd_workspace_bytes(n, int(height), int(width), models.max_pts)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(n, int(height), int(width), models.max_geom)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     rc = _lib.lib().bop_mask_overlap_dev(
       models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), cams.data_ptr(), n,
-      models.max_pts, int(height), int(width), int(bool(gate)), out['cus'].data_ptr(),
+      models.max_geom, int(height), int(width), int(bool(gate)), out['cus'].data_ptr(),
       out['cou_bb'].data_ptr(), out['counts'].data_ptr(), out['bbox'].data_ptr(), ws.data_ptr(),
       wsb, _stream_ptr())
   _lib.check(rc)
@@ -598,12 +600,12 @@ def gt_info_batch(models, obj, pose_gt, depth_test, im_idx, K, delta=15, depth_s
   if want_masks:
     out['mask'] = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
     out['mask_visib'] = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
-  wsb = _lib.lib().bop_gt_info_workspace_bytes(n, H, W, mx, my, models.max_pts)
+  wsb = _lib.lib().bop_gt_info_workspace_bytes(n, H, W, mx, my, models.max_geom)
   ws = _workspace(dev, wsb)
   with torch.cuda.device(dev):
     rc = _lib.lib().bop_gt_info_dev(
       models.table.data_ptr(), oi.data_ptr(), p.data_ptr(), dd.data_ptr(),
-      sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(), n, models.max_pts,
+      sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(), n, models.max_geom,
       H, W, code, float(delta), mx, my, out['counts'].data_ptr(), out['visib_fract'].data_ptr(),
       out['bbox'].data_ptr(), out['mask'].data_ptr() if want_masks else None,
       out['mask_visib'].data_ptr() if want_masks else None, ws.data_ptr(), wsb, _stream_ptr())

@@ -284,9 +284,10 @@ extern "C" int bop_render_depth_host(const bop_model_dev* model_dev, const doubl
   RC(zeros_i32(oi, n)); RC(o.alloc(ob));
   bop_model_dev mh;
   BOP_CUDA(cudaMemcpy(&mh, model_dev, sizeof(mh), cudaMemcpyDeviceToHost));
-  const size_t wsb = bop_render_workspace_bytes(n, height, width, mh.n_pts);
+  const int max_geom = mh.n_pts > (mh.n_faces + 1) / 2 ? mh.n_pts : (mh.n_faces + 1) / 2;
+  const size_t wsb = bop_render_workspace_bytes(n, height, width, max_geom);
   RC(ws.alloc(wsb));
-  RC(bop_render_depth_dev(model_dev, oi.as<int32_t>(), p.as<double>(), c.as<double>(), n, mh.n_pts,
+  RC(bop_render_depth_dev(model_dev, oi.as<int32_t>(), p.as<double>(), c.as<double>(), n, max_geom,
                           height, width, o.as<float>(), ws.p, wsb, nullptr));
   return download(depth_out, o.p, ob);
 }
@@ -312,10 +313,11 @@ extern "C" int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_e
   RC(zeros_i32(oi, n_pairs)); RC(e.alloc(eb));
   bop_model_dev mh;
   BOP_CUDA(cudaMemcpy(&mh, model_dev, sizeof(mh), cudaMemcpyDeviceToHost));
-  const size_t wsb = bop_vsd_workspace_bytes(n_pairs, prm->height, prm->width, mh.n_pts);
+  const int max_geom = mh.n_pts > (mh.n_faces + 1) / 2 ? mh.n_pts : (mh.n_faces + 1) / 2;
+  const size_t wsb = bop_vsd_workspace_bytes(n_pairs, prm->height, prm->width, max_geom);
   RC(ws.alloc(wsb));
   RC(bop_vsd_dev(model_dev, oi.as<int32_t>(), pe.as<double>(), pg.as<double>(), d.p,
                  depth_scale ? sc.as<float>() : nullptr, ii.as<int32_t>(), kk.as<double>(), nullptr, n_pairs,
-                 mh.n_pts, prm, e.as<double>(), nullptr, ws.p, wsb, nullptr));
+                 max_geom, prm, e.as<double>(), nullptr, ws.p, wsb, nullptr));
   return download(errors_out, e.p, eb);
 }

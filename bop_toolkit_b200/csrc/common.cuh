@@ -70,6 +70,20 @@ __device__ __forceinline__ uint2 ld_stream_u2(const void* p) {
   return r;
 }
 
+// Streaming loads of the assembled-triangle list (written once, read once per row band).
+__device__ __forceinline__ int4 ld_stream_i4(const int4* p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ld_stream_f1(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+
 // 3x3 helpers on row-major doubles.
 __device__ __forceinline__ void mat3_mul(const double* A, const double* B, double* C) {
 #pragma unroll

@@ -15,6 +15,7 @@
 // the reference's dtype ladder operation by operation, so given equal rendered
 // depths the integer counts -- and hence the errors -- are bit-identical to numpy's.
 #include <limits.h>
+#include <stddef.h>
 
 #include "raster.cuh"
 
@@ -37,8 +38,7 @@ struct PairDesc {
   double diameter;
   int x0, y0, w, h;       // union ROI; x0 and w are multiples of 4
   int obj, im;
-  int n_poses;
-  int cull_ok;            // bit p: back-face culling may be applied to pose p (camera outside the model)
+  int n_poses, pad;
 };
 
 struct WorkItem {
@@ -76,35 +76,63 @@ __device__ __forceinline__ void make_posecam(const double* pose, double fx, doub
 }
 
 // ---------------------------------------------------------------------------------
-// Pass A: project every vertex ONCE per (item, pose) into a 16-byte PVert record (snapped window
-// position + 1/Z) and reduce the exact projected bounding box.  One warp per (item, pose);
-// coalesced 128-bit loads and stores.
+// Pass A (geometry): one CTA per (item, pose).
+//   1. project every vertex ONCE into a 16-byte PVert record (snapped window position + 1/Z) held
+//      in shared memory (global scratch for models above kSmemVerts) and reduce the exact
+//      projected bounding box;
+//   2. assemble the triangles: gather the three records of every face, drop what can never
+//      produce a pixel -- a vertex behind the camera plane, no pixel centre inside the image under
+//      its bounding box, zero area, back-facing on a verified closed mesh (bop_model_dev.cull,
+//      only while the camera is outside the model) -- and append the survivors to a compact list
+//      (warp ballot + one shared atomic per warp).  The order of the list is arbitrary; the z-merge
+//      of the raster pass is order-independent.
+// The raster pass then streams the list with coalesced loads and every lane holds a live
+// triangle (about 40 % of the faces of a closed model survive).
 // cam_mode 0: K is [n_im][9] indexed through im_idx (VSD); 1: cam is [n][4] fx,fy,cx,cy (render).
-// pv out:   [n][n_poses][pv_stride] PVert
+// tri out:  [n][n_poses][tri_cap] records in three streams, tri_cnt[n][n_poses] valid
 // bbox out: [n][n_poses][4] = x0,y0,x1,y1 inclusive, clipped to the image; empty => x1 < x0.
 // ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-project_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
-               const double* __restrict__ pose_a, const double* __restrict__ pose_b,
-               const int32_t* __restrict__ im_idx, const double* __restrict__ K,
-               const double* __restrict__ diameters, int cam_mode, int n,
-               int n_poses, int H, int W, int gate, int pv_stride, PVert* __restrict__ pv,
-               int4* __restrict__ bbox, int cx_off, int cy_off) {
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (gw >= n * n_poses) return;
+constexpr int kAsmThreads = 512;
+constexpr int kSmemVerts = 12288;   // projected vertices the assemble kernel keeps in shared memory (192 KB)
+
+__device__ __forceinline__ bool tri_can_draw(const int4& r0, const int4& r1, const int4& r2, int W, int H,
+                                             int cull) {
+  if (!(r0.w & r1.w & r2.w)) return false;
+  const int minx = min(r0.x, min(r1.x, r2.x)), maxx = max(r0.x, max(r1.x, r2.x));
+  const int miny = min(r0.y, min(r1.y, r2.y)), maxy = max(r0.y, max(r1.y, r2.y));
+  if (min(W - 1, maxx >> kSubBits) < max(0, (minx + kSubOne - 1) >> kSubBits)) return false;
+  if (min(H - 1, maxy >> kSubBits) < max(0, (miny + kSubOne - 1) >> kSubBits)) return false;
+  const long long area2 = (long long)(r1.x - r0.x) * (r2.y - r0.y) - (long long)(r1.y - r0.y) * (r2.x - r0.x);
+  if (area2 == 0) return false;
+  return cull != (area2 > 0 ? -1 : 1);
+}
+
+__global__ void __launch_bounds__(kAsmThreads)
+assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
+                const double* __restrict__ pose_a, const double* __restrict__ pose_b,
+                const int32_t* __restrict__ im_idx, const double* __restrict__ K,
+                const double* __restrict__ diameters, int cam_mode, int n_poses, int H, int W, int gate,
+                int pv_stride, PVert* __restrict__ pv_global, int tri_cap, int4* __restrict__ tri_a,
+                int4* __restrict__ tri_b, float* __restrict__ tri_c, int* __restrict__ tri_cnt,
+                int4* __restrict__ bbox, int cx_off, int cy_off) {
+  extern __shared__ int4 s_pv[];
+  __shared__ int s_box[4];
+  __shared__ int s_n;
+  const int gw = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int item = gw / n_poses, which = gw - item * n_poses;
   const bop_model_dev M = models[obj_idx[item]];
   const double* pose = (which == 0 ? pose_a : pose_b) + 12 * (size_t)item;
-  if (gate && n_poses == 2) {
+  if (gate && n_poses == 2) {   // uniform over the CTA
     const double* pe = pose_a + 12 * (size_t)item;
     const double* pg = pose_b + 12 * (size_t)item;
     const double diam = diameters ? diameters[item] : M.diameter;
     if (!sphere_projections_overlap(0.5 * diam, pe + 9, pg + 9)) {
-      if (lane == 0) bbox[gw] = make_int4(0, 0, -1, -1);
+      if (tid == 0) { bbox[gw] = make_int4(0, 0, -1, -1); tri_cnt[gw] = 0; }
       return;
     }
   }
+  if (tid == 0) { s_box[0] = s_box[1] = INT_MAX; s_box[2] = s_box[3] = INT_MIN; s_n = 0; }
   double fx, fy, cx, cy;
   if (cam_mode == 0) {
     const double* Kp = K + 9 * (size_t)im_idx[item];
@@ -116,29 +144,98 @@ project_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restri
   PoseCamF P;
   make_posecam(pose, fx, fy, cx + cx_off, cy + cy_off, P);
   const float4* __restrict__ verts = (const float4*)M.verts4;
-  PVert* __restrict__ out = pv + (size_t)gw * pv_stride;
+  int4* const pvs = (M.n_pts <= kSmemVerts) ? s_pv : (int4*)(pv_global + (size_t)gw * pv_stride);
+  __syncthreads();
   int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
-  for (int i = lane; i < M.n_pts; i += 32) {
-    const PVert v = project_vertex(P, __ldg(verts + i));
-    *(int4*)(out + i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
-    if (v.valid) {
-      minx = min(minx, v.x); maxx = max(maxx, v.x);
-      miny = min(miny, v.y); maxy = max(maxy, v.y);
+  for (int i0 = tid; i0 < M.n_pts; i0 += 4 * kAsmThreads) {
+    float4 vin[4];   // four loads in flight before the first store (pvs may alias as far as nvcc knows)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = i0 + k * kAsmThreads;
+      vin[k] = i < M.n_pts ? __ldg(verts + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = i0 + k * kAsmThreads;
+      if (i < M.n_pts) {
+        const PVert v = project_vertex(P, vin[k]);
+        pvs[i] = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
+        if (v.valid) {
+          minx = min(minx, v.x); maxx = max(maxx, v.x);
+          miny = min(miny, v.y); maxy = max(maxy, v.y);
+        }
+      }
     }
   }
   minx = __reduce_min_sync(BOP_FULL_MASK, minx); miny = __reduce_min_sync(BOP_FULL_MASK, miny);
   maxx = __reduce_max_sync(BOP_FULL_MASK, maxx); maxy = __reduce_max_sync(BOP_FULL_MASK, maxy);
-  if (lane == 0) {
+  if (lane == 0 && maxx >= minx) {
+    atomicMin(&s_box[0], minx); atomicMin(&s_box[1], miny);
+    atomicMax(&s_box[2], maxx); atomicMax(&s_box[3], maxy);
+  }
+  __syncthreads();   // records (shared or this CTA's global scratch) and the box are complete
+  if (tid == 0) {
     int4 b = make_int4(0, 0, -1, -1);
-    if (maxx >= minx) {
-      b.x = max(0, (minx + kSubOne - 1) >> kSubBits);
-      b.y = max(0, (miny + kSubOne - 1) >> kSubBits);
-      b.z = min(W - 1, maxx >> kSubBits);
-      b.w = min(H - 1, maxy >> kSubBits);
+    if (s_box[2] >= s_box[0]) {
+      b.x = max(0, (s_box[0] + kSubOne - 1) >> kSubBits);
+      b.y = max(0, (s_box[1] + kSubOne - 1) >> kSubBits);
+      b.z = min(W - 1, s_box[2] >> kSubBits);
+      b.w = min(H - 1, s_box[3] >> kSubBits);
       if (b.z < b.x || b.w < b.y) b = make_int4(0, 0, -1, -1);
     }
     bbox[gw] = b;
   }
+  // Culling is only output-preserving while the camera centre is outside the mesh: require it
+  // outside the model's bounding sphere (|t| = distance of the camera from the model origin).
+  int cull = M.cull;
+  if (cull) {
+    const double r = (double)M.cull_min_dist;
+    if (!(pose[9] * pose[9] + pose[10] * pose[10] + pose[11] * pose[11] > r * r)) cull = 0;
+  }
+  const int4* __restrict__ faces = (const int4*)M.faces4;
+  const int F = M.n_faces;
+  const size_t out0 = (size_t)gw * tri_cap;
+  // Two faces per thread and iteration: both index loads and all six record gathers are in
+  // flight before the first test, and one shared atomic serves both ballots.
+  int4 na4 = make_int4(0, 0, 0, 0), nb4 = na4;   // indices of the NEXT iteration (prefetched)
+  if (tid < F) na4 = __ldg(faces + tid);
+  if (tid + kAsmThreads < F) nb4 = __ldg(faces + tid + kAsmThreads);
+  for (int f0 = 0; f0 < F; f0 += 2 * kAsmThreads) {
+    const int fa = f0 + tid, fb = fa + kAsmThreads;
+    const int4 ia = na4, ib = nb4;
+    if (fa + 2 * kAsmThreads < F) na4 = __ldg(faces + fa + 2 * kAsmThreads);
+    if (fb + 2 * kAsmThreads < F) nb4 = __ldg(faces + fb + 2 * kAsmThreads);
+    bool acc_a = false, acc_b = false;
+    int4 a0, a1, a2, b0, b1, b2;
+    if (fa < F) { a0 = pvs[ia.x]; a1 = pvs[ia.y]; a2 = pvs[ia.z]; }
+    if (fb < F) { b0 = pvs[ib.x]; b1 = pvs[ib.y]; b2 = pvs[ib.z]; }
+    if (fa < F) acc_a = tri_can_draw(a0, a1, a2, W, H, cull);
+    if (fb < F) acc_b = tri_can_draw(b0, b1, b2, W, H, cull);
+    const unsigned ma = __ballot_sync(BOP_FULL_MASK, acc_a), mb = __ballot_sync(BOP_FULL_MASK, acc_b);
+    if (ma | mb) {
+      const int na = __popc(ma);
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&s_n, na + __popc(mb));
+      base = __shfl_sync(BOP_FULL_MASK, base, 0);
+      const unsigned lt = (1u << lane) - 1u;
+      if (acc_a) {
+        const int slot = base + __popc(ma & lt);
+        if (slot >= tri_cap) __trap();   // caller passed a max_geom below (n_faces + 1) / 2: fail loudly
+        tri_a[out0 + slot] = make_int4(a0.x, a0.y, a1.x, a1.y);
+        tri_b[out0 + slot] = make_int4(a2.x, a2.y, a0.z, a1.z);
+        tri_c[out0 + slot] = __int_as_float(a2.z);
+      }
+      if (acc_b) {
+        const int slot = base + na + __popc(mb & lt);
+        if (slot >= tri_cap) __trap();
+        tri_a[out0 + slot] = make_int4(b0.x, b0.y, b1.x, b1.y);
+        tri_b[out0 + slot] = make_int4(b2.x, b2.y, b0.z, b1.z);
+        tri_c[out0 + slot] = __int_as_float(b2.z);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) tri_cnt[gw] = s_n;
 }
 
 // ---------------------------------------------------------------------------------
@@ -161,17 +258,7 @@ __global__ void plan_kernel(const bop_model_dev* __restrict__ models,
   D.obj = obj;
   D.diameter = diameters ? diameters[i] : models[obj].diameter;
   D.n_poses = n_poses;
-  {
-    // Culling is only output-preserving while the camera centre is outside the mesh: require it
-    // outside the model's bounding sphere (|t| = distance of the camera from the model origin).
-    const double r = (double)models[obj].cull_min_dist;
-    int ok = 0;
-    for (int p = 0; p < n_poses; ++p) {
-      const double* t = (p == 0 ? pose_a : pose_b) + 12 * (size_t)i + 9;
-      if (t[0] * t[0] + t[1] * t[1] + t[2] * t[2] > r * r) ok |= 1 << p;
-    }
-    D.cull_ok = ok;
-  }
+  D.pad = 0;
   double fx, fy, cx, cy;
   if (cam_mode == 0) {
     D.im = im_idx[i];
@@ -353,8 +440,13 @@ struct FusedArgs {
   const PairDesc* desc;
   const WorkItem* work;
   PlanCounters* ctr;
-  const PVert* pv;              // [n][n_poses][pv_stride] projected vertices
-  int pv_stride;
+  // Assembled triangles (assemble_kernel): [n][n_poses][tri_cap] records in three streams,
+  // tri_cnt[n][n_poses] of them valid.  ta = (x0,y0,x1,y1), tb = (x2,y2,iz0,iz1), tc = iz2.
+  const int4* tri_a;
+  const int4* tri_b;
+  const float* tri_c;
+  const int* tri_cnt;
+  int tri_cap;
   const void* depth_test;       // VSD
   const float* depth_scale;     // VSD, u16 input only
   unsigned long long* counts;   // VSD step: [n][2+BOP_MAX_TAUS] u64
@@ -386,6 +478,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
   __shared__ unsigned s_ticket;
   __shared__ int s_q;
   __shared__ int s_next;
+  __shared__ int s_nt[2];   // assembled triangles of pose 0 / 1 of the current pair
   __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS];
   __shared__ double s_sum[BOP_MAX_TAUS];
 
@@ -411,6 +504,11 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int* src = (const int*)(a.desc + sW.pair);
       int* dst = (int*)&sD;
       for (int i = tid; i < (int)(sizeof(PairDesc) / 4); i += nthr) dst[i] = src[i];
+      if (tid >= nthr - 2) {   // last two threads: triangle counts (n_poses is 1 or 2)
+        const int p = tid - (nthr - 2);
+        const int np = src[offsetof(PairDesc, n_poses) / 4];
+        s_nt[p] = p < np ? a.tri_cnt[(size_t)sW.pair * np + p] : 0;
+      }
     }
     __syncthreads();
     const int w = sD.w, nrows = sW.nrows;
@@ -431,38 +529,30 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
     __syncthreads();
 
-    const bop_model_dev M = a.models[sD.obj];
-    const int4* __restrict__ faces = (const int4*)M.faces4;
-    const int F = M.n_faces;
-    const int cull_ok = sD.cull_ok;
-    const int cull_m = M.cull;
-
-    // One loop over the triangles of BOTH poses (they draw into different z-tiles, so no barrier
-    // is needed between them).  Triangles with many candidate pixels are deferred to a queue and
-    // drawn warp-cooperatively afterwards.
-    const PVert* __restrict__ pv_base = a.pv + (size_t)sW.pair * n_poses * a.pv_stride;
-    const int nF = F * n_poses;
+    // One loop over the assembled triangles of BOTH poses (they draw into different z-tiles, so
+    // no barrier is needed between them).  Triangles with many candidate pixels are deferred to
+    // a queue and drawn warp-cooperatively afterwards.
+    const size_t t_base = (size_t)sW.pair * n_poses * a.tri_cap;
+    const int nT0 = s_nt[0];
+    const int nT = nT0 + s_nt[1];
     // Warps claim 32 consecutive triangles at a time from a shared ticket: triangle cost varies
-    // (0 .. small_tri_px candidate pixels), static striding leaves warps idle at the barrier.
+    // (1 .. small_tri_px candidate pixels), static striding leaves warps idle at the barrier.
     for (;;) {
       int base = 0;
       if (lane == 0) base = atomicAdd(&s_next, 32);
       base = __shfl_sync(BOP_FULL_MASK, base, 0);
-      if (base >= nF) break;
+      if (base >= nT) break;
       const int g = base + lane;
-      if (g < nF) {
-        const int p = g >= F ? 1 : 0;
-        const int f = g - p * F;
-        const int cull = ((cull_ok >> p) & 1) ? cull_m : 0;
-        const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
-        const int4 fi = __ldg(faces + f);
-        const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
-                   r2 = __ldg((const int4*)(pv + fi.z));
-        const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
-        const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
-        const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
+      if (g < nT) {
+        const int p = g >= nT0 ? 1 : 0;
+        const size_t ti = t_base + (size_t)p * a.tri_cap + (g - p * nT0);
+        const int4 ra = ld_stream_i4(a.tri_a + ti), rb = ld_stream_i4(a.tri_b + ti);
+        const float rc = ld_stream_f1(a.tri_c + ti);
+        const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
+        const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
+        const PVert v2 = {rb.x, rb.y, rc, 1};
         TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T, cull);
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
         if (n != 0) {
           unsigned* const z = zt + (size_t)p * a.tile_px;
           if (n > 0 && n <= a.small_tri_px) {
@@ -475,7 +565,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
               tri_raster_small(T, z, cx0, cy0, w);
             } else {
               TriSetup64 T64;
-              if (tri_setup64(v0, v1, v2, T, T64, cull)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+              if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
             }
           }
         }
@@ -486,23 +576,21 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int nq = min(s_q, kQueueCap);
       for (int qi = warp; qi < nq; qi += nwarps) {
         const int g = queue[qi];
-        const int p = g >= F ? 1 : 0;
-        const int cull = ((cull_ok >> p) & 1) ? cull_m : 0;
-        const PVert* __restrict__ pv = pv_base + (size_t)p * a.pv_stride;
-        const int4 fi = __ldg(faces + (g - p * F));
-        const int4 r0 = __ldg((const int4*)(pv + fi.x)), r1 = __ldg((const int4*)(pv + fi.y)),
-                   r2 = __ldg((const int4*)(pv + fi.z));
-        const PVert v0 = {r0.x, r0.y, __int_as_float(r0.z), r0.w};
-        const PVert v1 = {r1.x, r1.y, __int_as_float(r1.z), r1.w};
-        const PVert v2 = {r2.x, r2.y, __int_as_float(r2.z), r2.w};
+        const int p = g >= nT0 ? 1 : 0;
+        const size_t ti = t_base + (size_t)p * a.tri_cap + (g - p * nT0);
+        const int4 ra = __ldg(a.tri_a + ti), rb = __ldg(a.tri_b + ti);
+        const float rc = __ldg(a.tri_c + ti);
+        const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
+        const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
+        const PVert v2 = {rb.x, rb.y, rc, 1};
         unsigned* const z = zt + (size_t)p * a.tile_px;
         TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T, cull);
+        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
         if (n > 0) {
           tri_raster_warp(T, lane, z, cx0, cy0, w);
         } else if (n < 0) {
           TriSetup64 T64;
-          if (tri_setup64(v0, v1, v2, T, T64, cull)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
+          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
         }
       }
     }
@@ -864,39 +952,49 @@ namespace {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-constexpr size_t kPvBudgetBytes = (size_t)2 << 30;   // projected-vertex scratch per chunk
+constexpr size_t kGeomBudgetBytes = (size_t)8 << 30;   // assembled-triangle scratch per chunk
 
 struct WsLayout {
-  size_t ctr, counts, tl, bbox, mbox, desc, work, pv, total;
+  size_t ctr, counts, tl, bbox, mbox, desc, work, tri_cnt, tri_a, tri_b, tri_c, pv, total;
   unsigned max_items;
-  int chunk;       // items processed per pass (the batch is split so that pv fits the budget)
-  int pv_stride;   // PVert records per (item, pose)
+  int chunk;       // items processed per pass (the batch is split so that the scratch fits the budget)
+  int pv_stride;   // PVert records per (item, pose) (global fallback for models above kSmemVerts)
+  int tri_cap;     // assembled triangles per (item, pose)
 };
 
-WsLayout ws_layout(int n, int H, int W, int n_poses, int max_pts) {
+// max_geom = max over the models used of max(n_pts, (n_faces + 1) / 2).
+WsLayout ws_layout(int n, int H, int W, int n_poses, int max_geom) {
   WsLayout L;
-  L.pv_stride = (max_pts + 7) & ~7;
-  const size_t per_item_pv = (size_t)n_poses * L.pv_stride * sizeof(PVert);
-  size_t chunk = kPvBudgetBytes / (per_item_pv ? per_item_pv : 1);
+  L.pv_stride = (max_geom + 7) & ~7;
+  L.tri_cap = 2 * L.pv_stride;
+  const bool pv_global = max_geom > kSmemVerts;
+  const size_t per_item_pv = pv_global ? (size_t)n_poses * L.pv_stride * sizeof(PVert) : 0;
+  const size_t per_item = per_item_pv + (size_t)n_poses * L.tri_cap * 36;
+  size_t chunk = kGeomBudgetBytes / per_item;
   if (chunk < 1) chunk = 1;
   if (chunk > (size_t)(n > 0 ? n : 1)) chunk = (size_t)(n > 0 ? n : 1);
   L.chunk = (int)chunk;
   const int c = L.chunk;
   const int wp = (W + 3) & ~3;
   const int rows_per_band = kMinTilePx / (wp > 0 ? wp : 1);
-  const size_t per_item = (size_t)H / (size_t)(rows_per_band > 0 ? rows_per_band : 1) + 2;
-  size_t mi = per_item * (size_t)c;
+  const size_t items_per = (size_t)H / (size_t)(rows_per_band > 0 ? rows_per_band : 1) + 2;
+  size_t mi = items_per * (size_t)c;
   if (mi > 0x7fffffffull) mi = 0x7fffffffull;
   L.max_items = (unsigned)mi;
+  const size_t ntri = (size_t)c * n_poses * L.tri_cap;
   size_t off = 0;
-  L.ctr = off;    off = align_up(off + sizeof(PlanCounters), 256);
-  L.counts = off; off = align_up(off + (size_t)c * (2 + BOP_MAX_TAUS) * 8, 256);
-  L.tl = off;     off = align_up(off + (size_t)c * BOP_MAX_TAUS * 8, 256);
-  L.bbox = off;   off = align_up(off + (size_t)c * 2 * sizeof(int4), 256);
-  L.mbox = off;   off = align_up(off + (size_t)c * 8 * sizeof(int), 256);
-  L.desc = off;   off = align_up(off + (size_t)c * sizeof(PairDesc), 256);
-  L.work = off;   off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
-  L.pv = off;     off = align_up(off + (size_t)c * per_item_pv, 256);
+  L.ctr = off;     off = align_up(off + sizeof(PlanCounters), 256);
+  L.counts = off;  off = align_up(off + (size_t)c * (2 + BOP_MAX_TAUS) * 8, 256);
+  L.tl = off;      off = align_up(off + (size_t)c * BOP_MAX_TAUS * 8, 256);
+  L.bbox = off;    off = align_up(off + (size_t)c * 2 * sizeof(int4), 256);
+  L.mbox = off;    off = align_up(off + (size_t)c * 8 * sizeof(int), 256);
+  L.desc = off;    off = align_up(off + (size_t)c * sizeof(PairDesc), 256);
+  L.work = off;    off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
+  L.tri_cnt = off; off = align_up(off + (size_t)c * 2 * sizeof(int), 256);
+  L.tri_a = off;   off = align_up(off + ntri * sizeof(int4), 256);
+  L.tri_b = off;   off = align_up(off + ntri * sizeof(int4), 256);
+  L.tri_c = off;   off = align_up(off + ntri * sizeof(float), 256);
+  L.pv = off;      off = align_up(off + (size_t)c * per_item_pv, 256);
   L.total = off;
   return L;
 }
@@ -935,6 +1033,14 @@ int sm_count() {
   return g_sm_count;
 }
 
+void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
+  a.tri_a = (const int4*)(ws + L.tri_a);
+  a.tri_b = (const int4*)(ws + L.tri_b);
+  a.tri_c = (const float*)(ws + L.tri_c);
+  a.tri_cnt = (const int*)(ws + L.tri_cnt);
+  a.tri_cap = L.tri_cap;
+}
+
 template <int MODE>
 int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
@@ -967,9 +1073,12 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
   int4* bbox = (int4*)(ws + L.bbox);
   const int warps = n * n_poses;
   bop_prof_begin(BOP_PROF_VSD_PLAN, s);
-  project_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K,
-                                                          diameters, cam_mode, n, n_poses, H, W, gate,
-                                                          L.pv_stride, (PVert*)(ws + L.pv), bbox, cx_off, cy_off);
+  const size_t asm_smem = (size_t)(L.pv_stride < kSmemVerts ? L.pv_stride : kSmemVerts) * sizeof(PVert);
+  BOP_CUDA(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_smem));
+  assemble_kernel<<<warps, kAsmThreads, asm_smem, s>>>(
+      models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode, n_poses, H, W, gate, L.pv_stride,
+      (PVert*)(ws + L.pv), L.tri_cap, (int4*)(ws + L.tri_a), (int4*)(ws + L.tri_b), (float*)(ws + L.tri_c),
+      (int*)(ws + L.tri_cnt), bbox, cx_off, cy_off);
   BOP_LAUNCH_CHECK();
   plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
                                               n, n_poses, H, W, g_tune.tile_px, bbox,
@@ -1012,26 +1121,26 @@ extern "C" int bop_vsd_depth_bytes_fetched(const void* workspace, int depth_dtyp
   return 0;
 }
 
-extern "C" size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_pts) {
-  return ws_layout(n_pairs, height, width, 2, max_pts).total;
+extern "C" size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_geom) {
+  return ws_layout(n_pairs, height, width, 2, max_geom).total;
 }
-extern "C" size_t bop_render_workspace_bytes(int n, int height, int width, int max_pts) {
-  return ws_layout(n, height, width, 1, max_pts).total;
+extern "C" size_t bop_render_workspace_bytes(int n, int height, int width, int max_geom) {
+  return ws_layout(n, height, width, 1, max_geom).total;
 }
 
 extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                            const double* pose_est, const double* pose_gt, const void* depth_test,
                            const float* depth_scale, const int32_t* im_idx, const double* K,
-                           const double* diameters, int n_pairs, int max_pts,
+                           const double* diameters, int n_pairs, int max_geom,
                            const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
                            void* workspace, size_t workspace_bytes, void* stream) {
   if (n_pairs <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && depth_test && im_idx && K && errors_out,
               "bop_vsd_dev: null pointer");
-  BOP_REQUIRE(max_pts >= 1, "bop_vsd_dev: max_pts must be >= 1");
+  BOP_REQUIRE(max_geom >= 1, "bop_vsd_dev: max_geom must be >= 1");
   PixParams pp;
   if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
-  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W, 2, max_pts);
+  const WsLayout L = ws_layout(n_pairs, pp.H, pp.W, 2, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_vsd_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_vsd_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
@@ -1047,8 +1156,7 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
     a.desc = (const PairDesc*)(ws + L.desc);
     a.work = (const WorkItem*)(ws + L.work);
     a.ctr = (PlanCounters*)(ws + L.ctr);
-    a.pv = (const PVert*)(ws + L.pv);
-    a.pv_stride = L.pv_stride;
+    set_geometry(a, ws, L);
     a.depth_test = depth_test;
     a.depth_scale = depth_scale;
     a.counts = (unsigned long long*)(ws + L.counts);
@@ -1074,14 +1182,14 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
 }
 
 extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
-                                    const double* pose, const double* cam, int n, int max_pts,
+                                    const double* pose, const double* cam, int n, int max_geom,
                                     int height, int width, float* depth_out, void* workspace,
                                     size_t workspace_bytes, void* stream) {
   if (n <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose && cam && depth_out, "bop_render_depth_dev: null pointer");
   BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_render_depth_dev: bad image size");
-  BOP_REQUIRE(max_pts >= 1, "bop_render_depth_dev: max_pts must be >= 1");
-  const WsLayout L = ws_layout(n, height, width, 1, max_pts);
+  BOP_REQUIRE(max_geom >= 1, "bop_render_depth_dev: max_geom must be >= 1");
+  const WsLayout L = ws_layout(n, height, width, 1, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_render_depth_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_render_depth_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
@@ -1098,8 +1206,7 @@ extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* 
     a.desc = (const PairDesc*)(ws + L.desc);
     a.work = (const WorkItem*)(ws + L.work);
     a.ctr = (PlanCounters*)(ws + L.ctr);
-    a.pv = (const PVert*)(ws + L.pv);
-    a.pv_stride = L.pv_stride;
+    set_geometry(a, ws, L);
     a.depth_out = depth_out + (size_t)c0 * height * width;
     a.max_items = L.max_items;
     a.tile_px = g_tune.tile_px;
@@ -1165,15 +1272,15 @@ extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth
 // leave the SM.  cam: [n][4] fx,fy,cx,cy per pair.
 extern "C" int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* obj_idx,
                                     const double* pose_est, const double* pose_gt,
-                                    const double* cam, int n_pairs, int max_pts, int height,
+                                    const double* cam, int n_pairs, int max_geom, int height,
                                     int width, int gate, double* cus_out, double* cou_bb_out,
                                     int64_t* counts_out, int32_t* bbox_out, void* workspace,
                                     size_t workspace_bytes, void* stream) {
   if (n_pairs <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && cam, "bop_mask_overlap_dev: null pointer");
   BOP_REQUIRE(height > 0 && width > 0 && width <= kMaxWidth, "bop_mask_overlap_dev: bad image size");
-  BOP_REQUIRE(max_pts >= 1, "bop_mask_overlap_dev: max_pts must be >= 1");
-  const WsLayout L = ws_layout(n_pairs, height, width, 2, max_pts);
+  BOP_REQUIRE(max_geom >= 1, "bop_mask_overlap_dev: max_geom must be >= 1");
+  const WsLayout L = ws_layout(n_pairs, height, width, 2, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_mask_overlap_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_mask_overlap_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
@@ -1191,8 +1298,7 @@ extern "C" int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* 
     a.desc = (const PairDesc*)(ws + L.desc);
     a.work = (const WorkItem*)(ws + L.work);
     a.ctr = (PlanCounters*)(ws + L.ctr);
-    a.pv = (const PVert*)(ws + L.pv);
-    a.pv_stride = L.pv_stride;
+    set_geometry(a, ws, L);
     a.counts = (unsigned long long*)(ws + L.counts);
     a.mask_bbox = (int*)(ws + L.mbox);
     a.max_items = L.max_items;
@@ -1285,14 +1391,14 @@ extern "C" int bop_mask_overlap_from_depth_dev(const float* depth_est, const flo
 // image size, :76-79,121-128) so that px_count_all and bbox_obj include the part of the object
 // outside the image; calc_gt_masks uses no margin.
 extern "C" size_t bop_gt_info_workspace_bytes(int n, int height, int width, int margin_x,
-                                              int margin_y, int max_pts) {
-  return ws_layout(n, height + 2 * margin_y, width + 2 * margin_x, 1, max_pts).total;
+                                              int margin_y, int max_geom) {
+  return ws_layout(n, height + 2 * margin_y, width + 2 * margin_x, 1, max_geom).total;
 }
 
 extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_idx,
                                const double* pose_gt, const void* depth_test,
                                const float* depth_scale, const int32_t* im_idx, const double* K,
-                               int n, int max_pts, int height, int width, int depth_dtype,
+                               int n, int max_geom, int height, int width, int depth_dtype,
                                double delta, int margin_x, int margin_y, int64_t* counts_out,
                                double* visib_fract_out, int32_t* bbox_out,
                                unsigned char* mask_out, unsigned char* mask_visib_out,
@@ -1305,7 +1411,7 @@ extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_i
   BOP_REQUIRE(depth_dtype == BOP_DEPTH_F32 || depth_dtype == BOP_DEPTH_U16, "bop_gt_info_dev: unknown depth dtype");
   const int cw = width + 2 * margin_x, ch = height + 2 * margin_y;
   BOP_REQUIRE(((cw + 3) & ~3) <= g_tune.tile_px, "bop_gt_info_dev: canvas wider than the z-tile");
-  const WsLayout L = ws_layout(n, ch, cw, 1, max_pts);
+  const WsLayout L = ws_layout(n, ch, cw, 1, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_gt_info_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_gt_info_dev: workspace must be 256-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
@@ -1325,8 +1431,7 @@ extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_i
     a.desc = (const PairDesc*)(ws + L.desc);
     a.work = (const WorkItem*)(ws + L.work);
     a.ctr = (PlanCounters*)(ws + L.ctr);
-    a.pv = (const PVert*)(ws + L.pv);
-    a.pv_stride = L.pv_stride;
+    set_geometry(a, ws, L);
     a.depth_test = depth_test;
     a.depth_scale = depth_scale;
     a.counts = (unsigned long long*)(ws + L.counts);

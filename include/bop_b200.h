@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BOP_B200_ABI_VERSION 3
+#define BOP_B200_ABI_VERSION 4
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
 #define BOP_MAX_SYMS_PER_CTA 32
 
@@ -146,12 +146,14 @@ int bop_adi_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * renderer_vispy.py:433-466,509-538; shaders :123-146).  One image per pose:
  * depth_out[b] is H x W float32, nearest-surface camera Z in mm at the pixel
  * centre (c+0.5, r+0.5), 0 = background.  cam: [n][4] float64 fx,fy,cx,cy.
- * max_pts: largest n_pts among the models used (sizes the projected-vertex scratch).
- * workspace: bop_render_workspace_bytes(n, H, W, max_pts) bytes of device memory, 256-byte
- * aligned.  Batches whose scratch would exceed 2 GiB are processed in several passes.   */
-size_t bop_render_workspace_bytes(int n, int height, int width, int max_pts);
+ * max_geom: max over the models used of max(n_pts, (n_faces + 1) / 2); sizes the geometry scratch
+ * (the assembled-triangle list: 2 * max_geom records of 36 bytes per pose).  A smaller value
+ * is a contract violation and traps the kernel.
+ * workspace: bop_render_workspace_bytes(n, H, W, max_geom) bytes of device memory, 256-byte
+ * aligned.  Batches whose scratch would exceed 8 GiB are processed in several passes.   */
+size_t bop_render_workspace_bytes(int n, int height, int width, int max_geom);
 int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
-                         const double* pose, const double* cam, int n, int max_pts,
+                         const double* pose, const double* cam, int n, int max_geom,
                          int height, int width, float* depth_out,
                          void* workspace, size_t workspace_bytes, void* stream);
 
@@ -164,9 +166,9 @@ int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * depth_scale: [n_im] float32 or NULL; diameters: [n_pairs] float64.
  * errors_out: [n_pairs][n_taus] float64.  counts_out (optional, may be NULL):
  * [n_pairs][2+n_taus] int64 = union, inter, per-tau cost counts (step cost).
- * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_pts) bytes (max_pts = 1 suffices for
+ * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_geom) bytes (max_geom = 1 suffices for
  * bop_vsd_from_depth_dev, which projects nothing).                              */
-size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_pts);
+size_t bop_vsd_workspace_bytes(int n_pairs, int height, int width, int max_geom);
 int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
                            const int32_t* im_idx, const double* K,
                            const float* depth_est, const float* depth_gt,
@@ -186,7 +188,7 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const double* pose_est, const double* pose_gt,
                 const void* depth_test, const float* depth_scale,
                 const int32_t* im_idx, const double* K,
-                const double* diameters, int n_pairs, int max_pts,
+                const double* diameters, int n_pairs, int max_geom,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
@@ -201,10 +203,10 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * Outputs (each may be NULL): cus_out, cou_bb_out [n_pairs] float64; counts_out [n_pairs][4]
  * int64 = union, inter, est, gt pixel counts; bbox_out [n_pairs][8] int32 = (x, y, w, h) of the
  * est then of the gt silhouette (w = xmax - xmin; w = h = -1 when empty).
- * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_pts) bytes.                      */
+ * workspace: bop_vsd_workspace_bytes(n_pairs, H, W, max_geom) bytes.                      */
 int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* obj_idx,
                          const double* pose_est, const double* pose_gt, const double* cam,
-                         int n_pairs, int max_pts, int height, int width, int gate,
+                         int n_pairs, int max_geom, int height, int width, int gate,
                          double* cus_out, double* cou_bb_out, int64_t* counts_out,
                          int32_t* bbox_out, void* workspace, size_t workspace_bytes,
                          void* stream);
@@ -230,10 +232,10 @@ int bop_mask_overlap_from_depth_dev(const float* depth_est, const float* depth_g
  * mask_out / mask_visib_out (optional) [n][H][W] uint8, 255 inside (the PNG payloads).
  * workspace: bop_gt_info_workspace_bytes(...) bytes, 256-byte aligned.                     */
 size_t bop_gt_info_workspace_bytes(int n, int height, int width, int margin_x, int margin_y,
-                                   int max_pts);
+                                   int max_geom);
 int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_idx, const double* pose_gt,
                     const void* depth_test, const float* depth_scale, const int32_t* im_idx,
-                    const double* K, int n, int max_pts, int height, int width, int depth_dtype,
+                    const double* K, int n, int max_geom, int height, int width, int depth_dtype,
                     double delta, int margin_x, int margin_y, int64_t* counts_out,
                     double* visib_fract_out, int32_t* bbox_out, unsigned char* mask_out,
                     unsigned char* mask_visib_out, void* workspace, size_t workspace_bytes,

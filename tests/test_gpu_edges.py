@@ -203,13 +203,13 @@ def test_tau_limit_and_chunking(B):
   import ctypes
   import torch
   out = torch.empty((6, _lib.BOP_MAX_TAUS + 1), dtype=torch.float64, device='cuda')
-  wsb = _lib.lib().bop_vsd_workspace_bytes(6, 480, 640, ms.max_pts)
+  wsb = _lib.lib().bop_vsd_workspace_bytes(6, 480, 640, ms.max_geom)
   ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
   oi = torch.zeros(6, dtype=torch.int32, device='cuda')
   ii = torch.arange(6, dtype=torch.int32, device='cuda')
   rc = _lib.lib().bop_vsd_dev(ms.table.data_ptr(), oi.data_ptr(), torch.from_numpy(pe).cuda().data_ptr(),
                               torch.from_numpy(pg).cuda().data_ptr(), depth.data_ptr(), None, ii.data_ptr(),
-                              torch.from_numpy(Ks).cuda().data_ptr(), None, 6, ms.max_pts, ctypes.byref(prm),
+                              torch.from_numpy(Ks).cuda().data_ptr(), None, 6, ms.max_geom, ctypes.byref(prm),
                               out.data_ptr(), None, ws.data_ptr(), wsb, None)
   assert rc != 0 and _lib.lib().bop_last_error()
 
