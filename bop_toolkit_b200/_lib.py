@@ -90,6 +90,7 @@ _SIGNATURES = {
   'bop_render_depth_host': (_I, [_P, _P, _P, _I, _I, _I, _P]),
   'bop_vsd_host': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P]),
   'bop_vsd_set_tuning': (_I, [_I, _I, _I, _I]),
+  'bop_vsd_set_exact': (_I, [_I]),
   'bop_vsd_depth_bytes_fetched': (_I, [_P, _I, _P]),
   'bop_profile_enable': (_I, [_I]),
   'bop_profile_reset': (_I, []),

@@ -22,6 +22,7 @@
 namespace {
 
 constexpr int kMinTilePx = 4096;
+constexpr int kMaxBandRows = 1024;   // rows of one work item (>= kMinTilePx / 4, the narrowest ROI)
 constexpr int kMaxWidth = 4096;
 
 struct Tuning {
@@ -286,7 +287,7 @@ __global__ void plan_kernel(const bop_model_dev* __restrict__ models,
     const int w = ((x1 + 1 - x0) + 3) & ~3;
     const int h = y1 + 1 - y0;
     D.x0 = x0; D.y0 = y0; D.w = w; D.h = h;
-    const int cap_rows = max(1, tile_px / w);
+    const int cap_rows = min(kMaxBandRows, max(1, tile_px / w));
     nb = (h + cap_rows - 1) / cap_rows;
     band = (h + nb - 1) / nb;  // balanced bands
   } else {
@@ -323,26 +324,29 @@ struct PixParams {
   int H, W;
   int depth_dtype;
   int vec_ok;        // rows of depth_test are 16-byte (f32) / 8-byte (u16) aligned
+  // float32 decision path (step cost): thresholds and their undecidable bands (see vsd_pixel_fast)
+  float tau_f[BOP_MAX_TAUS], tau_eps[BOP_MAX_TAUS];
+  int fast;          // 1: try the float32 decision path first
 };
 
 constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2, MODE_MASK = 3, MODE_GTINFO = 4;
 
-template <int MODE>
+template <int MODE, int NT>
 struct Acc {
   int uni = 0, inter = 0;
-  int c[BOP_MAX_TAUS];
+  int c[NT];
   __device__ Acc() {
 #pragma unroll
-    for (int k = 0; k < BOP_MAX_TAUS; ++k) c[k] = 0;
+    for (int k = 0; k < NT; ++k) c[k] = 0;
   }
 };
-template <>
-struct Acc<MODE_TLINEAR> {
+template <int NT>
+struct Acc<MODE_TLINEAR, NT> {
   int uni = 0, inter = 0;
-  double c[BOP_MAX_TAUS];
+  double c[NT];
   __device__ Acc() {
 #pragma unroll
-    for (int k = 0; k < BOP_MAX_TAUS; ++k) c[k] = 0.0;
+    for (int k = 0; k < NT; ++k) c[k] = 0.0;
   }
 };
 
@@ -355,9 +359,10 @@ __device__ __forceinline__ double dist_of(double X, double Y, float d) {
 }
 
 // One pixel of pose_error.vsd lines 48-91.  dt/de/dg: depth_test, rendered est, rendered gt.
-template <int MODE>
+// NT >= pp.n_taus is the compile-time length of the tau sweep; pp.taus[k >= n_taus] = +inf adds nothing.
+template <int MODE, int NT>
 __device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double Y, float dt,
-                                          float de, float dg, double diameter, Acc<MODE>& acc) {
+                                          float de, float dg, double diameter, Acc<MODE, NT>& acc) {
   const bool he = de != 0.f, hg = dg != 0.f;   // d_model > 0 on the distance image
   if (!he && !hg) return;
   const double Dt = dist_of(X, Y, dt);
@@ -383,17 +388,68 @@ __device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double 
     double d = fabs(__dsub_rn(Dg, De));
     if (pp.normalized) d = __ddiv_rn(d, diameter);
 #pragma unroll
-    for (int k = 0; k < BOP_MAX_TAUS; ++k) {
-      if (k < pp.n_taus) {
-        if (MODE == MODE_TLINEAR) {
-          double c = __ddiv_rn(d, pp.taus[k]);
-          acc.c[k] += (c > 1.0) ? 1.0 : c;
-        } else {
-          acc.c[k] += (d >= pp.taus[k]) ? 1 : 0;
-        }
+    for (int k = 0; k < NT; ++k) {
+      if (MODE == MODE_TLINEAR) {
+        double c = __ddiv_rn(d, pp.taus[k]);
+        acc.c[k] += (c > 1.0) ? 1.0 : c;
+      } else {
+        acc.c[k] += (d >= pp.taus[k]) ? 1 : 0;
       }
     }
   }
+}
+
+// Float32 decision path of vsd_pixel for the step cost.  Every quantity the reference compares is
+// |depth difference| * s with s = sqrt(1 + X^2 + Y^2) (dist = depth * s for all three images), so
+// the float64 distance images are only needed when a comparison is too close to call:
+//   visibility  fl32(D_model) - fl32(D_test) <= delta : a = (d_model - d_test) * s, undecidable
+//               within 2.5e-7 * (d_model + d_test) * s + 3e-6 * |a| of delta (float32 roundings of
+//               the two distances <= 6e-8 relative each; a itself is good to < 4e-7 relative);
+//   cost        |D_gt - D_est| (/ diameter) >= tau_k : dn = |d_gt - d_est| * s (* 1/diameter),
+//               undecidable within 3e-6 * tau_k of tau_k (dn is good to < 6e-7 relative).
+// Returns false without touching acc when anything is undecidable; the caller then runs
+// vsd_pixel.  Decided pixels get exactly the counts vsd_pixel would give them.
+// s2x = fl32(1 + X^2) of the column, yy = fl32(Y^2) of the row.
+template <int NT>
+__device__ __forceinline__ bool vsd_pixel_fast(const PixParams& pp, float s2x, float yy, float dt,
+                                               float de, float dg, float inv_diam,
+                                               Acc<MODE_STEP, NT>& acc) {
+  const bool he = de != 0.f, hg = dg != 0.f;
+  if (!he && !hg) return true;
+  float s;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(__fadd_rn(s2x, yy)));
+  const float adt = fabsf(dt);                 // the distance image of a negative depth is positive
+  const bool t_zero = adt == 0.f, t_pos = adt > 0.f;
+  const bool bop19 = pp.visib_mode == BOP_VISIB_BOP19;
+  const bool c_matters = bop19 ? !t_zero : t_pos;
+  const float ks = 2.5e-7f * s;
+  bool vg = false, ve = false;
+  if (hg) {
+    const float a = (dg - adt) * s;
+    if (c_matters && !(fabsf(a - pp.delta_f32) > fmaf(ks, dg + adt, 3e-6f * fabsf(a)))) return false;
+    const bool c = a <= pp.delta_f32;
+    vg = bop19 ? (c || t_zero) : (c && t_pos);
+  }
+  if (he) {
+    const float a = (de - adt) * s;
+    if (c_matters && !(fabsf(a - pp.delta_f32) > fmaf(ks, de + adt, 3e-6f * fabsf(a)))) return false;
+    const bool c = a <= pp.delta_f32;
+    ve = bop19 ? (c || t_zero) : (c && t_pos);
+    ve = ve || vg;
+  }
+  if (!(vg || ve)) return true;
+  if (vg && ve) {
+    const float dn = fabsf(dg - de) * s * inv_diam;
+    bool near = false;
+#pragma unroll
+    for (int k = 0; k < NT; ++k) near = near || !(fabsf(dn - pp.tau_f[k]) > pp.tau_eps[k]);
+    if (near) return false;
+    acc.inter += 1;
+#pragma unroll
+    for (int k = 0; k < NT; ++k) acc.c[k] += (dn >= pp.tau_f[k]) ? 1 : 0;
+  }
+  acc.uni += 1;
+  return true;
 }
 
 // Loads 4 horizontally adjacent depth_test samples as float32 millimetres.
@@ -465,13 +521,18 @@ struct FusedArgs {
 
 // VARIANT 0: <= 512 threads, 1 CTA/SM (up to 128 registers); VARIANT 1: up to 1024 resident
 // threads per SM (64 registers): 1024-thread CTAs or two 512-thread CTAs per SM.
-template <int MODE, int VARIANT>
+// NT: compile-time length of the tau sweep (>= pp.n_taus; only the VSD modes use it).
+template <int MODE, int VARIANT, int NT>
 __global__ void __launch_bounds__(VARIANT == 0 ? 512 : 1024, 1)
 fused_kernel(const __grid_constant__ FusedArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int wpad = (a.pp.W + 3) & ~3;
   unsigned* const zt = (unsigned*)smem_raw;                       // [2][tile_px]
-  double* const xh = (double*)(smem_raw + (size_t)2 * a.tile_px * 4);  // [wpad]
-  int* const queue = (int*)(xh + ((a.pp.W + 3) & ~3));            // [kQueueCap]
+  double* const xh = (double*)(smem_raw + (size_t)2 * a.tile_px * 4);  // [wpad]       X = (x - cx) / fx
+  double* const yh = xh + wpad;                                   // [kMaxBandRows]  Y = (y - cy) / fy
+  float* const s2x = (float*)(yh + kMaxBandRows);                 // [wpad]          fl32(1 + X^2)
+  float* const yyf = s2x + wpad;                                  // [kMaxBandRows]  fl32(Y^2)
+  int* const queue = (int*)(yyf + kMaxBandRows);                  // [kQueueCap]
 
   __shared__ PairDesc sD;
   __shared__ WorkItem sW;
@@ -523,9 +584,18 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         uint4* z4 = (uint4*)(zt + (size_t)p * a.tile_px);
         for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = inf4;
       }
-      if (MODE == MODE_STEP || MODE == MODE_TLINEAR)
-        for (int c = tid; c < w; c += nthr)
-          xh[c] = __ddiv_rn(__dsub_rn((double)(cx0 + c), sD.kcx), sD.kfx);
+      if (MODE == MODE_STEP || MODE == MODE_TLINEAR) {
+        for (int c = tid; c < w; c += nthr) {
+          const double X = __ddiv_rn(__dsub_rn((double)(cx0 + c), sD.kcx), sD.kfx);
+          xh[c] = X;
+          s2x[c] = (float)(1.0 + X * X);
+        }
+        for (int r = tid; r < nrows; r += nthr) {
+          const double Y = __ddiv_rn(__dsub_rn((double)(cy0 + r), sD.kcy), sD.kfy);   // misc.py:138
+          yh[r] = Y;
+          yyf[r] = (float)(Y * Y);
+        }
+      }
     }
     __syncthreads();
 
@@ -687,11 +757,13 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
 
     // ---- pixel pass ------------------------------------------------------------------
-    Acc<MODE> acc;
+    Acc<MODE, NT> acc;
     int n_loaded = 0;
     const int w4 = w >> 2;
     const int ngroups = nrows * w4;
     const double diameter = sD.diameter;
+    const float inv_diam = a.pp.normalized ? (float)(1.0 / diameter) : 1.f;
+    const bool fast = MODE == MODE_STEP && a.pp.fast != 0;
     const float scale = (a.pp.depth_dtype == BOP_DEPTH_U16 && a.depth_scale) ? a.depth_scale[sD.im] : 1.f;
     for (int g = tid; g < ngroups; g += nthr) {
       const int r = g / w4, c4 = g - r * w4;
@@ -707,14 +779,19 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       float dt[4];
       load_depth4(a.pp, a.depth_test, scale, sD.im, row, col, dt);
       ++n_loaded;
-      const double Y = __ddiv_rn(__dsub_rn((double)row, sD.kcy), sD.kfy);   // misc.py:138
+      const float yy = yyf[r];
       const unsigned zev[4] = {ze.x, ze.y, ze.z, ze.w};
       const unsigned zgv[4] = {zg.x, zg.y, zg.z, zg.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float de = zev[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zev[k]);
         const float dg = zgv[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zgv[k]);
-        vsd_pixel<MODE>(a.pp, xh[4 * c4 + k], Y, dt[k], de, dg, diameter, acc);
+        if (MODE == MODE_STEP) {
+          if (fast && vsd_pixel_fast<NT>(a.pp, s2x[4 * c4 + k], yy, dt[k], de, dg, inv_diam,
+                                         *(Acc<MODE_STEP, NT>*)&acc))
+            continue;
+        }
+        vsd_pixel<MODE, NT>(a.pp, xh[4 * c4 + k], yh[r], dt[k], de, dg, diameter, acc);
       }
     }
     // ---- reduce: warp shuffle -> shared atomics -> one global atomic per counter ---------
@@ -726,7 +803,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         if (nl) atomicAdd(&a.ctr->depth_groups, (unsigned long long)nl);
       }
 #pragma unroll
-      for (int k = 0; k < BOP_MAX_TAUS; ++k) {
+      for (int k = 0; k < NT; ++k) {
         if (k < a.pp.n_taus) {
           if (MODE == MODE_TLINEAR) {
             const double s = warp_sum((double)acc.c[k]);
@@ -878,7 +955,7 @@ pixel_pass_kernel(const void* __restrict__ depth_test, const float* __restrict__
   const float* pg = depth_gt + (size_t)pair * H * W;
   const bool vec = pp.vec_ok != 0;
 
-  Acc<MODE> acc;
+  Acc<MODE, BOP_MAX_TAUS> acc;
 #pragma unroll 2
   for (int j = 0; j < kK2GroupsPerThread; ++j) {
     const int g = g0 + j * kK2Threads + threadIdx.x;
@@ -909,7 +986,7 @@ pixel_pass_kernel(const void* __restrict__ depth_test, const float* __restrict__
     for (int k = 0; k < 4; ++k) {
       if (de[k] != 0.f || dg[k] != 0.f) {
         const double X = __ddiv_rn(__dsub_rn((double)(col + k), cx), fx);
-        vsd_pixel<MODE>(pp, X, Y, dt[k], de[k], dg[k], diameter, acc);
+        vsd_pixel<MODE, BOP_MAX_TAUS>(pp, X, Y, dt[k], de[k], dg[k], diameter, acc);
       }
     }
   }
@@ -999,6 +1076,8 @@ WsLayout ws_layout(int n, int H, int W, int n_poses, int max_geom) {
   return L;
 }
 
+bool g_exact_pixels = false;   // bop_vsd_set_exact: disable the float32 decision path (tests)
+
 int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams& pp) {
   BOP_REQUIRE(prm, "vsd: null params");
   BOP_REQUIRE(prm->n_taus >= 1 && prm->n_taus <= BOP_MAX_TAUS, "vsd: n_taus must be in [1, BOP_MAX_TAUS]");
@@ -1009,7 +1088,15 @@ int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams
               "Unknown visibility mode.");
   BOP_REQUIRE(prm->depth_dtype == BOP_DEPTH_F32 || prm->depth_dtype == BOP_DEPTH_U16,
               "vsd: unknown depth dtype");
-  for (int k = 0; k < BOP_MAX_TAUS; ++k) pp.taus[k] = k < prm->n_taus ? prm->taus[k] : 0.0;
+  // Unused slots hold +inf: "d >= inf" and min(d / inf, 1) add nothing, so the sweep needs no length check.
+  bool fast = prm->cost_type == BOP_COST_STEP && !g_exact_pixels && prm->delta == prm->delta;
+  for (int k = 0; k < BOP_MAX_TAUS; ++k) {
+    pp.taus[k] = k < prm->n_taus ? prm->taus[k] : (double)INFINITY;
+    pp.tau_f[k] = (float)pp.taus[k];
+    pp.tau_eps[k] = k < prm->n_taus ? 3e-6f * fabsf(pp.tau_f[k]) + 1e-30f : 0.f;
+    if (k < prm->n_taus && !(pp.taus[k] == pp.taus[k])) fast = false;   // NaN tau: exact path only
+  }
+  pp.fast = fast ? 1 : 0;
   pp.delta_f32 = (float)prm->delta;
   pp.n_taus = prm->n_taus;
   pp.normalized = prm->normalized_by_diameter;
@@ -1041,25 +1128,35 @@ void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
   a.tri_cap = L.tri_cap;
 }
 
-template <int MODE>
-int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
+template <int MODE, int NT>
+int launch_fused_nt(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
-  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 8 + (size_t)kQueueCap * 4;
+  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 12 + (size_t)kMaxBandRows * 12 + (size_t)kQueueCap * 4;
+  BOP_REQUIRE(smem <= (size_t)225 * 1024, "fused kernel: z-tile + tables exceed shared memory (lower tile_px)");
   const int grid = sm_count() * g_tune.ctas_per_sm;
   const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : ((MODE == MODE_MASK || MODE == MODE_GTINFO) ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
   const bool dense = g_tune.threads * g_tune.ctas_per_sm > 512;
   if (dense)
-    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   else
-    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 0, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   bop_prof_begin(slot, s);
   if (dense)
-    fused_kernel<MODE, 1><<<grid, g_tune.threads, smem, s>>>(a);
+    fused_kernel<MODE, 1, NT><<<grid, g_tune.threads, smem, s>>>(a);
   else
-    fused_kernel<MODE, 0><<<grid, g_tune.threads, smem, s>>>(a);
+    fused_kernel<MODE, 0, NT><<<grid, g_tune.threads, smem, s>>>(a);
   bop_prof_end(slot, s);
   BOP_LAUNCH_CHECK();
   return 0;
+}
+
+template <int MODE>
+int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
+  if (MODE == MODE_STEP) {   // the step-cost sweep is unrolled to 4, 10 (the BOP19 default) or 16 taus
+    if (a.pp.n_taus <= 4) return launch_fused_nt<MODE, 4>(a, W, s);
+    if (a.pp.n_taus <= 10) return launch_fused_nt<MODE, 10>(a, W, s);
+  }
+  return launch_fused_nt<MODE, BOP_MAX_TAUS>(a, W, s);
 }
 
 // bbox + plan; shared by VSD and render.
@@ -1108,6 +1205,13 @@ extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int
     BOP_REQUIRE(small_tri_px >= 1, "tuning: small_tri_px out of range");
     g_tune.small_tri_px = small_tri_px;
   }
+  return 0;
+}
+
+// Test hook: exact != 0 makes every pixel take the float64 path (the float32 decision path must
+// give bit-identical counts; tests compare the two).
+extern "C" int bop_vsd_set_exact(int exact) {
+  g_exact_pixels = exact != 0;
   return 0;
 }
 

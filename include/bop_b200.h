@@ -280,6 +280,10 @@ int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_est,
  * tile_px: z-tile capacity in pixels per pose (shared memory = 8*tile_px bytes);
  * threads: CTA size; ctas_per_sm: persistent CTAs per SM.  0 keeps the current value. */
 int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_px);
+/* Test hook: exact != 0 forces the float64 arithmetic of the reference for every pixel of the
+ * step-cost pass; by default a float32 pre-test decides the comparisons that are not close to
+ * their thresholds (bit-identical counts either way; tests compare the two). */
+int bop_vsd_set_exact(int exact);
 
 
 #ifdef __cplusplus

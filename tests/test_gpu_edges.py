@@ -251,6 +251,13 @@ def test_full_size_properties(B):
   ident = np.arange(P)
   perm = np.random.default_rng(5).permutation(P)
   a, b = run(ident), run(perm)
+  from bop_toolkit_b200 import _lib
+  try:                                               # float32 decision path == all-float64 pixel pass
+    _lib.check(_lib.lib().bop_vsd_set_exact(1))
+    ex = run(ident)
+  finally:
+    _lib.check(_lib.lib().bop_vsd_set_exact(0))
+  assert torch.equal(a[0], ex[0]) and torch.equal(a[1], ex[1])
   pt = torch.from_numpy(perm).cuda()
   for x, y in zip(a, b):
     assert torch.equal(x[pt], y)                       # batch composition does not matter
@@ -275,3 +282,65 @@ def test_full_size_properties(B):
   add, mssd = a[4].cpu().numpy(), a[2].cpu().numpy()
   asym = (obj >= 3) & np.isfinite(mssd)
   assert np.all(mssd[asym] >= add[asym] * (1 - 1e-6))
+
+
+def test_float32_decision_path_equals_exact(B):
+  """The step-cost pixel pass decides comparisons in float32 when they are far from their
+  thresholds and falls back to the reference's float64 arithmetic otherwise.  Counts must be
+  bit-identical to the all-float64 run (bop_vsd_set_exact) -- on a normal workload and on
+  adversarial inputs built to sit ON the thresholds: depth_test at exactly delta behind the GT
+  surface (+- a few float32 ulps) and taus equal to exact per-pixel costs."""
+  import torch
+  from bop_toolkit_b200 import _lib, synth
+  lib = _lib.lib()
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(50, 100, 180.0, seed=31)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 180.0)
+  n = 48
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=32, z_range=(400.0, 1200.0), outlier_frac=0.05)
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  cams = _cams(K, n)
+  de = B.render_batch(ms, 0, pe, cams, 480, 640).cpu().numpy()
+  dg = B.render_batch(ms, 0, pg, cams, 480, 640).cpu().numpy()
+  ys, xs = np.mgrid[0:480, 0:640]
+  s = np.sqrt(((xs - K[0, 2]) / K[0, 0]) ** 2 + ((ys - K[1, 2]) / K[1, 1]) ** 2 + 1.0)
+  delta = 15.0
+  rng = np.random.default_rng(33)
+  # depth_test: delta behind the GT surface along the ray, nudged by -3..3 float32 ulps; elsewhere far
+  dt = np.where(dg > 0, dg + (delta / s).astype(np.float32), np.float32(1500.0)).astype(np.float32)
+  steps = rng.integers(-3, 4, size=dt.shape)
+  for k in range(1, 4):
+    dt = np.where(steps >= k, np.nextafter(dt, np.float32(np.inf)), dt)
+    dt = np.where(steps <= -k, np.nextafter(dt, np.float32(-np.inf)), dt)
+  dt[:, ::7, ::5] = 0.0                                     # missing depth
+  # taus that ARE per-pixel costs (float64, as the reference computes them)
+  both = (dg > 0) & (de > 0)
+  Dg, De = dg.astype(np.float64) * s, de.astype(np.float64) * s
+  costs = np.abs(Dg - De)[both] / 180.0
+  costs = costs[(costs > 1e-4) & (costs < 0.6)]
+  taus = sorted(float(c) for c in rng.choice(costs, 10, replace=False))
+  Ks = np.tile(K.reshape(1, 9), (n, 1))
+  im = np.arange(n, dtype=np.int32)
+  results = {}
+  noisy = np.where(dg > 0, dg + rng.normal(0, 3.0, dg.shape).astype(np.float32), 1500.0).astype(np.float32)
+  try:
+    for exact in (1, 0):
+      _lib.check(lib.bop_vsd_set_exact(exact))
+      out = []
+      for depth, tt in ((dt, taus), (dt, [0.05 * (k + 1) for k in range(10)]), (noisy, taus[:3])):
+        for mode in ('bop19', 'bop18'):
+          for norm in (True, False):
+            t2 = tt if norm else [t * 180.0 for t in tt]
+            e, c = B.vsd_batch(ms, 0, pe, pg, depth, im, Ks, delta, t2, norm, 'step', mode, return_counts=True)
+            out += [e.cpu().numpy(), c.cpu().numpy()]
+      results[exact] = out
+  finally:
+    _lib.check(lib.bop_vsd_set_exact(0))
+  for a, b in zip(results[1], results[0]):
+    assert np.array_equal(a, b)
+  assert results[1][1][:, 1].sum() > 1000                    # the cases do have intersections
+  # and the exact run equals the stand-alone float64 pixel pass on the same renders
+  e, c = B.vsd_from_depth_batch(torch.from_numpy(de).cuda(), torch.from_numpy(dg).cuda(), dt, im, Ks, 180.0,
+                                delta, taus, True, 'step', 'bop19', return_counts=True)
+  assert np.array_equal(c.cpu().numpy(), results[0][1])
