@@ -26,7 +26,7 @@ constexpr int kMaxBandRows = 1024;   // rows of one work item (>= kMinTilePx / 4
 constexpr int kMaxWidth = 4096;
 
 struct Tuning {
-  int tile_px = 18432;   // z-tile capacity per pose, pixels (2 poses x 4 B = 144 KB of smem; leaves L1 for gathers)
+  int tile_px = 20480;   // z-tile capacity per pose, pixels (2 poses x 4 B = 144 KB of smem; leaves L1 for gathers)
   int threads = 1024;
   int ctas_per_sm = 1;
   int small_tri_px = 256; // triangles with more candidate pixels go to the warp-cooperative path

@@ -17,7 +17,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-DEFAULT_TUNING = (18432, 1024, 1, 256)
+DEFAULT_TUNING = (20480, 1024, 1, 256)
 
 
 @pytest.fixture(scope='module')

@@ -376,7 +376,7 @@ def test_vsd_fused_equals_render_plus_k2(B):
         else:
           assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=0, atol=1e-11)
   finally:
-    _lib.check(_lib.lib().bop_vsd_set_tuning(18432, 1024, 1, 256))
+    _lib.check(_lib.lib().bop_vsd_set_tuning(20480, 1024, 1, 256))
 
 
 def test_c_abi_host_entry_points(B, golden):
