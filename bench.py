@@ -357,6 +357,10 @@ def gpu_arm(args):
     lib.bop_profile_sum_ms(slot, args.steps, byref(s_ms), byref(s_n))
     parts[name] = s_ms.value / max(1, s_n.value)
   ms_e2e, _, win_e2e, out_e2e = timed(step_e2e, args.steps, args.warmup, sampler)
+  e2e_parts = {}
+  for name, slot in (('fused', 0), ('vsd_plan', 1), ('mssd', 2), ('mspd', 3)):
+    lib.bop_profile_sum_ms(slot, args.steps, byref(s_ms), byref(s_n))
+    e2e_parts[name] = s_ms.value / max(1, s_n.value)
   depth_pulled = batch.depth_bytes_fetched(device, _lib.DEPTH_U16)
   ms_e2e_copy, _, _, out_e2e_copy = timed(lambda: step_e2e(False), max(1, args.steps // 2), 1, sampler)
   lib.bop_profile_enable(0)
@@ -402,14 +406,14 @@ def gpu_arm(args):
     'vs_baseline': None, 'dtype': 'f32 raster + f64 pixel/vertex arithmetic', 'data': 'synthetic',
     'config': {'workload': WORKLOAD % P, 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
                'l2': 'inputs larger than L2: resident pass reads its model pixels out of %.1f GB of depth; '
-                     'e2e pass fetches ~0.28 GB of host depth and streams %.1f GB of projected-vertex '
-                     'scratch per step (L2 = 126 MB)' % (P * H * W * 4 / 1e9, P * 2 * n_verts * 32 / 1e9),
+                     'e2e pass fetches ~0.28 GB of host depth; both write and re-read ~%.1f GB of assembled-'
+                     'triangle lists per step (L2 = 126 MB)' % (P * H * W * 4 / 1e9, P * 2 * 0.4 * n_faces * 36 / 1e9),
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
                'exchange': 'all-gather of error records per step' if world > 1 else 'none',
                'cpu_affinity': bound},
     'e2e': {'value': e2e_v, 'unit': 'pairs/s', 'ms_per_step': ms_e2e / args.steps,
             'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(h_out.numel() * 8),
-            'matches_resident': same,
+            'matches_resident': same, 'kernels_ms': e2e_parts,
             'mode': 'pinned host buffers; depth pulled on demand over PCIe by the fused kernel',
             'full_copy': {'value': e2e_copy_v, 'h2d_bytes_per_step': int(h2d_copy),
                           'note': 'same call with whole-image H2D copies of the uint16 depth'}},
@@ -422,8 +426,8 @@ def gpu_arm(args):
                  'other_kernels_ms': parts,
                  'note': 'achieved = algorithmic bytes of a NON-fused pipeline (SURVEY 8d: 3 reads + 2 z-buffer '
                          'writes of H*W*4 B + mesh) / kernel time, so frac > 1 means the fusion removed that '
-                         'traffic: `traffic` is the DRAM bytes ncu measured (3-4 % of DRAM bandwidth). The '
-                         'kernel is bound by instruction issue (ncu: issue slots 64-69 % busy, 19 of 32 lanes '
+                         'traffic: `traffic` is the DRAM bytes ncu measured (8 % of DRAM bandwidth). The '
+                         'kernel is bound by instruction issue (ncu: issue slots 66 % busy, 17 of 32 lanes '
                          'active); see DESIGN.md section 4.'},
   }
   if world == 1 and not args.no_cpu_baseline:
