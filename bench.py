@@ -46,10 +46,21 @@ def build_models():
   return models
 
 
-def build_pairs(n_pairs, seed):
+def build_pairs(n_pairs, seed, n_images=0):
+  """n_images = 0: every pair has its own image (cfg2 as quoted).  n_images > 0: the "shared
+  depth_test" variant of SURVEY 8d -- n_images images with one GT instance each and
+  n_pairs / n_images estimates per instance (the perturbations of the per-pair workload applied
+  to the image's GT pose)."""
   from bop_toolkit_b200 import synth
   R_e, t_e, R_g, t_g = synth.make_pose_pairs(n_pairs, seed=seed)
   obj = (np.arange(n_pairs) % N_OBJ).astype(np.int32)
+  if n_images:
+    per = n_pairs // n_images
+    first = (np.arange(n_pairs) // per) * per          # the pair whose GT the image shows
+    dR = np.einsum('nji,njk->nik', R_g, R_e)           # R_g^T R_e
+    dt = t_e - t_g
+    R_g, t_g, obj = R_g[first], t_g[first], obj[first]
+    R_e, t_e = np.einsum('nij,njk->nik', R_g, dR), t_g + dt
   return R_e, t_e, R_g, t_g, obj
 
 
@@ -265,7 +276,10 @@ def gpu_arm(args):
   for m in models:
     ms.add(m['obj_id'], m['pts'], m['faces'], m['syms'], m['diameter'])
   n_verts, n_faces = models[0]['pts'].shape[0], models[0]['faces'].shape[0]
-  R_e, t_e, R_g, t_g, obj_np = build_pairs(P, seed=rank)
+  n_images = args.images if args.images else P
+  assert P % n_images == 0, '--images must divide --pairs'
+  per_im = P // n_images
+  R_e, t_e, R_g, t_g, obj_np = build_pairs(P, seed=rank, n_images=args.images)
   pe_np, pg_np = batch.pack_poses(R_e, t_e), batch.pack_poses(R_g, t_g)
   diam_np = np.array([models[o]['diameter'] for o in obj_np])
   gate_ok = np.array([misc.overlapping_sphere_projections(0.5 * diam_np[i], t_e[i], t_g[i]) for i in range(P)])
@@ -273,18 +287,20 @@ def gpu_arm(args):
 
   pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
   h_pe, h_pg, h_obj = pin(pe_np), pin(pg_np), pin(obj_np)
-  h_im = pin(np.arange(P, dtype=np.int32))
-  h_K = pin(np.tile(K.reshape(1, 9), (P, 1)))
-  h_scale = pin(np.full(P, DEPTH_SCALE, dtype=np.float32))
+  h_im = pin((np.arange(P) // per_im).astype(np.int32))
+  h_K = pin(np.tile(K.reshape(1, 9), (n_images, 1)))
+  h_Kp = h_K if n_images == P else pin(np.tile(K.reshape(1, 9), (P, 1)))   # mspd takes K per pair
+  h_scale = pin(np.full(n_images, DEPTH_SCALE, dtype=np.float32))
   d_pe, d_pg, d_obj = h_pe.to(device), h_pg.to(device), h_obj.to(device)
-  d_im, d_K = h_im.to(device), h_K.to(device)
-  d16 = make_depth_gpu(batch, torch, ms, d_obj, d_pg, torch.from_numpy(t_g).to(device),
-                       torch.from_numpy(diam_np).to(device), K, device, seed=1234 + rank)
-  h_d16 = torch.empty((P, H, W), dtype=torch.int16).pin_memory()
+  d_im, d_K, d_Kp = h_im.to(device), h_K.to(device), h_Kp.to(device)
+  d16 = make_depth_gpu(batch, torch, ms, d_obj[::per_im].contiguous(), d_pg[::per_im].contiguous(),
+                       torch.from_numpy(t_g[::per_im].copy()).to(device),
+                       torch.from_numpy(diam_np[::per_im].copy()).to(device), K, device, seed=1234 + rank)
+  h_d16 = torch.empty((n_images, H, W), dtype=torch.int16).pin_memory()
   h_d16.copy_(d16)
   # Resident float32 millimetres: bit-identical to what the u16 path computes (u16 * 0.1f).
-  d_f32 = torch.empty((P, H, W), dtype=torch.float32, device=device)
-  for c0 in range(0, P, 1000):
+  d_f32 = torch.empty((n_images, H, W), dtype=torch.float32, device=device)
+  for c0 in range(0, n_images, 1000):
     v = d16[c0:c0 + 1000].to(torch.int32)
     d_f32[c0:c0 + 1000] = torch.where(v < 0, v + 65536, v).to(torch.float32) * DEPTH_SCALE
   del d16
@@ -297,7 +313,7 @@ def gpu_arm(args):
   def step_resident():
     vsd = batch.vsd_batch(ms, d_obj, d_pe, d_pg, d_f32, d_im, d_K, DELTA, TAUS, True, 'step', 'bop19', gate=True)
     mssd = batch.mssd_batch(ms, d_obj, d_pe, d_pg, gate=True)
-    mspd = batch.mspd_batch(ms, d_obj, d_pe, d_pg, d_K)
+    mspd = batch.mspd_batch(ms, d_obj, d_pe, d_pg, d_Kp)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
     if world > 1:   # the path's one exchange step: all-gather of fixed-width error records
       return sharding.gather_records(ids, errs, counts=[P] * world)[1]
@@ -311,7 +327,7 @@ def gpu_arm(args):
                           gate=True, depth_scale=h_scale, zero_copy=zero_copy)
     o, a, b = (x.to(device, non_blocking=True) for x in (h_obj, h_pe, h_pg))
     mssd = batch.mssd_batch(ms, o, a, b, gate=True)
-    mspd = batch.mspd_batch(ms, o, a, b, h_K)
+    mspd = batch.mspd_batch(ms, o, a, b, h_Kp)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
     if world > 1:
       sharding.gather_records(ids, errs, counts=[P] * world)
@@ -395,7 +411,7 @@ def gpu_arm(args):
   except Exception:
     pass
   small = sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_im, h_K, h_scale)) + \
-    sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_K))
+    sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_Kp))
   h2d = small + depth_pulled
   h2d_copy = small + h_d16.numel() * h_d16.element_size()
   e2e_copy_v = P * world * max(1, args.steps // 2) / (ms_e2e_copy * 1e-3)
@@ -404,10 +420,11 @@ def gpu_arm(args):
     'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
     'ms_per_step': ms_res / args.steps, 'higher_is_better': True, 'scaling': 'weak',
     'vs_baseline': None, 'dtype': 'f32 raster + f64 pixel/vertex arithmetic', 'data': 'synthetic',
-    'config': {'workload': WORKLOAD % P, 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
+    'config': {'workload': (WORKLOAD % P) if n_images == P else (WORKLOAD % P).replace(
+                 '1 obj/image', '%d shared images x %d estimates' % (n_images, per_im)), 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
                'l2': 'inputs larger than L2: resident pass reads its model pixels out of %.1f GB of depth; '
                      'e2e pass fetches ~0.28 GB of host depth; both write and re-read ~%.1f GB of assembled-'
-                     'triangle lists per step (L2 = 126 MB)' % (P * H * W * 4 / 1e9, P * 2 * 0.4 * n_faces * 36 / 1e9),
+                     'triangle lists per step (L2 = 126 MB)' % (n_images * H * W * 4 / 1e9, P * 2 * 0.4 * n_faces * 36 / 1e9),
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
                'exchange': 'all-gather of error records per step' if world > 1 else 'none',
                'cpu_affinity': bound},
@@ -430,7 +447,7 @@ def gpu_arm(args):
                          'kernel is bound by instruction issue (ncu: issue slots 66 % busy, 17 of 32 lanes '
                          'active); see DESIGN.md section 4.'},
   }
-  if world == 1 and not args.no_cpu_baseline:
+  if world == 1 and not args.no_cpu_baseline and n_images == P:   # the CPU sample reproduces the per-pair-image workload
     v, ms_step, _ = cpu_arm(P, args.cpu_sample, 1, 1, 0)
     line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': 1, 'kind': 'port',
                             'sample': '%d of the %d pairs, oracle port (numpy pose_error + C rasteriser), 1 core'
@@ -485,6 +502,8 @@ def main():
   ap.add_argument('--warmup', type=int, default=3)
   ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
   ap.add_argument('--pairs', type=int, default=10000)
+  ap.add_argument('--images', type=int, default=0,
+                  help='0: one image per pair (cfg2 as quoted); N: N shared images x pairs/N estimates each')
   ap.add_argument('--cpu-sample', type=int, default=256)
   ap.add_argument('--no-cpu-baseline', action='store_true')
   args = ap.parse_args()
