@@ -17,6 +17,9 @@
 
 namespace {
 
+#ifndef BOP_SYM_CTAS
+#define BOP_SYM_CTAS 3
+#endif
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 
@@ -78,7 +81,24 @@ struct SymMaxSmem {
   double xf[BOP_MAX_SYMS_PER_CTA][12];
   double Pe[12];
   unsigned long long symmax[BOP_MAX_SYMS_PER_CTA];
+  // Running maximum of every lane per symmetry (32 KB): the cross-lane reduction happens once
+  // per CTA and symmetry instead of once per 128 points and symmetry.
+  double run[kWarps][BOP_MAX_SYMS_PER_CTA][32];
 };
+
+// 1/x for the projections: float32 seed + two Newton steps in float64 (relative error ~1e-16, far
+// inside the 1e-5 bar; the compiler's IEEE division is twice as many instructions).  Values
+// outside the float32 range take the IEEE path, so x = 0 still yields +-inf like numpy.
+__device__ __forceinline__ double rcp_f64(double x) {
+  const double ax = fabs(x);
+  if (!(ax > 1e-30 && ax < 1e30)) return 1.0 / x;
+  float r0;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"((float)x));
+  double r = (double)r0;
+  r = fma(r, fma(-x, r, 1.0), r);
+  r = fma(r, fma(-x, r, 1.0), r);
+  return r;
+}
 
 template <typename PT, int MODE>  // MODE 0 = MSSD, 1 = MSPD
 __device__ __forceinline__ void
@@ -125,6 +145,7 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
     }
     symmax[tid] = 0ull;
   }
+  for (int i = tid; i < kWarps * BOP_MAX_SYMS_PER_CTA * 32; i += kThreads) (&sm.run[0][0][0])[i] = 0.0;
   if (MODE == 1 && tid == 32) {
     const double* Kp = Kmat + 9 * (size_t)pair;
 #pragma unroll
@@ -160,8 +181,9 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
           const double ex = Pe[0] * px[k] + Pe[1] * py[k] + Pe[2] * pz[k] + Pe[3];
           const double ey = Pe[4] * px[k] + Pe[5] * py[k] + Pe[6] * pz[k] + Pe[7];
           const double ew = Pe[8] * px[k] + Pe[9] * py[k] + Pe[10] * pz[k] + Pe[11];
-          eu[k] = ex / ew;                   // pts_im /= pts_im[2, :]  (misc.py:106)
-          ev[k] = ey / ew;
+          const double iw = rcp_f64(ew);     // pts_im /= pts_im[2, :]  (misc.py:106)
+          eu[k] = ex * iw;
+          ev[k] = ey * iw;
         }
       }
       for (int sy = 0; sy < ns; ++sy) {
@@ -175,13 +197,12 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
             const double gx = T[0] * px[k] + T[1] * py[k] + T[2] * pz[k] + T[3];
             const double gy = T[4] * px[k] + T[5] * py[k] + T[6] * pz[k] + T[7];
             const double gw = T[8] * px[k] + T[9] * py[k] + T[10] * pz[k] + T[11];
-            const double inv = 1.0 / gw;
+            const double inv = rcp_f64(gw);
             const double du = eu[k] - gx * inv, dv = ev[k] - gy * inv;
             m2 = fmax(m2, du * du + dv * dv);
           }
         }
-        m2 = warp_max(m2);
-        if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m2));
+        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], m2);
       }
     }
   }
@@ -214,10 +235,14 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
             m2 = fmax(m2, dx * dx + dy * dy + dz * dz);
           }
         }
-        m2 = warp_max(m2);
-        if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m2));
+        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], m2);
       }
     }
+  }
+  __syncthreads();
+  for (int sy = 0; sy < ns; ++sy) {   // 256 running maxima per symmetry -> one value
+    const double m = warp_max(sm.run[warp][sy][lane]);
+    if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m));
   }
   __syncthreads();
   if (tid == 0) {
@@ -229,7 +254,7 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, BOP_SYM_CTAS)
 sym_max_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
                const double* __restrict__ pose_est, const double* __restrict__ pose_gt,
                const double* __restrict__ Kmat, int syms_per_cta, int gate,

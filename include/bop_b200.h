@@ -33,7 +33,7 @@ extern "C" {
 
 #define BOP_B200_ABI_VERSION 4
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
-#define BOP_MAX_SYMS_PER_CTA 32
+#define BOP_MAX_SYMS_PER_CTA 16
 
 /* Cost types of pose_error.vsd (bop_toolkit_lib/pose_error.py:79-88). */
 #define BOP_COST_STEP 0
