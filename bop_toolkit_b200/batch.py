@@ -25,7 +25,10 @@ def to_device(x, dtype, device, shape=None):
   if isinstance(x, torch.Tensor):
     t = x
   else:
-    t = torch.from_numpy(np.ascontiguousarray(x))
+    arr = np.ascontiguousarray(x)
+    if not arr.flags.writeable:      # e.g. arrays out of np.load / broadcast views
+      arr = arr.copy()
+    t = torch.from_numpy(arr)
   if t.dtype != dtype:
     t = t.to(dtype)
   if t.device != device:

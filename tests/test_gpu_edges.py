@@ -344,3 +344,44 @@ def test_float32_decision_path_equals_exact(B):
   e, c = B.vsd_from_depth_batch(torch.from_numpy(de).cuda(), torch.from_numpy(dg).cuda(), dt, im, Ks, 180.0,
                                 delta, taus, True, 'step', 'bop19', return_counts=True)
   assert np.array_equal(c.cpu().numpy(), results[0][1])
+
+
+def test_dense_model_takes_the_global_vertex_scratch(B, oracle_built):
+  """Models above 12,288 vertices do not fit the assemble kernel's shared memory: their projected
+  vertices go through the global scratch.  Same renders (vs the oracle) and fused VSD == render +
+  stand-alone pixel pass, also when a small and a dense model share one batch."""
+  from bop_toolkit_b200 import synth
+  from oracle import renderer_oracle
+  from test_gpu_parity import _render_compare
+  K = synth.LM_K
+  dense_pts, dense_faces = synth.make_mesh(100, 200, 210.0, seed=41)
+  small_pts, small_faces = synth.make_mesh(24, 48, 150.0, seed=42)
+  assert dense_pts.shape[0] > 12288
+  ms = B.ModelSet()
+  ms.add(1, dense_pts, dense_faces, None, 210.0)
+  ms.add(2, small_pts, small_faces, None, 150.0)
+  n = 6
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=43, z_range=(350.0, 900.0), outlier_frac=0.0)
+  obj = np.array([0, 1, 0, 1, 0, 0], np.int32)
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  cams = _cams(K, n)
+  dg = B.render_batch(ms, obj, pg, cams, 480, 640)
+  de = B.render_batch(ms, obj, pe, cams, 480, 640)
+  tot_sil = tot_mis = tot_far = 0
+  for i in (0, 1, 2):
+    pts, faces = (dense_pts, dense_faces) if obj[i] == 0 else (small_pts, small_faces)
+    ref = renderer_oracle.render_depth(pts, faces, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], 480, 640, 8)
+    sil, mis, far, rel, bad = _render_compare(dg[i].cpu().numpy(), ref)
+    tot_sil += sil; tot_mis += mis; tot_far += far
+    assert int(bad.sum()) <= 1e-4 * rel.size + 2
+  assert tot_far == 0 and tot_mis <= 0.0005 * tot_sil + 2, (tot_mis, tot_sil)
+  depth = dg.clone()
+  depth[depth == 0] = 1600.0
+  Ks = np.tile(K.reshape(1, 9), (n, 1))
+  im = np.arange(n, dtype=np.int32)
+  taus = [0.05, 0.2, 0.5]
+  diam = np.where(obj == 0, 210.0, 150.0)
+  a, ca = B.vsd_batch(ms, obj, pe, pg, depth, im, Ks, 15, taus, True, 'step', return_counts=True)
+  b, cb = B.vsd_from_depth_batch(de, dg, depth, im, Ks, diam, 15, taus, True, 'step', return_counts=True)
+  assert np.array_equal(ca.cpu().numpy(), cb.cpu().numpy())
+  assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
