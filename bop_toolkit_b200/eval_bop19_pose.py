@@ -17,7 +17,7 @@ import numpy as np
 
 from . import eval_calc_errors as ece
 from . import eval_calc_scores as ecs
-from . import inout, misc
+from . import inout, misc, score_sweep
 
 
 def default_params():
@@ -108,18 +108,31 @@ def evaluate(p, log=misc.log, device=None):
       else:
         settings = [(misc.get_error_signature(error['type'], error['n_top']), None)]
       recalls = []
+      ps = ecs.default_params()
+      ps.update(eval_path=p['eval_path'], datasets_path=p['datasets_path'],
+                targets_filename=p['targets_filename'], visib_gt_min=float(p['visib_gt_min']))
+      # the reference round-trips the thresholds through str() on the command line (:205-207)
+      correct_ths = [[float(str(t)) for t in correct_th] for correct_th in error['correct_th']]
+      # One vectorised pass per error type over every threshold (and tau) when the thresholds are
+      # scalars (they are in BOP19); otherwise one score_errors call per setting.
+      sweep = None
+      if all(len(c) == 1 for c in correct_ths):
+        sweep = score_sweep.ThresholdSweep(ps, error['type'], error['n_top'], dataset, split, split_type,
+                                           records, ctx)
       for error_sign, tau_id in settings:
-        recs = records if tau_id is None else {s: ece.records_for_tau(r, tau_id) for s, r in records.items()}
-        for correct_th in error['correct_th']:
-          ps = ecs.default_params()
-          ps.update(eval_path=p['eval_path'], datasets_path=p['datasets_path'],
-                    targets_filename=p['targets_filename'], visib_gt_min=float(p['visib_gt_min']))
-          ps['correct_th'][error['type']] = [float(str(t)) for t in correct_th]
-          scores, matches = ecs.score_errors(ps, error['type'], error['n_top'], dataset, split,
-                                             split_type, recs, do_print=False, ctx=ctx)
-          sign = misc.get_score_signature(ps['correct_th'][error['type']], ps['visib_gt_min'])
-          base = os.path.join(p['eval_path'], result_name, error_sign)
-          misc.ensure_dir(base)
+        if sweep is not None:
+          results = sweep.run([c[0] for c in correct_ths], col=tau_id or 0)
+        else:
+          recs = records if tau_id is None else {s: ece.records_for_tau(r, tau_id) for s, r in records.items()}
+          results = []
+          for correct_th in correct_ths:
+            ps['correct_th'][error['type']] = correct_th
+            results.append(ecs.score_errors(ps, error['type'], error['n_top'], dataset, split,
+                                            split_type, recs, do_print=False, ctx=ctx))
+        base = os.path.join(p['eval_path'], result_name, error_sign)
+        misc.ensure_dir(base)
+        for correct_th, (scores, matches) in zip(correct_ths, results):
+          sign = misc.get_score_signature(correct_th, ps['visib_gt_min'])
           inout.save_json(os.path.join(base, 'scores_{}.json'.format(sign)), scores)
           inout.save_json(os.path.join(base, 'matches_{}.json'.format(sign)), matches)
           recalls.append(scores['recall'])

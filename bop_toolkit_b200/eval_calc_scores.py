@@ -112,13 +112,9 @@ def normalize_errors(scene_errs, err_type, p, models_info, im_width):
   return out
 
 
-def score_errors(p, err_type, n_top, dataset, split, split_type, scene_errs_by_scene,
-                 do_print=True, ctx=None):
-  """Matches + scores for one error setting from in-memory records.
-  scene_errs_by_scene: {scene_id: records} (never mutated).
-  ctx: optional cache dict shared between calls (targets, GT, GT info, models info).
-  Returns (scores, matches)."""
-  ctx = {} if ctx is None else ctx
+def load_context(p, dataset, split, split_type, ctx):
+  """Fills the cache dict `ctx` with what every score setting of a dataset split shares: dataset
+  tables, models info, the targets organised by scene / image / object."""
   key = (dataset, split, split_type, p['targets_filename'], p['datasets_path'])
   if ctx.get('key') != key:
     ctx.clear()
@@ -132,14 +128,29 @@ def score_errors(p, err_type, n_top, dataset, split, split_type, scene_errs_by_s
       torg.setdefault(t['scene_id'], {}).setdefault(t['im_id'], {})[t['obj_id']] = t
     ctx['targets_org'] = torg
     ctx['scene_gt'], ctx['scene_gt_info'] = {}, {}
+  return ctx
+
+
+def scene_gt_and_info(ctx, scene_id):
+  if scene_id not in ctx['scene_gt']:
+    dp_split = ctx['dp_split']
+    ctx['scene_gt'][scene_id] = inout.load_scene_gt(dp_split['scene_gt_tpath'].format(scene_id=scene_id))
+    ctx['scene_gt_info'][scene_id] = inout.load_json(
+      dp_split['scene_gt_info_tpath'].format(scene_id=scene_id), keys_to_int=True)
+  return ctx['scene_gt'][scene_id], ctx['scene_gt_info'][scene_id]
+
+
+def score_errors(p, err_type, n_top, dataset, split, split_type, scene_errs_by_scene,
+                 do_print=True, ctx=None):
+  """Matches + scores for one error setting from in-memory records.
+  scene_errs_by_scene: {scene_id: records} (never mutated).
+  ctx: optional cache dict shared between calls (targets, GT, GT info, models info).
+  Returns (scores, matches).  (score_sweep.ThresholdSweep does many thresholds in one pass.)"""
+  ctx = load_context(p, dataset, split, split_type, {} if ctx is None else ctx)
   dp_split, dp_model = ctx['dp_split'], ctx['dp_model']
   matches = []
   for scene_id, scene_targets in ctx['targets_org'].items():
-    if scene_id not in ctx['scene_gt']:
-      ctx['scene_gt'][scene_id] = inout.load_scene_gt(dp_split['scene_gt_tpath'].format(scene_id=scene_id))
-      ctx['scene_gt_info'][scene_id] = inout.load_json(
-        dp_split['scene_gt_info_tpath'].format(scene_id=scene_id), keys_to_int=True)
-    scene_gt, scene_gt_info = ctx['scene_gt'][scene_id], ctx['scene_gt_info'][scene_id]
+    scene_gt, scene_gt_info = scene_gt_and_info(ctx, scene_id)
     gt_curr, valid = {}, {}
     for im_id, im_targets in scene_targets.items():
       gt_curr[im_id] = scene_gt[im_id]

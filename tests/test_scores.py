@@ -199,3 +199,45 @@ def test_eval_bop19_pose_matches_reference(dataset, driver_golden, tmp_path):
   print('bop19: %d of %d score files and %d of %d match files byte-identical to the reference; AR %s'
         % (same_scores, len(gold['scores']), same_matches, len(gold['matches_sha256']),
            {k: round(float(v), 4) for k, v in final.items()}))
+
+
+def test_threshold_sweep_equals_per_setting_scoring(dataset, driver_golden):
+  """score_sweep.ThresholdSweep (all thresholds of an error type in one vectorised pass) against
+  eval_calc_scores.score_errors on the REFERENCE's error files: identical scores and matches for
+  every (error type, n_top, tau, threshold, visib_gt_min) combination tried, including
+  thresholds equal to actual error values (strict '<') and an n_top cut."""
+  import copy
+  from bop_toolkit_b200 import eval_calc_scores as ecs, inout, score_sweep
+  _install_gt_info(dataset, driver_golden)
+  n_cmp = 0
+  for error_type, n_top in driver_golden['score_runs']:
+    files = _golden_files(driver_golden, error_type, n_top)
+    by_dir = {}
+    for rel, text in files.items():
+      scene_id = int(os.path.basename(rel).split('_')[1].split('.')[0])
+      recs = json.loads(text, parse_constant=lambda c: {'Infinity': float('inf'), '-Infinity': -float('inf'),
+                                                         'NaN': float('nan')}[c])
+      for r in recs:
+        r['errors'] = {int(k): v for k, v in r['errors'].items()}
+      by_dir.setdefault(os.path.dirname(rel), {})[scene_id] = recs
+    for error_dir, scene_errs in by_dir.items():
+      if any(len(v) != 1 for recs in scene_errs.values() for r in recs for v in r['errors'].values()):
+        continue                                           # multi-element errors: not the sweep's job
+      vals = sorted({v[0] for recs in scene_errs.values() for r in recs for v in r['errors'].values()
+                     if np.isfinite(v[0])})
+      for visib in (0.1, -1.0, 0.6):
+        ps = ecs.parse_args(['--datasets_path=' + dataset['datasets_path'], '--visib_gt_min=%s' % visib])
+        base = {'vsd': [0.05, 0.3, 0.5], 'mssd': [0.05, 0.3], 'mspd': [5.0, 20.0]}.get(error_type, [0.1, 10.0])
+        diam_like = [v for v in vals[::max(1, len(vals) // 4)]][:4]     # thresholds ON error values
+        ths = base + [float(v) for v in diam_like] + [1e9, 0.0]
+        ctx = {}
+        sweep = score_sweep.ThresholdSweep(ps, error_type, n_top, 'lm', 'test', None, scene_errs, ctx)
+        fast = sweep.run(ths)
+        for th, (sc_f, m_f) in zip(ths, fast):
+          p1 = copy.deepcopy(ps)
+          p1['correct_th'][error_type] = [th]
+          sc_s, m_s = ecs.score_errors(p1, error_type, n_top, 'lm', 'test', None, scene_errs, do_print=False, ctx=ctx)
+          assert inout.dumps_errors_layout(m_f) == inout.dumps_errors_layout(m_s), (error_type, n_top, th, visib)
+          assert json.dumps(sc_f, sort_keys=True) == json.dumps(sc_s, sort_keys=True), (error_type, n_top, th)
+          n_cmp += 1
+  assert n_cmp >= 100

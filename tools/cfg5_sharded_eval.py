@@ -123,14 +123,13 @@ def main():
            'mspd': [float(x) for x in np.arange(5, 51, 5)]}
     ar, n_scores, ctx = {}, 0, {}
     p_vsd = params('vsd')
+    from bop_toolkit_b200 import score_sweep
     for et in ('vsd', 'mssd', 'mspd'):
       recalls = []
-      taus = range(len(p_vsd['vsd_taus'])) if et == 'vsd' else [None]
-      for tau_id in taus:
-        recs = {s: (ece.records_for_tau(r, tau_id) if et == 'vsd' else r) for s, r in records[et].items()}
-        for th in ths[et]:
-          ps = ecs.parse_args(['--datasets_path=' + info['datasets_path'], '--correct_th_%s=%s' % (et, th)])
-          sc, _ = ecs.score_errors(ps, et, -1, 'ycbv', 'test', None, recs, do_print=False, ctx=ctx)
+      ps = ecs.parse_args(['--datasets_path=' + info['datasets_path']])
+      sweep = score_sweep.ThresholdSweep(ps, et, -1, 'ycbv', 'test', None, records[et], ctx)
+      for col in range(len(p_vsd['vsd_taus']) if et == 'vsd' else 1):
+        for sc, _ in sweep.run(ths[et], col=col, want_matches=False):
           recalls.append(sc['recall'])
           n_scores += 1
       ar[et] = float(np.mean(recalls))
