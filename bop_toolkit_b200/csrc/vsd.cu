@@ -16,6 +16,7 @@
 // depths the integer counts -- and hence the errors -- are bit-identical to numpy's.
 #include <limits.h>
 #include <stddef.h>
+#include <type_traits>
 
 #include "raster.cuh"
 
@@ -108,7 +109,7 @@ __device__ __forceinline__ bool tri_can_draw(const int4& r0, const int4& r1, con
   return cull != (area2 > 0 ? -1 : 1);
 }
 
-__global__ void __launch_bounds__(kAsmThreads)
+__global__ void __launch_bounds__(kAsmThreads, 2)
 assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
                 const double* __restrict__ pose_a, const double* __restrict__ pose_b,
                 const int32_t* __restrict__ im_idx, const double* __restrict__ K,
@@ -145,8 +146,13 @@ assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restr
   PoseCamF P;
   make_posecam(pose, fx, fy, cx + cx_off, cy + cy_off, P);
   const float4* __restrict__ verts = (const float4*)M.verts4;
-  int4* const pvs = (M.n_pts <= kSmemVerts) ? s_pv : (int4*)(pv_global + (size_t)gw * pv_stride);
+  int4* const gpv = (int4*)(pv_global + (size_t)gw * pv_stride);
   __syncthreads();
+  // The projected-vertex records are addressed through a compile-time switch so that the common
+  // case compiles to shared-memory loads / stores (LDS / STS) instead of generic ones.
+#define PV(i) (*(SMEM ? &s_pv[i] : &gpv[i]))
+  auto body = [&](auto smem_tag) {
+  constexpr bool SMEM = decltype(smem_tag)::value;
   int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
   for (int i0 = tid; i0 < M.n_pts; i0 += 4 * kAsmThreads) {
     float4 vin[4];   // four loads in flight before the first store (pvs may alias as far as nvcc knows)
@@ -160,7 +166,7 @@ assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restr
       const int i = i0 + k * kAsmThreads;
       if (i < M.n_pts) {
         const PVert v = project_vertex(P, vin[k]);
-        pvs[i] = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
+        PV(i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
         if (v.valid) {
           minx = min(minx, v.x); maxx = max(maxx, v.x);
           miny = min(miny, v.y); maxy = max(maxy, v.y);
@@ -208,8 +214,8 @@ assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restr
     if (fb + 2 * kAsmThreads < F) nb4 = __ldg(faces + fb + 2 * kAsmThreads);
     bool acc_a = false, acc_b = false;
     int4 a0, a1, a2, b0, b1, b2;
-    if (fa < F) { a0 = pvs[ia.x]; a1 = pvs[ia.y]; a2 = pvs[ia.z]; }
-    if (fb < F) { b0 = pvs[ib.x]; b1 = pvs[ib.y]; b2 = pvs[ib.z]; }
+    if (fa < F) { a0 = PV(ia.x); a1 = PV(ia.y); a2 = PV(ia.z); }
+    if (fb < F) { b0 = PV(ib.x); b1 = PV(ib.y); b2 = PV(ib.z); }
     if (fa < F) acc_a = tri_can_draw(a0, a1, a2, W, H, cull);
     if (fb < F) acc_b = tri_can_draw(b0, b1, b2, W, H, cull);
     const unsigned ma = __ballot_sync(BOP_FULL_MASK, acc_a), mb = __ballot_sync(BOP_FULL_MASK, acc_b);
@@ -235,6 +241,9 @@ assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restr
       }
     }
   }
+  };
+  if (M.n_pts <= kSmemVerts) body(std::true_type{}); else body(std::false_type{});
+#undef PV
   __syncthreads();
   if (tid == 0) tri_cnt[gw] = s_n;
 }
