@@ -1137,6 +1137,16 @@ void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
   a.tri_cap = L.tri_cap;
 }
 
+// z-tile capacity actually used for images of width W: the tuned value, lowered when the per-column
+// ray tables of a wide image would not leave room for it in shared memory.
+int effective_tile_px(int W) {
+  const int wp = (W + 3) & ~3;
+  const long long room = (long long)225 * 1024 - (long long)wp * 12 - (long long)kMaxBandRows * 12 - (long long)kQueueCap * 4;
+  long long fit = (room / 8) & ~3ll;
+  if (fit < kMinTilePx) fit = kMinTilePx;
+  return g_tune.tile_px < fit ? g_tune.tile_px : (int)fit;
+}
+
 template <int MODE, int NT>
 int launch_fused_nt(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
@@ -1187,7 +1197,7 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
       (int*)(ws + L.tri_cnt), bbox, cx_off, cy_off);
   BOP_LAUNCH_CHECK();
   plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
-                                              n, n_poses, H, W, g_tune.tile_px, bbox,
+                                              n, n_poses, H, W, effective_tile_px(W), bbox,
                                               (PairDesc*)(ws + L.desc), (WorkItem*)(ws + L.work),
                                               (PlanCounters*)(ws + L.ctr), L.max_items, cx_off, cy_off);
   bop_prof_end(BOP_PROF_VSD_PLAN, s);
@@ -1276,7 +1286,7 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
     a.tl_sums = (double*)(ws + L.tl);
     a.depth_out = nullptr;
     a.max_items = L.max_items;
-    a.tile_px = g_tune.tile_px;
+    a.tile_px = effective_tile_px(pp.W);
     a.small_tri_px = g_tune.small_tri_px;
     a.pp = pp;
     a.canvas_w = pp.W;
@@ -1322,7 +1332,7 @@ extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* 
     set_geometry(a, ws, L);
     a.depth_out = depth_out + (size_t)c0 * height * width;
     a.max_items = L.max_items;
-    a.tile_px = g_tune.tile_px;
+    a.tile_px = effective_tile_px(width);
     a.small_tri_px = g_tune.small_tri_px;
     a.pp.H = height;
     a.pp.W = width;
@@ -1415,7 +1425,7 @@ extern "C" int bop_mask_overlap_dev(const bop_model_dev* models, const int32_t* 
     a.counts = (unsigned long long*)(ws + L.counts);
     a.mask_bbox = (int*)(ws + L.mbox);
     a.max_items = L.max_items;
-    a.tile_px = g_tune.tile_px;
+    a.tile_px = effective_tile_px(width);
     a.small_tri_px = g_tune.small_tri_px;
     a.pp.H = height;
     a.pp.W = width;
@@ -1523,7 +1533,7 @@ extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_i
   BOP_REQUIRE(margin_x >= 0 && margin_y >= 0, "bop_gt_info_dev: negative margin");
   BOP_REQUIRE(depth_dtype == BOP_DEPTH_F32 || depth_dtype == BOP_DEPTH_U16, "bop_gt_info_dev: unknown depth dtype");
   const int cw = width + 2 * margin_x, ch = height + 2 * margin_y;
-  BOP_REQUIRE(((cw + 3) & ~3) <= g_tune.tile_px, "bop_gt_info_dev: canvas wider than the z-tile");
+  BOP_REQUIRE(((cw + 3) & ~3) <= effective_tile_px(cw), "bop_gt_info_dev: canvas wider than the z-tile");
   const WsLayout L = ws_layout(n, ch, cw, 1, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_gt_info_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_gt_info_dev: workspace must be 256-byte aligned");
@@ -1552,7 +1562,7 @@ extern "C" int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_i
     a.mask_full = mask_out ? mask_out + (size_t)c0 * height * width : nullptr;
     a.mask_visib = mask_visib_out ? mask_visib_out + (size_t)c0 * height * width : nullptr;
     a.max_items = L.max_items;
-    a.tile_px = g_tune.tile_px;
+    a.tile_px = effective_tile_px(cw);
     a.small_tri_px = g_tune.small_tri_px;
     a.pp.H = height;
     a.pp.W = width;

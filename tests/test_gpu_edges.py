@@ -385,3 +385,40 @@ def test_dense_model_takes_the_global_vertex_scratch(B, oracle_built):
   b, cb = B.vsd_from_depth_batch(de, dg, depth, im, Ks, diam, 15, taus, True, 'step', return_counts=True)
   assert np.array_equal(ca.cpu().numpy(), cb.cpu().numpy())
   assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+
+
+def test_wide_image(B, oracle_built):
+  """4000-pixel-wide images: the per-column ray tables grow with the width and the z-tile shrinks
+  to fit shared memory; renders and VSD must not care."""
+  from bop_toolkit_b200 import synth
+  from oracle import renderer_oracle
+  from test_gpu_parity import _render_compare
+  H, W = 200, 4000
+  K = np.array([[2500.0, 0, 2000.3], [0, 2500.0, 99.6], [0, 0, 1]])
+  pts, faces = synth.make_mesh(24, 48, 200.0, seed=51)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(3, seed=52, K=K, width=W, height=H, z_range=(1500.0, 3000.0),
+                                             outlier_frac=0.0)
+  t_g[0] = [-900.0, 0.0, 1500.0]; t_e[0] = [-897.0, 2.0, 1510.0]     # far left
+  t_g[1] = [950.0, 10.0, 1600.0]; t_e[1] = [955.0, 8.0, 1590.0]      # far right
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  cams = _cams(K, 3)
+  dg = B.render_batch(ms, 0, pg, cams, H, W)
+  de = B.render_batch(ms, 0, pe, cams, H, W)
+  for i in range(3):
+    ref = renderer_oracle.render_depth(pts, faces, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2], H, W, 8)
+    sil, mis, far, rel, bad = _render_compare(dg[i].cpu().numpy(), ref)
+    assert sil > 0 and far == 0 and mis <= 0.0005 * sil + 2 and int(bad.sum()) <= 1e-4 * rel.size + 2
+  depth = dg.clone()
+  depth[depth == 0] = 4000.0
+  Ks = np.tile(K.reshape(1, 9), (3, 1))
+  im = np.arange(3, dtype=np.int32)
+  taus = [0.05, 0.2, 0.5]
+  for cost in ('step', 'tlinear'):
+    a, ca = B.vsd_batch(ms, 0, pe, pg, depth, im, Ks, 15, taus, True, cost, return_counts=True)
+    b, cb = B.vsd_from_depth_batch(de, dg, depth, im, Ks, 200.0, 15, taus, True, cost, return_counts=True)
+    assert np.array_equal(ca.cpu().numpy()[:, :2], cb.cpu().numpy()[:, :2])
+    assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=0, atol=1e-11)
+  st = B.mask_overlap_batch(ms, 0, pe, pg, K, H, W)
+  assert int(st['counts'][:, 0].min()) > 0
