@@ -146,6 +146,7 @@ assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restr
   PoseCamF P;
   make_posecam(pose, fx, fy, cx + cx_off, cy + cy_off, P);
   const float4* __restrict__ verts = (const float4*)M.verts4;
+  if (M.n_pts > pv_stride || M.n_faces > tri_cap) __trap();   // max_geom below the model's size: fail loudly
   int4* const gpv = (int4*)(pv_global + (size_t)gw * pv_stride);
   __syncthreads();
   // The projected-vertex records are addressed through a compile-time switch so that the common
