@@ -197,6 +197,24 @@ def _io_threads():
     return max(1, min(32, os.cpu_count() or 8))
 
 
+_PINNED = {}
+
+
+def _pinned_stack(dtype, n, height, width):
+  """[n,H,W] view of a grow-only pinned host buffer (cudaHostAlloc runs at a few GB/s, which is
+  seconds per dataset when every chunk allocates its own).  The caller finishes with a chunk --
+  the driver reads the errors back, which synchronises -- before asking for the next one."""
+  import torch
+  need = n * height * width
+  if not torch.cuda.is_available():
+    return torch.empty((n, height, width), dtype=dtype)
+  buf = _PINNED.get(dtype)
+  if buf is None or buf.numel() < need:
+    _PINNED.pop(dtype, None)
+    buf = _PINNED[dtype] = torch.empty(max(need, 64 * height * width), dtype=dtype, pin_memory=True)
+  return buf[:need].view(n, height, width)
+
+
 def load_depth_stack(paths, scales, height, width, threads=None):
   """Decodes the depth images of a chunk into ONE pinned host tensor the fused kernel reads in
   place.  uint16 PNG samples stay uint16 (the kernel multiplies by float32(depth_scale) exactly
@@ -211,14 +229,13 @@ def load_depth_stack(paths, scales, height, width, threads=None):
     if im.shape != (height, width):
       raise ValueError('depth image {} is {}x{}, expected {}x{}'.format(
         path, im.shape[1], im.shape[0], width, height))
-  pin = torch.cuda.is_available()
   if all(im.dtype == np.uint16 for im in ims):
-    out = torch.empty((n, height, width), dtype=torch.int16, pin_memory=pin)
+    out = _pinned_stack(torch.int16, n, height, width)
     view = out.numpy().view(np.uint16)
     for i, im in enumerate(ims):
       view[i] = im
     return out, np.asarray(scales, dtype=np.float32)
-  out = torch.empty((n, height, width), dtype=torch.float32, pin_memory=pin)
+  out = _pinned_stack(torch.float32, n, height, width)
   view = out.numpy()
   for i, im in enumerate(ims):
     view[i] = im.astype(np.float32)
@@ -422,6 +439,10 @@ def calc_errors(p, device=None, log=misc.log, write=True):
     engine = ErrorEngine(p, dataset, dp_model, dp_split, needed, device)
     n_ests = 0
     scenes = {}
+    # Error files are written by one background thread: encoding JSON holds the GIL, but the main
+    # thread spends the next scene mostly inside the PNG decoders and the GPU calls, which do not.
+    writer = ThreadPoolExecutor(max_workers=1) if (write and rank == 0) else None
+    pending = []
     for scene_id, scene_targets in targets_org.items():
       scene_camera = _memo(inout.load_scene_camera, dp_split['scene_camera_tpath'].format(scene_id=scene_id))
       scene_gt = _memo(inout.load_scene_gt, dp_split['scene_gt_tpath'].format(scene_id=scene_id))
@@ -436,8 +457,12 @@ def calc_errors(p, device=None, log=misc.log, write=True):
         errs = _gather_errors(errs, sel, len(sp.rec), engine.device, sp=sp, world=world)
       records = fill_records(sp, errs)
       scenes[scene_id] = records
-      if write and rank == 0:
-        save_scene_errors(p, dataset, result_name, scene_id, records, log)
+      if writer is not None:
+        pending.append(writer.submit(save_scene_errors, p, dataset, result_name, scene_id, records, log))
+    if writer is not None:
+      for f in pending:
+        f.result()          # re-raises I/O errors
+      writer.shutdown()
     all_out[result_name] = scenes
     log('Calculation of errors for {} estimates took {}s.'.format(n_ests, time.time() - t_start))
   log('Done.')
