@@ -197,7 +197,8 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
             const double gw = T[8] * px[k] + T[9] * py[k] + T[10] * pz[k] + T[11];
             const double inv = rcp_f64(gw);
             const double du = eu[k] - gx * inv, dv = ev[k] - gy * inv;
-            m2 = fmax(m2, du * du + dv * dv);
+            const double d2 = du * du + dv * dv;
+            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
           }
         }
         sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], m2);
@@ -230,7 +231,8 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
             const double dx = T[0] * px[k] + T[1] * py[k] + T[2] * pz[k] + T[9];
             const double dy = T[3] * px[k] + T[4] * py[k] + T[5] * pz[k] + T[10];
             const double dz = T[6] * px[k] + T[7] * py[k] + T[8] * pz[k] + T[11];
-            m2 = fmax(m2, dx * dx + dy * dy + dz * dz);
+            const double d2 = dx * dx + dy * dy + dz * dz;
+            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
           }
         }
         sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], m2);
