@@ -28,7 +28,10 @@ sys.path.insert(0, ROOT)
 
 def main():
   ap = argparse.ArgumentParser()
-  ap.add_argument('--images', type=int, default=20, help='images per scene (12 scenes)')
+  ap.add_argument('--images', type=int, default=20, help='images per scene')
+  ap.add_argument('--config', default='cfg5', choices=['cfg5', 'cfg3'],
+                  help='cfg5: YCB-V layout, 12 scenes, 21 models, 5 targets/image, n_top=-1; '
+                       'cfg3: LM-O layout, 1 scene, 8 models in every image, n_top=1 (BASELINE.json configs)')
   ap.add_argument('--root', default=None)
   ap.add_argument('--keep', action='store_true')
   ap.add_argument('--profile', action='store_true', help='cProfile of the error + score stages (rank 0)')
@@ -45,7 +48,16 @@ def main():
   if world > 1:
     os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
-  root = args.root or os.path.join(tempfile.gettempdir(), 'bop_cfg5_%d' % args.images)
+  if args.config == 'cfg5':
+    ds = dict(dataset='ycbv', scene_ids=tuple(range(48, 60)), obj_ids=tuple(range(1, 22)), objs_per_image=5,
+              ests_per_target=2)
+    n_top = -1
+  else:
+    ds = dict(dataset='lmo', scene_ids=(2,), obj_ids=(1, 5, 6, 8, 9, 10, 11, 12), objs_per_image=8,
+              ests_per_target=2)
+    n_top = 1
+  dataset = ds['dataset']
+  root = args.root or os.path.join(tempfile.gettempdir(), 'bop_%s_%d' % (args.config, args.images))
   quiet = lambda s: None
   t = {}
 
@@ -65,13 +77,11 @@ def main():
       cam = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]])
       return batch.render_batch(cache[key], 0, batch.pack_poses(R[None], t_[None]), cam,
                                 synth.IM_H, synth.IM_W)[0].cpu().numpy()
-    info = synth.write_bop_dataset(root, render_fn, dataset='ycbv', split='test',
-                                   scene_ids=tuple(range(48, 60)), n_images=args.images,
-                                   obj_ids=tuple(range(1, 22)), objs_per_image=5, ests_per_target=2,
-                                   seed=3, mesh_res=(50, 100))
+    info = synth.write_bop_dataset(root, render_fn, split='test', n_images=args.images, seed=3,
+                                   mesh_res=(50, 100), **ds)
     t['write_dataset_s'] = time.time() - t0
     t0 = time.time()
-    p = calc_gt_info.parse_args(['--dataset=ycbv', '--dataset_split=test',
+    p = calc_gt_info.parse_args(['--dataset=' + dataset, '--dataset_split=test',
                                  '--datasets_path=' + info['datasets_path']])
     p['device'] = 'cuda:%d' % local
     calc_gt_info.calc_gt_info(p, log=quiet)
@@ -84,7 +94,7 @@ def main():
 
   # ---- errors: sharded over the ranks ------------------------------------------------------
   def params(error_type):
-    return ece.parse_args(['--error_type=' + error_type, '--n_top=-1',
+    return ece.parse_args(['--error_type=' + error_type, '--n_top=%d' % n_top,
                            '--result_filenames=' + info['result_filename'],
                            '--results_path=' + info['results_path'], '--eval_path=' + info['eval_path'],
                            '--datasets_path=' + info['datasets_path']])
@@ -97,7 +107,7 @@ def main():
   for et in ('vsd', 'mssd', 'mspd'):
     torch.cuda.synchronize()
     t0 = time.time()
-    records[et] = ece.calc_errors(params(et), log=quiet, write=(rank == 0))['synth_ycbv-test']
+    records[et] = ece.calc_errors(params(et), log=quiet, write=(rank == 0))['synth_%s-test' % dataset]
     torch.cuda.synchronize()
     t['errors_%s_s' % et] = time.time() - t0
     n_pairs[et] = sum(len(r['errors']) for recs in records[et].values() for r in recs)
@@ -112,7 +122,7 @@ def main():
       ece._dist_info = lambda: (0, 1)
       try:
         for et in ('vsd', 'mssd', 'mspd'):
-          single = ece.calc_errors(params(et), log=quiet, write=False)['synth_ycbv-test']
+          single = ece.calc_errors(params(et), log=quiet, write=False)['synth_%s-test' % dataset]
           identical = identical and (single == records[et])
       finally:
         ece._dist_info = real_info
@@ -127,7 +137,7 @@ def main():
     for et in ('vsd', 'mssd', 'mspd'):
       recalls = []
       ps = ecs.parse_args(['--datasets_path=' + info['datasets_path']])
-      sweep = score_sweep.ThresholdSweep(ps, et, -1, 'ycbv', 'test', None, records[et], ctx)
+      sweep = score_sweep.ThresholdSweep(ps, et, n_top, dataset, 'test', None, records[et], ctx)
       for col in range(len(p_vsd['vsd_taus']) if et == 'vsd' else 1):
         for sc, _ in sweep.run(ths[et], col=col, want_matches=False):
           recalls.append(sc['recall'])
@@ -138,8 +148,8 @@ def main():
       import pstats
       prof.disable()
       pstats.Stats(prof, stream=sys.stderr).sort_stats('cumulative').print_stats(45)
-    out = {'config': 'synthetic ycbv-test layout: 12 scenes x %d images, 6 GT instances / image, 21 models of 4902 verts'
-                     % args.images,
+    out = {'config': 'synthetic %s-test layout (%s): %d scene(s) x %d images, %d models of 4902 verts, n_top=%d'
+                     % (dataset, args.config, len(ds['scene_ids']), args.images, len(ds['obj_ids']), n_top),
            'n_gpus': world, 'pairs': n_pairs, 'seconds': {k: round(v, 3) for k, v in t.items()},
            'pairs_per_s_driver': {et: round(n_pairs[et] / t['errors_%s_s' % et], 1) for et in n_pairs},
            'AR': ar, 'AR_mean': float(np.mean(list(ar.values()))), 'score_settings_evaluated': n_scores,
