@@ -10,8 +10,8 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 SO_PATH = os.path.join(CSRC, 'libbop_b200.so')
-SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu']
-HEADERS = ['common.cuh', 'raster.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
+SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu', 'png_depth.cu']
+HEADERS = ['common.cuh', 'raster.cuh', 'png_inflate.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
 
 BOP_MAX_TAUS = 16
 COST_TYPES = {'step': 0, 'tlinear': 1}
@@ -26,6 +26,17 @@ class ModelDev(ctypes.Structure):
     ('syms', ctypes.c_void_p), ('diameter', ctypes.c_double), ('n_pts', ctypes.c_int32),
     ('n_faces', ctypes.c_int32), ('n_syms', ctypes.c_int32), ('pts_f64', ctypes.c_int32),
     ('cull', ctypes.c_int32), ('cull_min_dist', ctypes.c_float)]
+
+
+class PngInfo(ctypes.Structure):
+  """struct bop_png_info (include/bop_b200.h)."""
+  _fields_ = [
+    ('width', ctypes.c_int32), ('height', ctypes.c_int32), ('bit_depth', ctypes.c_int32),
+    ('color_type', ctypes.c_int32), ('interlace', ctypes.c_int32), ('status', ctypes.c_int32),
+    ('idat_bytes', ctypes.c_int64)]
+
+
+PNG_UNSUPPORTED, PNG_STAGING_TOO_SMALL = -104, -105
 
 
 class VsdParams(ctypes.Structure):
@@ -95,6 +106,11 @@ _SIGNATURES = {
   'bop_profile_enable': (_I, [_I]),
   'bop_profile_reset': (_I, []),
   'bop_profile_sum_ms': (_I, [_I, _I, _P, _P]),
+  'bop_png_stage_files_host': (_I, [_P, _I, _P, ctypes.c_size_t, _P, _P, _P, _I, _P]),
+  'bop_png_scan_host': (_I, [_P, ctypes.c_size_t, _P, _P]),
+  'bop_png_decode_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I]),
+  'bop_png_decode_dev': (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, ctypes.c_size_t, _P]),
+  'bop_png_decode_selftest_host': (_I, [_P, ctypes.c_int32, _I, _I, _P]),
 }
 EXPORTED_SYMBOLS = sorted(_SIGNATURES)
 

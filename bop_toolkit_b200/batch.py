@@ -5,6 +5,7 @@ sit on.  torch is used for device memory, streams and pinned staging only; all a
 in the hand-written sm_100a kernels behind the C ABI (include/bop_b200.h).
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -613,6 +614,92 @@ def gt_info_batch(models, obj, pose_gt, depth_test, im_idx, K, delta=15, depth_s
       out['bbox'].data_ptr(), out['mask'].data_ptr() if want_masks else None,
       out['mask_visib'].data_ptr() if want_masks else None, ws.data_ptr(), wsb, _stream_ptr())
   _lib.check(rc)
+  return out
+
+
+# ------------------------------------------------------------------------ depth PNGs on the GPU
+_png_staging = {}
+
+
+def png_stage(paths, threads=8, slot=0):
+  """Host half of the depth-PNG path: files -> zlib streams in a grow-only pinned buffer (one per
+  `slot`, so a caller can stage the next chunk on a thread while the GPU decodes this one; the
+  ctypes call releases the GIL).  Returns an opaque tuple for `decode_depth_staged`."""
+  L = _lib.lib()
+  n = len(paths)
+  arr = (ctypes.c_char_p * n)(*[os.fsencode(p) for p in paths])
+  offs = np.zeros(n, dtype=np.int64)
+  nbytes = np.zeros(n, dtype=np.int32)
+  infos = (_lib.PngInfo * n)()
+  need = ctypes.c_size_t()
+  for _ in range(2):
+    buf = _png_staging.get(slot)
+    cap = buf.numel() if buf is not None else 0
+    rc = L.bop_png_stage_files_host(arr, n, buf.data_ptr() if buf is not None else None, cap,
+                                    offs.ctypes.data, nbytes.ctypes.data, infos, int(threads),
+                                    ctypes.byref(need))
+    if rc != _lib.PNG_STAGING_TOO_SMALL:
+      _lib.check(rc)
+      return list(paths), buf, int(need.value), offs, nbytes, infos
+    _png_staging.pop(slot, None)
+    _png_staging[slot] = torch.empty(max(int(need.value * 1.25), 1 << 24), dtype=torch.uint8,
+                                      pin_memory=torch.cuda.is_available())
+  raise _lib.BopCudaError('bop_png_stage_files_host: staging buffer still too small')
+
+
+def decode_depth_pngs(paths, height, width, device=None, threads=8):
+  """`inout.load_depth` for a whole chunk of 16-bit depth PNGs, decoded ON THE GPU
+  (inout.py:39-46 as called by eval_calc_errors.py:236-243): host threads only read the files and
+  strip the PNG container (bop_png_stage_files_host), the zlib streams cross PCIe compressed and
+  one warp per image inflates + unfilters them (bop_png_decode_dev).  Returns an int16 CUDA tensor
+  [n,H,W] holding the raw uint16 samples (what the VSD entry points take with depth_scale).
+  Files that are not 16-bit greyscale non-interlaced PNGs (none in the BOP datasets) are decoded
+  on the host by OpenCV and uploaded; they must still be 16-bit."""
+  _lib.require_cuda()
+  if len(paths) == 0:
+    return torch.empty((0, height, width), dtype=torch.int16, device=_dev(device))
+  return decode_depth_staged(png_stage(paths, threads), height, width, device)
+
+
+def decode_depth_staged(staged, height, width, device=None):
+  """Device half of `decode_depth_pngs` on the result of `png_stage`."""
+  _lib.require_cuda()
+  dev = _dev(device)
+  paths, buf, used, offs, nbytes, infos = staged
+  n = len(paths)
+  out = torch.empty((n, height, width), dtype=torch.int16, device=dev)
+  foreign = []
+  for i in range(n):
+    st = infos[i].status
+    if st == _lib.PNG_UNSUPPORTED:
+      foreign.append(i)
+    elif st != 0:
+      raise IOError('cannot read depth image {} (status {})'.format(paths[i], st))
+    if (infos[i].height, infos[i].width) != (height, width):
+      raise ValueError('depth image {} is {}x{}, expected {}x{}'.format(
+        paths[i], infos[i].width, infos[i].height, width, height))
+  L = _lib.lib()
+  with torch.cuda.device(dev):
+    comp = buf[:max(used, 16)].to(dev, non_blocking=True)
+    offs_d = torch.from_numpy(offs).to(dev, non_blocking=True)
+    nb_d = torch.from_numpy(nbytes).to(dev, non_blocking=True)
+    status = torch.zeros(n, dtype=torch.int32, device=dev)
+    wsb = L.bop_png_decode_workspace_bytes(n, height, width)
+    ws = _workspace(dev, wsb)
+    _lib.check(L.bop_png_decode_dev(comp.data_ptr(), offs_d.data_ptr(), nb_d.data_ptr(), n, height,
+                                    width, out.data_ptr(), status.data_ptr(), ws.data_ptr(), wsb,
+                                    _stream_ptr()))
+    st = status.cpu().numpy()       # synchronises: the staging buffer may be refilled afterwards
+  for i in foreign:
+    from . import inout
+    im = inout.load_depth_raw(paths[i])
+    if im.dtype != np.uint16:
+      raise ValueError('depth image {} is not 16-bit'.format(paths[i]))
+    out[i] = torch.from_numpy(im.view(np.int16)).to(dev)
+    st[i] = 0
+  bad = np.nonzero(st)[0]
+  if bad.size:
+    raise IOError('corrupt depth PNG {} (decoder status {})'.format(paths[bad[0]], int(st[bad[0]])))
   return out
 
 

@@ -62,7 +62,7 @@ def _setup(p, model_type):
   return batch, dp_split, dp_model, ms
 
 
-def _scene_batch(p, dp_split, scene_id, load_depth_stack):
+def _scene_batch(p, dp_split, scene_id, load_depth_stack, device=None):
   """Flattens the GT instances of a scene: (im_ids, depth tensor, scales, K rows, per-instance
   image position / obj ids / poses, scene_gt)."""
   scene_camera = inout.load_scene_camera(dp_split['scene_camera_tpath'].format(scene_id=scene_id))
@@ -75,7 +75,8 @@ def _scene_batch(p, dp_split, scene_id, load_depth_stack):
     if not os.path.exists(path):
       path = path.replace('.tif', '.png')      # calc_gt_info.py:104-105
     paths.append(path)
-  depth, sc = load_depth_stack(paths, [scene_camera[i]['depth_scale'] for i in im_ids], h, w)
+  depth, sc = load_depth_stack(paths, [scene_camera[i]['depth_scale'] for i in im_ids], h, w,
+                              device=device)
   K = np.stack([np.asarray(scene_camera[i]['cam_K'], np.float64).reshape(9) for i in im_ids])
   im_pos, obj_ids, poses = [], [], []
   for pos, im_id in enumerate(im_ids):
@@ -95,9 +96,9 @@ def calc_gt_info(p, log=misc.log, write=True, images_per_chunk=512):
   for scene_id in present_scene_ids(dp_split):
     log('Calculating GT info - dataset: {} ({}, {}), scene: {}'.format(
       p['dataset'], p['dataset_split'], p['dataset_split_type'], scene_id))
-    im_ids, depth, sc, K, im_pos, obj_ids, poses, scene_gt = _scene_batch(p, dp_split, scene_id, load_depth_stack)
+    im_ids, depth, sc, K, im_pos, obj_ids, poses, scene_gt = _scene_batch(p, dp_split, scene_id, load_depth_stack, ms.device)
     res = batch.gt_info_batch(ms, ms.indices(obj_ids), poses, depth, im_pos, K, p['delta'], sc,
-                              margin=None, zero_copy=depth.is_pinned())
+                              margin=None, zero_copy=(not depth.is_cuda) and depth.is_pinned())
     counts = res['counts'].cpu().numpy()
     fract = res['visib_fract'].cpu().numpy()
     bbox = res['bbox'].cpu().numpy()
@@ -130,7 +131,7 @@ def calc_gt_masks(p, log=misc.log, instances_per_chunk=256):
       continue
     log('Calculating masks - dataset: {} ({}, {}), scene: {}'.format(
       p['dataset'], p['dataset_split'], p['dataset_split_type'], scene_id))
-    im_ids, depth, sc, K, im_pos, obj_ids, poses, scene_gt = _scene_batch(p, dp_split, scene_id, load_depth_stack)
+    im_ids, depth, sc, K, im_pos, obj_ids, poses, scene_gt = _scene_batch(p, dp_split, scene_id, load_depth_stack, ms.device)
     for tp in ('mask_tpath', 'mask_visib_tpath'):
       misc.ensure_dir(os.path.dirname(dp_split[tp].format(scene_id=scene_id, im_id=0, gt_id=0)))
     names = [(im_id, g) for im_id in im_ids for g in range(len(scene_gt[im_id]))]
@@ -138,7 +139,7 @@ def calc_gt_masks(p, log=misc.log, instances_per_chunk=256):
     for c0 in range(0, len(names), instances_per_chunk):
       sl = slice(c0, c0 + instances_per_chunk)
       res = batch.gt_info_batch(ms, oi[sl], poses[sl], depth, im_pos[sl], K, p['delta'], sc,
-                                margin=(0, 0), want_masks=True, zero_copy=depth.is_pinned())
+                                margin=(0, 0), want_masks=True, zero_copy=(not depth.is_cuda) and depth.is_pinned())
       mask, visib = res['mask'].cpu().numpy(), res['mask_visib'].cpu().numpy()
       for k, (im_id, g) in enumerate(names[sl]):
         cv2.imwrite(dp_split['mask_tpath'].format(scene_id=scene_id, im_id=im_id, gt_id=g), mask[k])

@@ -13,7 +13,8 @@ int bop_set_error_msg(int code, const char* msg);
 void bop_count_launch(int n = 1);
 // Optional per-kernel CUDA-event timing (enabled by bop_profile_enable); slot ids below.
 enum { BOP_PROF_VSD_FUSED = 0, BOP_PROF_VSD_PLAN = 1, BOP_PROF_MSSD = 2, BOP_PROF_MSPD = 3,
-       BOP_PROF_K2 = 4, BOP_PROF_RENDER = 5, BOP_PROF_ADI = 6, BOP_PROF_MASK = 7, BOP_PROF_SLOTS = 8 };
+       BOP_PROF_K2 = 4, BOP_PROF_RENDER = 5, BOP_PROF_ADI = 6, BOP_PROF_MASK = 7, BOP_PROF_PNG = 8,
+       BOP_PROF_SLOTS = 9 };
 void bop_prof_begin(int slot, cudaStream_t s);
 void bop_prof_end(int slot, cudaStream_t s);
 

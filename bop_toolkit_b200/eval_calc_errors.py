@@ -215,14 +215,27 @@ def _pinned_stack(dtype, n, height, width):
   return buf[:need].view(n, height, width)
 
 
-def load_depth_stack(paths, scales, height, width, threads=None):
-  """Decodes the depth images of a chunk into ONE pinned host tensor the fused kernel reads in
-  place.  uint16 PNG samples stay uint16 (the kernel multiplies by float32(depth_scale) exactly
-  as `depth_im *= depth_scale` does, eval_calc_errors.py:239-243); any other sample type is
-  converted to float32 millimetres here.  Returns (tensor [n,H,W], scales float32 [n] or None)."""
+def gpu_depth_decode(paths):
+  """True when the depth images of a chunk go through the GPU PNG decoder (all '.png', and
+  BOP_B200_DEPTH_DECODE is not 'host')."""
+  return os.environ.get('BOP_B200_DEPTH_DECODE', 'gpu') != 'host' and len(paths) > 0 and \
+    all(q.lower().endswith('.png') for q in paths)
+
+
+def load_depth_stack(paths, scales, height, width, threads=None, device=None):
+  """The depth images of a chunk as ONE tensor [n,H,W] + scales (float32 [n] or None).
+  With `device` and PNG files: inflated and unfiltered on the GPU (batch.decode_depth_pngs), a
+  CUDA int16 tensor of raw samples.  Otherwise decoded by OpenCV on host threads into ONE pinned
+  host tensor the fused kernel reads in place.  uint16 PNG samples stay uint16 (the kernel
+  multiplies by float32(depth_scale) exactly as `depth_im *= depth_scale` does,
+  eval_calc_errors.py:239-243); any other sample type is converted to float32 millimetres."""
   import torch
   n = len(paths)
   threads = threads or _io_threads()      # PNG inflate releases the GIL: one decoder per host core
+  if device is not None and gpu_depth_decode(paths):
+    from . import batch
+    return batch.decode_depth_pngs(paths, height, width, device, threads), \
+      np.asarray(scales, dtype=np.float32)
   with ThreadPoolExecutor(max_workers=max(1, min(threads, n))) as ex:
     ims = list(ex.map(inout.load_depth_raw, paths))
   for im, path in zip(ims, paths):
@@ -323,19 +336,38 @@ class ErrorEngine(object):
     out = np.empty((len(sel), T))
     im_pos = sp.im_pos[sel]
     used = np.unique(im_pos)                      # images this rank touches, ascending position
-    for c0 in range(0, len(used), images_per_chunk):
-      chunk = used[c0:c0 + images_per_chunk]
-      im_ids = [sp.im_ids[i] for i in chunk]
-      paths = [self.dp_split['depth_tpath'].format(scene_id=scene_id, im_id=i) for i in im_ids]
-      scales = [scene_camera[i]['depth_scale'] for i in im_ids]
-      depth, sc = load_depth_stack(paths, scales, h, w)
-      rows = np.nonzero(np.isin(im_pos, chunk))[0]
-      local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
-      err = batch.vsd_batch(self.ms, oi[rows], pe[rows], pg[rows], depth, local,
-                            self._K_rows(scene_camera, im_ids), p['vsd_deltas'][self.dataset],
-                            p['vsd_taus'], p['vsd_normalized_by_diameter'], 'step', 'bop19',
-                            gate=True, depth_scale=sc, zero_copy=depth.is_pinned())
-      out[rows] = err.cpu().numpy()
+    chunks = [used[c0:c0 + images_per_chunk] for c0 in range(0, len(used), images_per_chunk)]
+    paths = [[self.dp_split['depth_tpath'].format(scene_id=scene_id, im_id=sp.im_ids[i]) for i in c]
+             for c in chunks]
+    # 16-bit PNGs (every BOP dataset) are inflated and unfiltered on the GPU: the host threads only
+    # read the files, and they stage chunk k+1 while the GPU works on chunk k.
+    # BOP_B200_DEPTH_DECODE=host keeps the OpenCV decode + zero-copy pinned path.
+    on_gpu = gpu_depth_decode([q for c in paths for q in c])
+    stager = ThreadPoolExecutor(max_workers=1) if on_gpu else None
+    fut = stager.submit(batch.png_stage, paths[0], _io_threads(), 0) if on_gpu and chunks else None
+    try:
+      for k, chunk in enumerate(chunks):
+        im_ids = [sp.im_ids[i] for i in chunk]
+        if on_gpu:
+          staged = fut.result()
+          if k + 1 < len(chunks):
+            fut = stager.submit(batch.png_stage, paths[k + 1], _io_threads(), (k + 1) & 1)
+          depth = batch.decode_depth_staged(staged, h, w, self.device)
+          sc = np.asarray([scene_camera[i]['depth_scale'] for i in im_ids], dtype=np.float32)
+        else:
+          scales = [scene_camera[i]['depth_scale'] for i in im_ids]
+          depth, sc = load_depth_stack(paths[k], scales, h, w)
+        rows = np.nonzero(np.isin(im_pos, chunk))[0]
+        local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
+        err = batch.vsd_batch(self.ms, oi[rows], pe[rows], pg[rows], depth, local,
+                              self._K_rows(scene_camera, im_ids), p['vsd_deltas'][self.dataset],
+                              p['vsd_taus'], p['vsd_normalized_by_diameter'], 'step', 'bop19',
+                              gate=True, depth_scale=sc,
+                              zero_copy=(not depth.is_cuda) and depth.is_pinned())
+        out[rows] = err.cpu().numpy()
+    finally:
+      if stager is not None:
+        stager.shutdown(wait=True)
     return out
 
 

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BOP_B200_ABI_VERSION 4
+#define BOP_B200_ABI_VERSION 5
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
 #define BOP_MAX_SYMS_PER_CTA 16
 
@@ -99,7 +99,7 @@ uint64_t    bop_kernel_launch_count(void);
 
 /* Per-kernel device timing (CUDA events on the launching stream), used by bench.py for the
  * roofline figure.  Slots: 0 fused VSD kernel, 1 VSD bbox+plan, 2 MSSD, 3 MSPD, 4 K2 pixel pass,
- * 5 render, 6 ADI, 7 mask overlap.  bop_profile_sum_ms synchronises on the recorded events and returns the summed
+ * 5 render, 6 ADI, 7 mask overlap, 8 depth-PNG decode (inflate + unfilter).  bop_profile_sum_ms synchronises on the recorded events and returns the summed
  * duration of the last `last_n` timed launches of the slot (0 = all kept, ring of 256).        */
 int bop_profile_enable(int on);
 int bop_profile_reset(void);
@@ -284,6 +284,46 @@ int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_
  * step-cost pass; by default a float32 pre-test decides the comparisons that are not close to
  * their thresholds (bit-identical counts either way; tests compare the two). */
 int bop_vsd_set_exact(int exact);
+
+
+/* ---- depth-PNG input on the device -------------------------------------------------------
+ * Replaces inout.load_depth (bop_toolkit_lib/inout.py:39-46: imageio.imread of a 16-bit
+ * greyscale PNG) as called per image by scripts/eval_calc_errors.py:236-243.  The host only
+ * reads the files and strips the PNG container; zlib inflate and the PNG row filters run on
+ * the GPU, one warp per image, and leave uint16 samples in HBM in the layout the VSD entry
+ * points take as BOP_DEPTH_U16.  Chunk CRCs and the zlib Adler-32 are not verified.         */
+#define BOP_PNG_IO_ERROR          (-101)  /* file missing / unreadable                         */
+#define BOP_PNG_NOT_PNG           (-102)  /* bad signature or IHDR                             */
+#define BOP_PNG_TRUNCATED         (-103)  /* chunk runs past the end of the file, no IDAT      */
+#define BOP_PNG_UNSUPPORTED       (-104)  /* not 16-bit greyscale non-interlaced: decode it on
+                                             the host (the caller's choice), fields are filled */
+#define BOP_PNG_STAGING_TOO_SMALL (-105)  /* returned by the call; *needed_bytes tells the size */
+typedef struct bop_png_info {
+  int32_t width, height, bit_depth, color_type, interlace;
+  int32_t status;            /* 0 or one of BOP_PNG_* for this file                             */
+  int64_t idat_bytes;        /* length of the concatenated IDAT payloads (the zlib stream)      */
+} bop_png_info;
+/* Reads `n` files with `threads` host threads into `staging` (pinned memory recommended) and
+ * compacts each file's IDAT payloads in place: afterwards staging + offsets[i] holds the zlib
+ * stream of file i (comp_bytes[i] bytes, 16-byte aligned, zero padded).  Per-file problems are
+ * reported in infos[i].status (comp_bytes[i] = 0).  If staging_bytes is too small nothing is
+ * read, *needed_bytes is set and BOP_PNG_STAGING_TOO_SMALL is returned.                       */
+int bop_png_stage_files_host(const char* const* paths, int n, void* staging, size_t staging_bytes,
+                             int64_t* offsets, int32_t* comp_bytes, bop_png_info* infos,
+                             int threads, size_t* needed_bytes);
+/* Same container walk for one file already in memory (compacts in place in `file_bytes`). */
+int bop_png_scan_host(void* file_bytes, size_t nbytes, bop_png_info* info, int64_t* idat_bytes);
+size_t bop_png_decode_workspace_bytes(int n, int height, int width);
+/* comp/offsets/comp_bytes: the staged streams in DEVICE memory (comp 16-byte aligned);
+ * depth_out [n][height][width] uint16; status[n] int32: 0 or a negative decoder status
+ * (bop_toolkit_b200/csrc/png_inflate.cuh) -- images with a non-zero status are not written. */
+int bop_png_decode_dev(const void* comp, const int64_t* offsets, const int32_t* comp_bytes, int n,
+                       int height, int width, uint16_t* depth_out, int32_t* status,
+                       void* workspace, size_t workspace_bytes, void* stream);
+/* The device decoder's source compiled for the host, for the CPU test-suite only (checks the
+ * inflate core against zlib without a GPU).  No product path calls it.                       */
+int bop_png_decode_selftest_host(const void* idat, int32_t comp_bytes, int height, int width,
+                                 uint16_t* depth_out);
 
 
 #ifdef __cplusplus

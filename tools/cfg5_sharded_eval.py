@@ -34,6 +34,8 @@ def main():
                        'cfg3: LM-O layout, 1 scene, 8 models in every image, n_top=1 (BASELINE.json configs)')
   ap.add_argument('--root', default=None)
   ap.add_argument('--keep', action='store_true')
+  ap.add_argument('--host_decode_too', action='store_true',
+                  help='also time the VSD pass with OpenCV decoding the depth PNGs on the host')
   ap.add_argument('--profile', action='store_true', help='cProfile of the error + score stages (rank 0)')
   args = ap.parse_args()
 
@@ -104,6 +106,15 @@ def main():
     import cProfile
     prof = cProfile.Profile()
     prof.enable()
+  if args.host_decode_too:
+    # the same VSD pass with the depth PNGs decoded by OpenCV on the host threads (the r01 path)
+    os.environ['BOP_B200_DEPTH_DECODE'] = 'host'
+    torch.cuda.synchronize()
+    t0 = time.time()
+    rec_host = ece.calc_errors(params('vsd'), log=quiet, write=False)['synth_%s-test' % dataset]
+    torch.cuda.synchronize()
+    t['errors_vsd_host_png_decode_s'] = time.time() - t0
+    os.environ['BOP_B200_DEPTH_DECODE'] = 'gpu'
   for et in ('vsd', 'mssd', 'mspd'):
     torch.cuda.synchronize()
     t0 = time.time()
@@ -113,6 +124,8 @@ def main():
     n_pairs[et] = sum(len(r['errors']) for recs in records[et].values() for r in recs)
 
   out = None
+  if args.host_decode_too:
+    t['vsd_records_equal_host_decode'] = bool(rec_host == records['vsd'])
   if rank == 0:
     # ---- sharded == unsharded (bit-identical records) ----------------------------------
     identical = None
@@ -150,7 +163,7 @@ def main():
       pstats.Stats(prof, stream=sys.stderr).sort_stats('cumulative').print_stats(45)
     out = {'config': 'synthetic %s-test layout (%s): %d scene(s) x %d images, %d models of 4902 verts, n_top=%d'
                      % (dataset, args.config, len(ds['scene_ids']), args.images, len(ds['obj_ids']), n_top),
-           'n_gpus': world, 'pairs': n_pairs, 'seconds': {k: round(v, 3) for k, v in t.items()},
+           'n_gpus': world, 'pairs': n_pairs, 'seconds': {k: (round(v, 3) if isinstance(v, float) else v) for k, v in t.items()},
            'pairs_per_s_driver': {et: round(n_pairs[et] / t['errors_%s_s' % et], 1) for et in n_pairs},
            'AR': ar, 'AR_mean': float(np.mean(list(ar.values()))), 'score_settings_evaluated': n_scores,
            'sharded_equals_unsharded': identical}
