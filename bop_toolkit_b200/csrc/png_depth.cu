@@ -34,22 +34,45 @@ inline size_t image_stride(int height, int width) {       // inflated bytes of o
   return round_up((size_t)height * (2 * (size_t)width + 1) + 64, 256);
 }
 
+// Loads words [w0, w0 + count) of the stream into the ring (16-byte loads, zeros past the end).
+__device__ __forceinline__ void ring_load(uint32_t* ring, const uint32_t* __restrict__ src,
+                                          uint32_t nwords, uint32_t w0, uint32_t count, int lane) {
+  for (uint32_t w = w0 + 4u * lane; w < w0 + count; w += 128u) {
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (w + 3u < nwords) {
+      v = *reinterpret_cast<const uint4*>(src + w);
+    } else {
+      if (w < nwords) v.x = src[w];
+      if (w + 1u < nwords) v.y = src[w + 1];
+      if (w + 2u < nwords) v.z = src[w + 2];
+    }
+    *reinterpret_cast<uint4*>(ring + (w & (kRingWords - 1u))) = v;
+  }
+}
+
 __global__ void __launch_bounds__(kInflateWarps * 32)
 png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__ offsets,
                    const int32_t* __restrict__ comp_bytes, int n, uint8_t* raw, size_t stride,
                    uint32_t expect, int32_t* __restrict__ status) {
   __shared__ Tables tabs[kInflateWarps];
+  __shared__ __align__(16) uint32_t rings[kInflateWarps][kRingWords];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int img = blockIdx.x * kInflateWarps + warp;
   if (img >= n) return;
   uint8_t* out = raw + (size_t)img * stride;
+  const int32_t nb = comp_bytes[img];
+  const uint32_t nwords = nb > 0 ? (uint32_t)((nb + 3) >> 2) : 0u;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(comp + offsets[img]);
+  uint32_t* ring = rings[warp];
+  ring_load(ring, src, nwords, 0u, kRingWords, lane);
+  uint32_t ring_hi = kRingWords;           // words [ring_hi - kRingWords, ring_hi) are in the ring
+  __syncwarp();
   State s;
   int ev = 0;
   if (lane == 0) {
-    const int32_t nb = comp_bytes[img];
     if (nb < 6) ev = EV_TRUNCATED;
-    else ev = inflate_begin(s, reinterpret_cast<const uint32_t*>(comp + offsets[img]),
-                            (uint32_t)((nb + 3) >> 2), out, expect);
+    else ev = inflate_begin(s, ring, nwords, kRingWords - 1u,
+                            ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin, out, expect);
   }
   ev = __shfl_sync(BOP_FULL_MASK, ev, 0);
   if (ev == 0) {
@@ -60,16 +83,25 @@ png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__
         o = s.o; len = s.m_len; dist = s.m_dist;
       }
       ev = __shfl_sync(BOP_FULL_MASK, ev, 0);
+      if (ev == EV_INPUT) {
+        // the reader is within kRingMargin words of the ring's end: everything more than that
+        // behind it is consumed, so the oldest kRingRefill words can be replaced
+        ring_load(ring, src, nwords, ring_hi, kRingRefill, lane);
+        ring_hi += kRingRefill;
+        __syncwarp();
+        if (lane == 0) s.br.limit = ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin;
+        continue;
+      }
       if (ev != EV_COPY) break;
       o = __shfl_sync(BOP_FULL_MASK, o, 0);
       len = __shfl_sync(BOP_FULL_MASK, len, 0);
       dist = __shfl_sync(BOP_FULL_MASK, dist, 0);
       // every source byte lies in the already written window [o - dist, o)
-      const uint8_t* src = out + o - dist;
+      const uint8_t* srcb = out + o - dist;
       if (dist >= len) {
-        for (uint32_t i = lane; i < len; i += 32) out[o + i] = src[i];
+        for (uint32_t i = lane; i < len; i += 32) out[o + i] = srcb[i];
       } else {
-        for (uint32_t i = lane; i < len; i += 32) out[o + i] = src[i % dist];
+        for (uint32_t i = lane; i < len; i += 32) out[o + i] = srcb[i % dist];
       }
       __syncwarp();
       if (lane == 0) s.o = o + len;
@@ -329,10 +361,17 @@ extern "C" int bop_png_decode_selftest_host(const void* idat, int32_t comp_bytes
   std::vector<uint8_t> raw(expect + 64, 0);
   Tables* t = new Tables;
   State s;
+  uint32_t input_limit = 64;
   int ev = comp_bytes < 6 ? (int)EV_TRUNCATED
-                          : inflate_begin(s, in.data(), (uint32_t)((comp_bytes + 3) >> 2), raw.data(), (uint32_t)expect);
-  while (ev == 0 || ev == EV_COPY) {
+                          : inflate_begin(s, in.data(), (uint32_t)((comp_bytes + 3) >> 2), 0xffffffffu,
+                                          input_limit, raw.data(), (uint32_t)expect);
+  while (ev == 0 || ev == EV_COPY || ev == EV_INPUT) {
     ev = inflate_run(s, *t);
+    if (ev == EV_INPUT) {        // the test hook hands the input out in slices, like the device ring
+      input_limit += 64;
+      s.br.limit = input_limit;
+      continue;
+    }
     if (ev != EV_COPY) break;
     uint8_t* o = raw.data() + s.o;
     for (uint32_t k = 0; k < s.m_len; ++k) o[k] = o[(ptrdiff_t)k - (ptrdiff_t)s.m_dist];

@@ -24,10 +24,15 @@ namespace bop_png {
 constexpr int kLitBits = 10;    // primary lookup width of the literal/length code
 constexpr int kDistBits = 8;    // primary lookup width of the distance code
 constexpr uint32_t kCoopMin = 16;  // matches at least this long are copied by the whole warp
+constexpr uint32_t kRingWords = 1024;   // device input ring per stream (4 KB of shared memory)
+constexpr uint32_t kRingRefill = 512;   // words loaded per EV_INPUT
+constexpr uint32_t kRingMargin = 256;   // the reader asks for input this far before the ring's end:
+                                        // more than one dynamic block header (<= 160 words) needs
 
 enum {
   EV_DONE = 0,           // final block finished
   EV_COPY = 1,           // caller copies m_len bytes from distance m_dist, then adds m_len to o
+  EV_INPUT = 2,          // caller loads more of the stream into the ring and raises br.limit
   EV_BAD_HEADER = -1,    // not a zlib stream (CM != 8, preset dictionary, bad check bits)
   EV_BAD_BLOCK = -2,     // reserved block type / stored LEN != ~NLEN
   EV_BAD_CODES = -3,     // over-subscribed or otherwise invalid Huffman code description
@@ -49,13 +54,17 @@ struct Tables {
 };
 
 struct BitReader {
-  const uint32_t* in;   // 4-byte aligned stream, zero padded to a whole word
+  // Word w of the 4-byte aligned, zero padded stream lives at in[w & mask]: the whole stream on
+  // the host (mask = ~0), a shared-memory ring on the device that the warp refills whenever the
+  // reader passes `limit` (EV_INPUT).
+  const uint32_t* in;
+  uint32_t mask, limit;
   uint32_t nwords, ipos;
   uint32_t nextw;       // word `ipos`, loaded one refill ahead so its latency is hidden
   uint64_t buf;
   int cnt;
-  BOP_HD void init(const uint32_t* p, uint32_t n) {
-    in = p; nwords = n; ipos = 0; buf = 0; cnt = 0;
+  BOP_HD void init(const uint32_t* p, uint32_t n, uint32_t ring_mask, uint32_t lim) {
+    in = p; nwords = n; mask = ring_mask; limit = lim; ipos = 0; buf = 0; cnt = 0;
     nextw = n > 0 ? p[0] : 0u;
   }
   BOP_HD void refill() {   // afterwards cnt > 32
@@ -63,9 +72,10 @@ struct BitReader {
       buf |= (uint64_t)nextw << cnt;
       cnt += 32;
       ++ipos;
-      nextw = ipos < nwords ? in[ipos] : 0u;
+      nextw = ipos < nwords ? in[ipos & mask] : 0u;
     }
   }
+  BOP_HD bool starved() const { return ipos > limit; }
   BOP_HD uint32_t peek(int n) const { return (uint32_t)buf & ((1u << n) - 1u); }
   BOP_HD void drop(int n) { buf >>= n; cnt -= n; }
   BOP_HD uint32_t bits(int n) { uint32_t v = peek(n); drop(n); return v; }
@@ -79,6 +89,7 @@ struct State {
   uint32_t o, cap;
   int in_block;     // 1 while inside a Huffman-coded block
   int final_block;
+  uint32_t stored_left;   // bytes of a stored block still to copy
   uint32_t m_len, m_dist;
 };
 
@@ -202,8 +213,10 @@ BOP_HD_NOINLINE int build_dynamic(BitReader& br, Tables& t) {
 }
 
 // zlib header (RFC 1950): CM = 8, window <= 32 KB, no preset dictionary, FCHECK.
-BOP_HD int inflate_begin(State& s, const uint32_t* in, uint32_t nwords, uint8_t* out, uint32_t cap) {
-  s.br.init(in, nwords);
+BOP_HD int inflate_begin(State& s, const uint32_t* in, uint32_t nwords, uint32_t ring_mask,
+                         uint32_t limit, uint8_t* out, uint32_t cap) {
+  s.br.init(in, nwords, ring_mask, limit);
+  s.stored_left = 0;
   s.out = out;
   s.o = 0;
   s.cap = cap;
@@ -225,8 +238,21 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
   const uint32_t cap = s.cap;
   int ev = EV_DONE;
   for (;;) {
+    if (s.stored_left) {
+      uint32_t left = s.stored_left;
+      while (left && !br.starved()) {
+        br.refill();
+        out[o++] = (uint8_t)br.bits(8);
+        --left;
+      }
+      s.stored_left = left;
+      if (left) { ev = EV_INPUT; break; }
+      if (br.overrun()) { ev = EV_TRUNCATED; break; }
+      continue;
+    }
     if (!s.in_block) {
       if (s.final_block) { ev = EV_DONE; break; }
+      if (br.starved()) { ev = EV_INPUT; break; }
       br.refill();
       if (br.overrun()) { ev = EV_TRUNCATED; break; }
       s.final_block = (int)br.bits(1);
@@ -239,11 +265,7 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
         const uint32_t nlen = br.bits(16);
         if ((len ^ nlen) != 0xffffu) { ev = EV_BAD_BLOCK; break; }
         if (o + len > cap) { ev = EV_OVERFLOW; break; }
-        for (uint32_t k = 0; k < len; ++k) {
-          br.refill();
-          out[o++] = (uint8_t)br.bits(8);
-        }
-        if (br.overrun()) { ev = EV_TRUNCATED; break; }
+        s.stored_left = len;
         continue;
       } else if (type == 1) {
         build_fixed(t);
@@ -257,65 +279,108 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
       s.in_block = 1;
     }
     // ---- Huffman-coded symbols --------------------------------------------------------
-    bool leave = false;
+    // One warp instruction per step of one lane: what counts here is the number of instructions
+    // and taken branches per symbol, so the checks that only guard against corrupt input are
+    // folded (one range test per match, input exhaustion looked at only when a word is loaded).
     for (;;) {
-      br.refill();
+      if (br.cnt <= 32) {
+        if (br.starved()) { ev = EV_INPUT; goto done; }
+        br.refill();
+      }
       int sym;
       {
         const uint32_t e = t.lit_fast[br.peek(kLitBits)];
         if (e & 15u) { br.drop((int)(e & 15u)); sym = (int)(e >> 4); }
-        else sym = decode_slow(br, t.lit_count, t.lit_sym, 15);
+        else {
+          sym = decode_slow(br, t.lit_count, t.lit_sym, 15);
+          if (sym < 0) { ev = EV_BAD_SYMBOL; goto done; }
+        }
       }
       if (sym < 256) {
-        if (sym < 0) { ev = EV_BAD_SYMBOL; leave = true; break; }
-        if (o >= cap) { ev = EV_OVERFLOW; leave = true; break; }
+        if (o >= cap) { ev = EV_OVERFLOW; goto done; }
         out[o++] = (uint8_t)sym;
         continue;
       }
       if (sym == 256) {
         s.in_block = 0;
-        if (br.overrun()) { ev = EV_TRUNCATED; leave = true; }
+        if (br.overrun()) { ev = EV_TRUNCATED; goto done; }
         break;
       }
       sym -= 257;
-      if (sym >= 29) { ev = EV_BAD_SYMBOL; leave = true; break; }
-      uint32_t len;
-      if (sym < 8) len = 3u + (uint32_t)sym;
-      else if (sym == 28) len = 258u;
-      else {
+      if (sym >= 29) { ev = EV_BAD_SYMBOL; goto done; }
+      uint32_t len = 3u + (uint32_t)sym;
+      if (sym >= 8) {
         const int eb = (sym - 4) >> 2;
-        len = ((4u + ((uint32_t)sym & 3u)) << eb) + 3u + br.bits(eb);
+        len = sym == 28 ? 258u : ((4u + ((uint32_t)sym & 3u)) << eb) + 3u + br.bits(eb);
       }
       br.refill();
-      int ds;
+      uint32_t ds;
       {
         const uint32_t e = t.dist_fast[br.peek(kDistBits)];
-        if (e & 15u) { br.drop((int)(e & 15u)); ds = (int)(e >> 4); }
-        else ds = decode_slow(br, t.dist_count, t.dist_sym, 15);
+        if (e & 15u) { br.drop((int)(e & 15u)); ds = e >> 4; }
+        else ds = (uint32_t)decode_slow(br, t.dist_count, t.dist_sym, 15);   // -1 -> out of range
       }
-      if (ds < 0 || ds >= 30) { ev = EV_BAD_SYMBOL; leave = true; break; }
-      uint32_t dist;
-      if (ds < 4) dist = 1u + (uint32_t)ds;
-      else {
-        const int eb = (ds >> 1) - 1;
-        dist = ((2u + ((uint32_t)ds & 1u)) << eb) + 1u + br.bits(eb);
+      if (ds >= 30u) { ev = EV_BAD_SYMBOL; goto done; }
+      uint32_t dist = 1u + ds;
+      if (ds >= 4u) {
+        const int eb = (int)(ds >> 1) - 1;
+        dist = ((2u + (ds & 1u)) << eb) + 1u + br.bits(eb);
       }
-      if (dist > o) { ev = EV_BAD_DISTANCE; leave = true; break; }
-      if (o + len > cap) { ev = EV_OVERFLOW; leave = true; break; }
-      if (br.overrun()) { ev = EV_TRUNCATED; leave = true; break; }
+      if (dist > o || o + len > cap) { ev = dist > o ? EV_BAD_DISTANCE : EV_OVERFLOW; goto done; }
       if (len >= kCoopMin) {
         s.m_len = len;
         s.m_dist = dist;
         ev = EV_COPY;
-        leave = true;
-        break;
+        goto done;
       }
+      // 3 <= len < kCoopMin.  Without overlap every load is issued before the first store (one
+      // memory round trip, not one per byte) and the two switches execute exactly len loads and
+      // len stores.
       const uint8_t* src = out + o - dist;
-      for (uint32_t k = 0; k < len; ++k) out[o + k] = src[k];
+      uint8_t* dst = out + o;
       o += len;
+      if (dist >= len) {
+        uint8_t b0, b1, b2, b3 = 0, b4 = 0, b5 = 0, b6 = 0, b7 = 0, b8 = 0, b9 = 0, b10 = 0, b11 = 0,
+                b12 = 0, b13 = 0, b14 = 0;
+        switch (len) {
+          case 15: b14 = src[14];  // fallthrough
+          case 14: b13 = src[13];  // fallthrough
+          case 13: b12 = src[12];  // fallthrough
+          case 12: b11 = src[11];  // fallthrough
+          case 11: b10 = src[10];  // fallthrough
+          case 10: b9 = src[9];    // fallthrough
+          case 9: b8 = src[8];     // fallthrough
+          case 8: b7 = src[7];     // fallthrough
+          case 7: b6 = src[6];     // fallthrough
+          case 6: b5 = src[5];     // fallthrough
+          case 5: b4 = src[4];     // fallthrough
+          case 4: b3 = src[3];     // fallthrough
+          default: b2 = src[2]; b1 = src[1]; b0 = src[0];
+        }
+        switch (len) {
+          case 15: dst[14] = b14;  // fallthrough
+          case 14: dst[13] = b13;  // fallthrough
+          case 13: dst[12] = b12;  // fallthrough
+          case 12: dst[11] = b11;  // fallthrough
+          case 11: dst[10] = b10;  // fallthrough
+          case 10: dst[9] = b9;    // fallthrough
+          case 9: dst[8] = b8;     // fallthrough
+          case 8: dst[7] = b7;     // fallthrough
+          case 7: dst[6] = b6;     // fallthrough
+          case 6: dst[5] = b5;     // fallthrough
+          case 5: dst[4] = b4;     // fallthrough
+          case 4: dst[3] = b3;     // fallthrough
+          default: dst[2] = b2; dst[1] = b1; dst[0] = b0;
+        }
+      } else if (dist == 1) {
+        const uint8_t v = src[0];
+        for (uint32_t k = 0; k < len; ++k) dst[k] = v;
+      } else {
+        for (uint32_t k = 0; k < len; ++k) dst[k] = src[k];
+      }
     }
-    if (leave) break;
   }
+done:
   s.br = br;
   s.o = o;
   return ev;

@@ -215,6 +215,12 @@ def _pinned_stack(dtype, n, height, width):
   return buf[:need].view(n, height, width)
 
 
+# One image keeps the GPU decoder busy for tens of milliseconds (a DEFLATE stream is serial); below
+# this many images per call the host threads are quicker.  The VSD driver is not affected: it
+# groups images across scenes (GpuDepthSource).
+GPU_DECODE_MIN_IMAGES = 192
+
+
 def gpu_depth_decode(paths):
   """True when the depth images of a chunk go through the GPU PNG decoder (all '.png', and
   BOP_B200_DEPTH_DECODE is not 'host')."""
@@ -232,7 +238,7 @@ def load_depth_stack(paths, scales, height, width, threads=None, device=None):
   import torch
   n = len(paths)
   threads = threads or _io_threads()      # PNG inflate releases the GIL: one decoder per host core
-  if device is not None and gpu_depth_decode(paths):
+  if device is not None and n >= GPU_DECODE_MIN_IMAGES and gpu_depth_decode(paths):
     from . import batch
     return batch.decode_depth_pngs(paths, height, width, device, threads), \
       np.asarray(scales, dtype=np.float32)
@@ -254,6 +260,83 @@ def load_depth_stack(paths, scales, height, width, threads=None, device=None):
     view[i] = im.astype(np.float32)
     view[i] *= np.float32(scales[i])
   return out, None
+
+
+class GpuDepthSource(object):
+  """The depth PNGs of a whole run, decoded on the GPU in groups that cut ACROSS scenes.
+
+  One DEFLATE stream is serial, so a single image takes the decoder tens of milliseconds however
+  few images are in flight; its throughput comes from thousands of streams decoding side by side
+  (one warp each).  The driver therefore registers the images of every scene up front and this
+  class decodes them `group` at a time (a scene of 100 images shares its launch with its
+  neighbours, a scene of 5,000 spans two), staging group g+1 on a host thread while group g is
+  in use.  Access is expected in registration order; groups behind the current one are freed."""
+
+  def __init__(self, batch, device, height, width, group=4096):
+    self.batch, self.device, self.h, self.w, self.group = batch, device, height, width, group
+    self.paths, self.index = [], {}
+    self.live, self.futs = {}, {}
+    self.pool = None
+
+  def register(self, scene_id, im_ids, paths):
+    for im_id, path in zip(im_ids, paths):
+      if (scene_id, im_id) not in self.index:
+        self.index[(scene_id, im_id)] = len(self.paths)
+        self.paths.append(path)
+
+  def _submit(self, g):
+    lo = g * self.group
+    if lo >= len(self.paths) or g in self.futs or g in self.live:
+      return
+    if self.pool is None:
+      self.pool = ThreadPoolExecutor(max_workers=1)
+    # the group's extent is fixed at submission: images registered later start a new read
+    self.futs[g] = self.pool.submit(self.batch.png_stage, self.paths[lo:lo + self.group],
+                                    _io_threads(), g & 1)
+
+  def _ensure(self, g, n_needed):
+    t = self.live.get(g)
+    if t is not None and t.shape[0] >= n_needed:
+      return t
+    self.live.pop(g, None)
+    if g in self.futs and len(self.futs[g].result()[0]) < n_needed:
+      self.futs.pop(g)                       # staged before later images were registered
+    self._submit(g)
+    staged = self.futs.pop(g).result()
+    self._submit(g + 1)
+    t = self.live[g] = self.batch.decode_depth_staged(staged, self.h, self.w, self.device)
+    return t
+
+  def get(self, scene_id, im_ids):
+    """-> CUDA int16 tensor [len(im_ids),H,W] of raw samples (a view when the images are
+    consecutive inside one group)."""
+    import torch
+    pos = np.asarray([self.index[(scene_id, i)] for i in im_ids], dtype=np.int64)
+    if pos.size == 0:
+      return torch.empty((0, self.h, self.w), dtype=torch.int16, device=self.device)
+    grp = pos // self.group
+    for g in [k for k in self.live if k < grp.min()]:
+      del self.live[g]
+    parts = []
+    for g in np.unique(grp):
+      local = pos[grp == g] - g * self.group
+      t = self._ensure(int(g), int(local.max()) + 1)
+      if np.array_equal(local, np.arange(local[0], local[0] + local.size)):
+        parts.append(t[int(local[0]):int(local[0]) + local.size])
+      else:
+        parts.append(t.index_select(0, torch.from_numpy(local).to(t.device)))
+    if len(parts) > 1 and not np.all(np.diff(grp) >= 0):
+      raise ValueError('depth images must be requested in registration order')
+    return parts[0] if len(parts) == 1 else torch.cat(parts, dim=0)
+
+  def close(self):
+    self.live.clear()
+    for f in self.futs.values():
+      f.cancel()
+    self.futs.clear()
+    if self.pool is not None:
+      self.pool.shutdown(wait=True)
+      self.pool = None
 
 
 # ---------------------------------------------------------------------------- compute
@@ -285,6 +368,29 @@ class ErrorEngine(object):
         diameter = self.models_info[obj_id]['diameter'] if self.models_info is not None else 0.0
         self.ms.add(obj_id, model['pts'], model.get('faces') if need_faces else None, syms, diameter)
     self.device = self.ms.device if self.ms is not None else torch.device(device or 'cuda:0')
+    self.depth_source = None
+
+  def _depth_paths(self, scene_id, im_ids):
+    return [self.dp_split['depth_tpath'].format(scene_id=scene_id, im_id=i) for i in im_ids]
+
+  def register_scene(self, scene_id, sp, sel):
+    """VSD only: announces the depth images the pairs `sel` of a scene will read, so that the
+    GPU PNG decoder can work on groups of images that cut across scenes (GpuDepthSource)."""
+    if self.p['error_type'] != 'vsd' or len(sel) == 0:
+      return
+    im_ids = [sp.im_ids[i] for i in np.unique(sp.im_pos[sel])]
+    paths = self._depth_paths(scene_id, im_ids)
+    if not gpu_depth_decode(paths):
+      return
+    if self.depth_source is None:
+      w, h = self.dp_split['im_size']
+      self.depth_source = GpuDepthSource(self.batch, self.device, h, w)
+    self.depth_source.register(scene_id, im_ids, paths)
+
+  def close(self):
+    if self.depth_source is not None:
+      self.depth_source.close()
+      self.depth_source = None
 
   def _K_rows(self, scene_camera, im_ids):
     return np.stack([np.asarray(scene_camera[i]['cam_K'], np.float64).reshape(9) for i in im_ids]) \
@@ -329,45 +435,33 @@ class ErrorEngine(object):
       return batch.cus_batch(self.ms, oi, pe, pg, K, h, w, gate=True).cpu().numpy().reshape(n, 1)
     raise ValueError('Unknown pose error function.')
 
-  def _vsd(self, scene_id, sp, scene_camera, sel, oi, pe, pg, images_per_chunk=1024):
+  def _vsd(self, scene_id, sp, scene_camera, sel, oi, pe, pg, images_per_chunk=2048):
     p, batch = self.p, self.batch
     w, h = self.dp_split['im_size']
     T = len(p['vsd_taus'])
     out = np.empty((len(sel), T))
     im_pos = sp.im_pos[sel]
     used = np.unique(im_pos)                      # images this rank touches, ascending position
-    chunks = [used[c0:c0 + images_per_chunk] for c0 in range(0, len(used), images_per_chunk)]
-    paths = [[self.dp_split['depth_tpath'].format(scene_id=scene_id, im_id=sp.im_ids[i]) for i in c]
-             for c in chunks]
-    # 16-bit PNGs (every BOP dataset) are inflated and unfiltered on the GPU: the host threads only
-    # read the files, and they stage chunk k+1 while the GPU works on chunk k.
-    # BOP_B200_DEPTH_DECODE=host keeps the OpenCV decode + zero-copy pinned path.
-    on_gpu = gpu_depth_decode([q for c in paths for q in c])
-    stager = ThreadPoolExecutor(max_workers=1) if on_gpu else None
-    fut = stager.submit(batch.png_stage, paths[0], _io_threads(), 0) if on_gpu and chunks else None
-    try:
-      for k, chunk in enumerate(chunks):
-        im_ids = [sp.im_ids[i] for i in chunk]
-        if on_gpu:
-          staged = fut.result()
-          if k + 1 < len(chunks):
-            fut = stager.submit(batch.png_stage, paths[k + 1], _io_threads(), (k + 1) & 1)
-          depth = batch.decode_depth_staged(staged, h, w, self.device)
-          sc = np.asarray([scene_camera[i]['depth_scale'] for i in im_ids], dtype=np.float32)
-        else:
-          scales = [scene_camera[i]['depth_scale'] for i in im_ids]
-          depth, sc = load_depth_stack(paths[k], scales, h, w)
-        rows = np.nonzero(np.isin(im_pos, chunk))[0]
-        local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
-        err = batch.vsd_batch(self.ms, oi[rows], pe[rows], pg[rows], depth, local,
-                              self._K_rows(scene_camera, im_ids), p['vsd_deltas'][self.dataset],
-                              p['vsd_taus'], p['vsd_normalized_by_diameter'], 'step', 'bop19',
-                              gate=True, depth_scale=sc,
-                              zero_copy=(not depth.is_cuda) and depth.is_pinned())
-        out[rows] = err.cpu().numpy()
-    finally:
-      if stager is not None:
-        stager.shutdown(wait=True)
+    # 16-bit PNGs (every BOP dataset) are inflated and unfiltered on the GPU; the host threads only
+    # read the files.  BOP_B200_DEPTH_DECODE=host keeps the OpenCV decode + zero-copy pinned path.
+    self.register_scene(scene_id, sp, sel)        # no-op if calc_errors announced the scene already
+    for c0 in range(0, len(used), images_per_chunk):
+      chunk = used[c0:c0 + images_per_chunk]
+      im_ids = [sp.im_ids[i] for i in chunk]
+      paths = self._depth_paths(scene_id, im_ids)
+      if self.depth_source is not None and gpu_depth_decode(paths):
+        depth = self.depth_source.get(scene_id, im_ids)
+        sc = np.asarray([scene_camera[i]['depth_scale'] for i in im_ids], dtype=np.float32)
+      else:
+        depth, sc = load_depth_stack(paths, [scene_camera[i]['depth_scale'] for i in im_ids], h, w)
+      rows = np.nonzero(np.isin(im_pos, chunk))[0]
+      local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
+      err = batch.vsd_batch(self.ms, oi[rows], pe[rows], pg[rows], depth, local,
+                            self._K_rows(scene_camera, im_ids), p['vsd_deltas'][self.dataset],
+                            p['vsd_taus'], p['vsd_normalized_by_diameter'], 'step', 'bop19',
+                            gate=True, depth_scale=sc,
+                            zero_copy=(not depth.is_cuda) and depth.is_pinned())
+      out[rows] = err.cpu().numpy()
     return out
 
 
@@ -475,15 +569,22 @@ def calc_errors(p, device=None, log=misc.log, write=True):
     # thread spends the next scene mostly inside the PNG decoders and the GPU calls, which do not.
     writer = ThreadPoolExecutor(max_workers=1) if (write and rank == 0) else None
     pending = []
+    # Pass 1 (host): flatten every scene and announce the depth images its pairs will read, so
+    # the GPU PNG decoder gets groups of thousands of images whatever the scene size.
+    plan = []
     for scene_id, scene_targets in targets_org.items():
       scene_camera = _memo(inout.load_scene_camera, dp_split['scene_camera_tpath'].format(scene_id=scene_id))
       scene_gt = _memo(inout.load_scene_gt, dp_split['scene_gt_tpath'].format(scene_id=scene_id))
       sp = flatten_scene(p, scene_id, scene_targets, ests_org.get(scene_id, {}), scene_gt)
+      sel = _shard_pairs(sp, rank, world)
+      engine.register_scene(scene_id, sp, sel)
+      plan.append((scene_id, scene_camera, sp, sel))
+    # Pass 2: the batched kernels, scene by scene.
+    for scene_id, scene_camera, sp, sel in plan:
       n_ests += sp.n_ests
       log('Calculating error {} - method: {}, dataset: {}{}, scene: {}, pairs: {}'.format(
         p['error_type'], method, dataset, ' - ' + split_type if split_type else '', scene_id,
         len(sp.rec)))
-      sel = _shard_pairs(sp, rank, world)
       errs = engine.compute(scene_id, sp, scene_camera, sel)
       if world > 1:
         errs = _gather_errors(errs, sel, len(sp.rec), engine.device, sp=sp, world=world)
@@ -491,6 +592,7 @@ def calc_errors(p, device=None, log=misc.log, write=True):
       scenes[scene_id] = records
       if writer is not None:
         pending.append(writer.submit(save_scene_errors, p, dataset, result_name, scene_id, records, log))
+    engine.close()
     if writer is not None:
       for f in pending:
         f.result()          # re-raises I/O errors
