@@ -127,6 +127,7 @@ def select_top_estimates(obj_ests, n_top_curr):
 def flatten_scene(p, scene_id, scene_targets, scene_ests, scene_gt):
   sp = ScenePairs()
   im_pos_of = {}
+  est_R, est_t, gt_R, gt_t = [], [], [], []
   for im_id, im_targets in scene_targets.items():
     gts = scene_gt[im_id]
     for obj_id, target in im_targets.items():
@@ -153,24 +154,36 @@ def flatten_scene(p, scene_id, scene_targets, scene_ests, scene_gt):
         if im_id not in im_pos_of:
           im_pos_of[im_id] = len(sp.im_ids)
           sp.im_ids.append(im_id)
-        pe = np.concatenate([np.asarray(est['R'], np.float64).reshape(9),
-                             np.asarray(est['t'], np.float64).reshape(3)])
+        pos = im_pos_of[im_id]
         for g in gt_ids:
           gt = gts[g]
           sp.rec.append(ri)
           sp.gt_id.append(g)
           sp.obj_id.append(obj_id)
-          sp.im_pos.append(im_pos_of[im_id])
-          sp.pose_est.append(pe)
-          sp.pose_gt.append(np.concatenate([np.asarray(gt['cam_R_m2c'], np.float64).reshape(9),
-                                            np.asarray(gt['cam_t_m2c'], np.float64).reshape(3)]))
+          sp.im_pos.append(pos)
+          est_R.append(est['R'])      # stacked once per scene below: one numpy call per pair
+          est_t.append(est['t'])      # costs more than the kernels spend on it
+          gt_R.append(gt['cam_R_m2c'])
+          gt_t.append(gt['cam_t_m2c'])
   n = len(sp.rec)
   sp.rec = np.asarray(sp.rec, dtype=np.int64)
   sp.gt_id = np.asarray(sp.gt_id, dtype=np.int64)
   sp.obj_id = np.asarray(sp.obj_id, dtype=np.int64)
   sp.im_pos = np.asarray(sp.im_pos, dtype=np.int32)
-  sp.pose_est = np.asarray(sp.pose_est, dtype=np.float64).reshape(n, 12)
-  sp.pose_gt = np.asarray(sp.pose_gt, dtype=np.float64).reshape(n, 12)
+
+  def stack(Rs, ts):
+    out = np.empty((n, 12), dtype=np.float64)
+    if n:
+      try:
+        out[:, :9] = np.asarray(Rs, dtype=np.float64).reshape(n, 9)
+        out[:, 9:] = np.asarray(ts, dtype=np.float64).reshape(n, 3)
+      except ValueError:       # ragged input: convert entry by entry (raises where the reference would)
+        for k in range(n):
+          out[k, :9] = np.asarray(Rs[k], np.float64).reshape(9)
+          out[k, 9:] = np.asarray(ts[k], np.float64).reshape(3)
+    return out
+  sp.pose_est = stack(est_R, est_t)
+  sp.pose_gt = stack(gt_R, gt_t)
   return sp
 
 
@@ -523,19 +536,24 @@ def records_for_tau(records, tau_id):
 
 
 def save_scene_errors(p, dataset, result_name, scene_id, records, log=misc.log):
-  def save(sign, recs):
+  """The error files of one scene in the reference's layout (eval_calc_errors.py:380-418,
+  inout.save_json): VSD -> one file per tau holding 1-element error lists."""
+  tails = inout.error_record_tails(records)
+
+  def save(sign, tau_id):
     path = p['out_errors_tpath'].format(eval_path=p['eval_path'], result_name=result_name,
                                         error_sign=sign, scene_id=scene_id)
     misc.ensure_dir(os.path.dirname(path))
     log('Saving errors to: {}'.format(path))
-    inout.save_json(path, recs)
+    with open(path, 'w') as f:
+      f.write(inout.dumps_error_records(records, tau_id, tails))
   if p['error_type'] == 'vsd':
     for tau_id, tau in enumerate(p['vsd_taus']):
       sign = misc.get_error_signature(p['error_type'], p['n_top'],
                                       vsd_delta=p['vsd_deltas'][dataset], vsd_tau=tau)
-      save(sign, records_for_tau(records, tau_id))
+      save(sign, tau_id)
   else:
-    save(misc.get_error_signature(p['error_type'], p['n_top']), records)
+    save(misc.get_error_signature(p['error_type'], p['n_top']), None)
 
 
 def calc_errors(p, device=None, log=misc.log, write=True):

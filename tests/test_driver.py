@@ -120,8 +120,38 @@ def test_writer_layout_roundtrip(driver_golden):
     for r in recs:
       r['errors'] = {int(k): v for k, v in r['errors'].items()}
     assert inout.dumps_errors_layout(recs) == text, key
+    assert inout.dumps_error_records(recs) == text, key       # the driver's fast writer
     n += 1
   assert n >= 60
+
+
+def test_fast_writer_equals_json_dumps():
+  """inout.dumps_error_records == the json.dumps-based layout, also for per-tau views, several GT
+  instances per record, records without GT, inf / nan / tiny / huge / integer-valued errors."""
+  from bop_toolkit_b200 import eval_calc_errors as ece, inout
+  rng = np.random.default_rng(0)
+  special = [float('inf'), -float('inf'), float('nan'), 0.0, -0.0, 1.0, 1e16, 1e-5, 1.5e-7, 123456789012345678.0,
+             0.1 + 0.2, 5e-324, 1.7976931348623157e308, 1e22, 1e15, 9999999999999998.0]
+  recs = []
+  for i in range(400):
+    n_gt = int(rng.integers(0, 4))
+    gts = sorted(rng.choice(30, n_gt, replace=False).tolist(), reverse=bool(i & 1))
+    errs = {}
+    for g in gts:
+      e = (rng.random(10) * 10.0 ** rng.integers(-8, 8, 10)).tolist()
+      if i % 7 == 0:
+        e[int(rng.integers(0, 10))] = special[int(rng.integers(0, len(special)))]
+      errs[int(g)] = e
+    recs.append({'im_id': int(rng.integers(0, 2000)), 'obj_id': int(rng.integers(1, 30)), 'est_id': i % 5,
+                 'score': [float(rng.random()), 1.0, -1.0, 3][i % 4], 'errors': errs})
+  for e in special:
+    recs.append({'im_id': 1, 'obj_id': 2, 'est_id': 0, 'score': e, 'errors': {4: [e] * 10}})
+  assert inout.dumps_error_records(recs) == inout.dumps_errors_layout(recs)
+  tails = inout.error_record_tails(recs)
+  for tau_id in (0, 3, 9):
+    assert inout.dumps_error_records(recs, tau_id, tails) == \
+      inout.dumps_errors_layout(ece.records_for_tau(recs, tau_id))
+  assert inout.dumps_error_records([]) == inout.dumps_errors_layout([])
 
 
 TOL = {'vsd': (0.0, 1e-3), 'cus': (0.0, 2e-3), 'adi': (1e-5, 1e-6), 'ad': (1e-5, 1e-6), 're': (1e-5, 1e-6), 'rete': (1e-5, 1e-6)}
