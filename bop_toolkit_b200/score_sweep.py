@@ -45,8 +45,9 @@ class ThresholdSweep(object):
 
     row_scene, row_im, row_obj, row_gt, row_valid = [], [], [], [], []
     est_rank, est_id, est_score = [], [], []
-    cand = []                 # per estimate: (rows, errors[C][n_cand]) in dict order
-    n_cols = None
+    # candidates (estimate, GT row) as flat Python lists, turned into arrays once at the end: a
+    # YCB-V-size run has 1.6e5 estimates and a numpy call per estimate was most of the score stage
+    c_est, c_slot, c_row, c_vals, c_diam, c_valid = [], [], [], [], [], []
     for scene_id, scene_targets in ctx['targets_org'].items():
       scene_gt, scene_gt_info = ecs.scene_gt_and_info(ctx, scene_id)
       by_im_obj = {}
@@ -54,11 +55,12 @@ class ThresholdSweep(object):
         by_im_obj.setdefault(e['im_id'], {}).setdefault(e['obj_id'], []).append(e)
       for im_id, im_targets in scene_targets.items():
         im_gts = scene_gt[im_id]
-        valid = ecs.gt_valid_mask(im_gts, scene_gt_info[im_id], im_targets, p['visib_gt_min'])
+        valid = [bool(v) for v in
+                 ecs.gt_valid_mask(im_gts, scene_gt_info[im_id], im_targets, p['visib_gt_min'])]
         row0 = len(row_gt)
         for gt_id, gt in enumerate(im_gts):
           row_scene.append(scene_id); row_im.append(im_id); row_obj.append(gt['obj_id'])
-          row_gt.append(gt_id); row_valid.append(bool(valid[gt_id]))
+          row_gt.append(gt_id); row_valid.append(valid[gt_id])
         im_errs = by_im_obj.get(im_id)
         if not im_errs:
           continue
@@ -66,38 +68,43 @@ class ThresholdSweep(object):
           if obj_id not in im_errs:
             continue
           errs = im_errs[obj_id]
-          order = np.argsort(-np.array([e['score'] for e in errs], dtype=np.float64), kind='stable')
+          if len(errs) == 1:
+            order = (0,)
+          else:   # descending score, stable: what np.argsort(-scores, kind='stable') gives
+            order = np.argsort(-np.array([e['score'] for e in errs], dtype=np.float64), kind='stable')
           if n_top > 0:
             order = order[:n_top]
-          diameter = float(models_info[obj_id]['diameter']) if by_diam else None
+          diameter = float(models_info[obj_id]['diameter']) if by_diam else 1.0
           for rank, k in enumerate(order):
             e = errs[k]
-            gts = list(e['errors'].keys())
-            vals = np.array([e['errors'][g] for g in gts], dtype=np.float64).reshape(len(gts), -1)
-            if n_cols is None:
-              n_cols = vals.shape[1]
-            if vals.shape[1] != n_cols:
-              raise ValueError('ThresholdSweep needs error lists of one length')
-            if by_diam:
-              vals = vals / diameter
-            if by_width:
-              vals = factor * vals
-            for j, g in enumerate(gts):
-              if not valid[g]:
-                vals[j, :] = np.inf
+            i = len(est_rank)
             est_rank.append(rank); est_id.append(e['est_id']); est_score.append(e['score'])
-            cand.append((np.array(gts, dtype=np.int64) + row0, vals))
-    self.n_cols = n_cols or 1
+            for j, (g, ev) in enumerate(e['errors'].items()):
+              c_est.append(i); c_slot.append(j); c_row.append(row0 + g); c_vals.append(ev)
+              c_diam.append(diameter); c_valid.append(valid[g])
+    n_est = len(est_rank)
+    try:
+      vals = np.array(c_vals, dtype=np.float64).reshape(len(c_vals), -1)
+    except ValueError:
+      raise ValueError('ThresholdSweep needs error lists of one length')
+    self.n_cols = vals.shape[1] if len(c_vals) else 1
+    if by_diam:
+      vals = vals / np.array(c_diam, dtype=np.float64)[:, None]
+    if by_width:
+      vals = factor * vals
+    if len(c_vals):
+      vals[~np.array(c_valid, dtype=bool)] = np.inf
     self.rows = dict(scene_id=row_scene, im_id=row_im, obj_id=row_obj, gt_id=row_gt, valid=row_valid)
     self.n_rows = len(row_gt)
-    n_est = len(cand)
-    g_max = max([len(c[0]) for c in cand] + [1])
+    c_est = np.array(c_est, dtype=np.int64)
+    c_slot = np.array(c_slot, dtype=np.int64)
+    g_max = int(c_slot.max()) + 1 if len(c_slot) else 1
     # padded candidate tables; the pad row (index n_rows) is permanently taken
     self.cand_rows = np.full((n_est, g_max), self.n_rows, dtype=np.int64)
     self.cand_err = np.full((self.n_cols, n_est, g_max), np.inf, dtype=np.float64)
-    for i, (r, v) in enumerate(cand):
-      self.cand_rows[i, :len(r)] = r
-      self.cand_err[:, i, :len(r)] = v.T
+    if len(c_slot):
+      self.cand_rows[c_est, c_slot] = np.array(c_row, dtype=np.int64)
+      self.cand_err[:, c_est, c_slot] = vals.T
     self.est_id, self.est_score = est_id, est_score
     rank = np.array(est_rank, dtype=np.int64)
     self.by_rank = [np.flatnonzero(rank == r) for r in range(int(rank.max()) + 1 if n_est else 0)]
