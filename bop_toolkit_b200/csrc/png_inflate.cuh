@@ -234,6 +234,13 @@ BOP_HD int inflate_begin(State& s, const uint32_t* in, uint32_t nwords, uint32_t
 BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
   BitReader br = s.br;
   uint8_t* const out = s.out;
+#ifdef __CUDA_ARCH__
+  // the device caller keeps the input ring and the tables in shared memory and writes to global
+  // memory: lets the compiler use LDS / STG instead of generic accesses
+  __builtin_assume(__isShared(br.in));
+  __builtin_assume(__isShared(&t));
+  __builtin_assume(__isGlobal(out));
+#endif
   uint32_t o = s.o;
   const uint32_t cap = s.cap;
   int ev = EV_DONE;
@@ -283,6 +290,19 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
     // and taken branches per symbol, so the checks that only guard against corrupt input are
     // folded (one range test per match, input exhaustion looked at only when a word is loaded).
     for (;;) {
+      // Runs of literals: one table look-up, one combined test (a literal whose code fits the
+      // primary table has an entry in [1, 4095]; 0 = long code, >= 4096 = end of block / length),
+      // everything else drops to the general step below.
+      for (;;) {
+        if (br.cnt <= 32) {
+          if (br.starved()) break;
+          br.refill();
+        }
+        const uint32_t e = t.lit_fast[br.peek(kLitBits)];
+        if (e - 1u >= 4095u || o >= cap) break;
+        br.drop((int)(e & 15u));
+        out[o++] = (uint8_t)(e >> 4);
+      }
       if (br.cnt <= 32) {
         if (br.starved()) { ev = EV_INPUT; goto done; }
         br.refill();
