@@ -10,7 +10,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 SO_PATH = os.path.join(CSRC, 'libbop_b200.so')
-SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu', 'png_depth.cu']
+SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu', 'png_depth.cu', 'error_json.cpp']
 HEADERS = ['common.cuh', 'raster.cuh', 'png_inflate.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
 
 BOP_MAX_TAUS = 16
@@ -111,6 +111,9 @@ _SIGNATURES = {
   'bop_png_decode_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I]),
   'bop_png_decode_dev': (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, ctypes.c_size_t, _P]),
   'bop_png_decode_selftest_host': (_I, [_P, ctypes.c_int32, _I, _I, _P]),
+  'bop_write_error_file_host': (_I, [ctypes.c_char_p, ctypes.c_int64, _P, _P, _P, _P, ctypes.c_int64,
+                                     _P, _P, _P, _I, _I]),
+  'bop_format_double_host': (_I, [ctypes.c_double, ctypes.c_char_p]),
 }
 EXPORTED_SYMBOLS = sorted(_SIGNATURES)
 

@@ -535,16 +535,49 @@ def records_for_tau(records, tau_id):
            'errors': {g: [e[tau_id]] for g, e in r['errors'].items()}} for r in records]
 
 
-def save_scene_errors(p, dataset, result_name, scene_id, records, log=misc.log):
+def _record_arrays(sp, errs):
+  """Flat arrays for bop_write_error_file_host, or None when the records hold anything the native
+  writer does not format exactly like json.dumps (non-int ids, non-float scores, unsorted pairs)."""
+  recs = sp.records
+  cols = [[r[k] for r in recs] for k in ('im_id', 'obj_id', 'est_id', 'score')]
+  if not all(type(v) is int for c in cols[:3] for v in c) or not all(type(v) is float for v in cols[3]):
+    return None
+  errs = np.ascontiguousarray(errs, dtype=np.float64)
+  rec, gt = np.ascontiguousarray(sp.rec, np.int64), np.ascontiguousarray(sp.gt_id, np.int64)
+  if errs.ndim != 2 or errs.shape[0] != rec.size:
+    return None
+  if rec.size > 1:
+    d = np.diff(rec)
+    if (d < 0).any() or ((d == 0) & (np.diff(gt) <= 0)).any():
+      return None
+  try:
+    ids = [np.array(c, dtype=np.int64) for c in cols[:3]]
+  except OverflowError:
+    return None
+  return ids + [np.array(cols[3], dtype=np.float64), rec, gt, errs]
+
+
+def save_scene_errors(p, dataset, result_name, scene_id, records, log=misc.log, sp=None, errs=None):
   """The error files of one scene in the reference's layout (eval_calc_errors.py:380-418,
-  inout.save_json): VSD -> one file per tau holding 1-element error lists."""
-  tails = inout.error_record_tails(records)
+  inout.save_json): VSD -> one file per tau holding 1-element error lists.  With the scene's
+  flat arrays (`sp`, `errs`) the text is produced by the native writer (same bytes, no GIL);
+  otherwise by inout.dumps_error_records."""
+  arrays = _record_arrays(sp, errs) if (sp is not None and errs is not None) else None
+  tails = inout.error_record_tails(records) if arrays is None else None
 
   def save(sign, tau_id):
     path = p['out_errors_tpath'].format(eval_path=p['eval_path'], result_name=result_name,
                                         error_sign=sign, scene_id=scene_id)
     misc.ensure_dir(os.path.dirname(path))
     log('Saving errors to: {}'.format(path))
+    if arrays is not None:
+      from . import _lib
+      im, ob, es, sc, rec, gt, e = arrays
+      _lib.check(_lib.lib().bop_write_error_file_host(
+        os.fsencode(path), len(im), im.ctypes.data, ob.ctypes.data, es.ctypes.data, sc.ctypes.data,
+        rec.size, rec.ctypes.data, gt.ctypes.data, e.ctypes.data, e.shape[1],
+        -1 if tau_id is None else tau_id))
+      return
     with open(path, 'w') as f:
       f.write(inout.dumps_error_records(records, tau_id, tails))
   if p['error_type'] == 'vsd':
@@ -609,7 +642,8 @@ def calc_errors(p, device=None, log=misc.log, write=True):
       records = fill_records(sp, errs)
       scenes[scene_id] = records
       if writer is not None:
-        pending.append(writer.submit(save_scene_errors, p, dataset, result_name, scene_id, records, log))
+        pending.append(writer.submit(save_scene_errors, p, dataset, result_name, scene_id, records, log,
+                                     sp, errs))
     engine.close()
     if writer is not None:
       for f in pending:

@@ -326,6 +326,19 @@ int bop_png_decode_selftest_host(const void* idat, int32_t comp_bytes, int heigh
                                  uint16_t* depth_out);
 
 
+/* ---- error files -------------------------------------------------------------------------
+ * The text inout.save_json (bop_toolkit_lib/inout.py:85-113) writes for the record list of
+ * scripts/eval_calc_errors.py:380-418, from flat arrays: records r = 0..n_rec-1 with
+ * (im_id, obj_id, est_id, score); pairs sorted by record, GT ids ascending within a record,
+ * errs [n_pairs][n_cols].  col >= 0 writes the 1-element lists of one VSD tau file, col < 0
+ * whole lists.  Floats are formatted like Python's float.__repr__ / json (Infinity, NaN).     */
+int bop_write_error_file_host(const char* path, int64_t n_rec, const int64_t* im_id,
+                              const int64_t* obj_id, const int64_t* est_id, const double* score,
+                              int64_t n_pairs, const int64_t* pair_rec, const int64_t* pair_gt,
+                              const double* errs, int n_cols, int col);
+/* float.__repr__(v) as json.dumps writes it, NUL-terminated into out32 (>= 32 bytes). */
+int bop_format_double_host(double v, char* out32);
+
 #ifdef __cplusplus
 }
 #endif

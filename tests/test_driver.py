@@ -189,3 +189,47 @@ def test_driver_files_match_reference(dataset, driver_golden, tmp_path):
           assert np.all(np.abs(ea[fin] - eb[fin]) <= atol + rtol * np.abs(eb[fin])), \
             (error_type, n_top, rel, ra, rb)
   print('driver files: %d of %d byte-identical to the reference' % (identical, total))
+
+
+def test_native_error_file_writer_equals_python(tmp_path):
+  """bop_write_error_file_host (flat arrays -> file, no GIL) writes the bytes of the json.dumps
+  layout: VSD tau files, single-value files, two-element lists ('rete'), records without GT and
+  with several GT instances, inf / nan / tiny / huge values; odd records fall back to Python."""
+  from bop_toolkit_b200 import _lib, eval_calc_errors as ece, misc
+  _lib.build()
+  rng = np.random.default_rng(4)
+  special = [float('inf'), float('nan'), 0.0, 1.0, 1e16, 1e-5, 1.5e-7, 0.1 + 0.2, 5e-324, 1e22, 1e15, 123456.0]
+  sp = ece.ScenePairs()
+  rec, gt = [], []
+  for i in range(500):
+    n_gt = int(rng.integers(0, 4))
+    gts = sorted(rng.choice(30, n_gt, replace=False).tolist())
+    sp.records.append({'im_id': int(rng.integers(0, 2000)), 'obj_id': int(rng.integers(1, 30)),
+                       'est_id': i % 5, 'score': float(rng.random()) if i % 9 else -1.0,
+                       'errors': {int(g): None for g in gts}})
+    rec += [i] * n_gt
+    gt += gts
+  sp.rec, sp.gt_id = np.array(rec, np.int64), np.array(gt, np.int64)
+  for et, T in (('vsd', 10), ('mssd', 1), ('rete', 2)):
+    errs = rng.random((len(rec), T)) * 10.0 ** rng.integers(-8, 8, (len(rec), T))
+    errs[rng.random(errs.shape) < 0.05] = rng.choice(special, int((rng.random(errs.shape) < 0.05).sum()) or 1)[0]
+    for k, v in enumerate(special):
+      errs[k % len(rec), k % T] = v
+    records = ece.fill_records(sp, errs)
+    outs = {}
+    for mode in ('native', 'python'):
+      p = ece.default_params()
+      p.update({'error_type': et, 'n_top': -1, 'eval_path': str(tmp_path / (mode + et)), 'vsd_taus': list(p['vsd_taus'])})
+      kw = dict(sp=sp, errs=errs) if mode == 'native' else {}
+      ece.save_scene_errors(p, 'lm', 'res', 7, records, log=lambda s: None, **kw)
+      files = {}
+      for dirpath, _, names in os.walk(p['eval_path']):
+        for name in names:
+          files[os.path.relpath(os.path.join(dirpath, name), p['eval_path'])] = \
+            open(os.path.join(dirpath, name), 'rb').read()
+      outs[mode] = files
+    assert len(outs['native']) == (10 if et == 'vsd' else 1)
+    assert outs['native'] == outs['python'], et
+  assert ece._record_arrays(sp, errs) is not None
+  sp.records[3]['score'] = 1          # an int score prints as `1`: not the native writer's job
+  assert ece._record_arrays(sp, errs) is None
