@@ -114,6 +114,7 @@ _SIGNATURES = {
   'bop_write_error_file_host': (_I, [ctypes.c_char_p, ctypes.c_int64, _P, _P, _P, _P, ctypes.c_int64,
                                      _P, _P, _P, _I, _I]),
   'bop_format_double_host': (_I, [ctypes.c_double, ctypes.c_char_p]),
+  'bop_parse_results_csv_host': (_I, [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int64, _P, _P, _P, _P, _P, _P]),
 }
 EXPORTED_SYMBOLS = sorted(_SIGNATURES)
 

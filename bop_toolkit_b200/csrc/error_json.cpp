@@ -160,3 +160,78 @@ extern "C" int bop_write_error_file_host(const char* path, int64_t n_rec, const 
     return bop_set_error_msg(-2, "bop_write_error_file_host: short write");
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Result-file reader: the numbers of a BOP19 results CSV (inout.load_bop_results,
+// bop_toolkit_lib/inout.py:221-261: `scene_id,im_id,obj_id,score,R(9 space-sep),t(3 space-sep),
+// time`, header line skipped) into flat arrays.  Only the plain forms are taken (digits, sign,
+// decimal point, exponent, inf / nan as std::from_chars reads them); any line that Python's
+// int() / float() might read differently -- or reject -- makes the call return 1 so that the
+// caller parses the file line by line the reference's way and raises the reference's errors.
+// ---------------------------------------------------------------------------------------------
+namespace {
+inline const char* skip_ws(const char* p, const char* e) {
+  while (p < e && (*p == ' ' || *p == '\t' || *p == '\r')) ++p;
+  return p;
+}
+inline bool read_i64(const char*& p, const char* e, int64_t& v) {
+  p = skip_ws(p, e);
+  const auto r = std::from_chars(p, e, v);
+  if (r.ec != std::errc() || r.ptr == p) return false;
+  p = skip_ws(r.ptr, e);
+  return true;
+}
+inline bool read_f64(const char*& p, const char* e, double& v) {
+  p = skip_ws(p, e);
+  if (p < e && *p == '+') return false;
+  const auto r = std::from_chars(p, e, v, std::chars_format::general);
+  if (r.ec != std::errc() || r.ptr == p) return false;
+  // "1.5x" / "1_0" / hex and the like: not ours to judge
+  if (r.ptr < e && *r.ptr != ' ' && *r.ptr != '\t' && *r.ptr != '\r' && *r.ptr != ',') return false;
+  p = skip_ws(r.ptr, e);
+  return true;
+}
+inline bool eat(const char*& p, const char* e, char c) {
+  if (p < e && *p == c) { ++p; return true; }
+  return false;
+}
+}  // namespace
+
+// Returns 0 and *n_out rows on success, 1 if the text holds anything irregular (nothing is
+// guaranteed about the outputs then), < 0 on bad arguments.  Arrays hold `cap` rows.
+extern "C" int bop_parse_results_csv_host(const char* text, size_t nbytes, int64_t cap,
+                                          int64_t* ids, double* score, double* R, double* t,
+                                          double* time, int64_t* n_out) {
+  if (!text || !n_out || cap < 0 || (cap > 0 && !(ids && score && R && t && time)))
+    return bop_set_error_msg(-1, "bop_parse_results_csv_host: bad arguments");
+  static const char header[] = "scene_id,im_id,obj_id,score,R,t,time";
+  const char* p = text;
+  const char* const end = text + nbytes;
+  int64_t n = 0;
+  bool first = true;
+  while (p < end) {
+    const char* eol = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+    if (!eol) eol = end;
+    if (first) {
+      first = false;
+      const std::string line(p, (size_t)(eol - p));
+      if (line.find(header) != std::string::npos) { p = eol < end ? eol + 1 : end; continue; }
+    }
+    if (n >= cap) return 1;
+    const char* q = p;
+    int64_t* id = ids + 3 * n;
+    if (!read_i64(q, eol, id[0]) || !eat(q, eol, ',') || !read_i64(q, eol, id[1]) || !eat(q, eol, ',') ||
+        !read_i64(q, eol, id[2]) || !eat(q, eol, ',') || !read_f64(q, eol, score[n]) || !eat(q, eol, ','))
+      return 1;
+    for (int k = 0; k < 9; ++k)
+      if (!read_f64(q, eol, R[9 * n + k])) return 1;
+    if (!eat(q, eol, ',')) return 1;
+    for (int k = 0; k < 3; ++k)
+      if (!read_f64(q, eol, t[3 * n + k])) return 1;
+    if (!eat(q, eol, ',') || !read_f64(q, eol, time[n]) || q != eol) return 1;
+    ++n;
+    p = eol < end ? eol + 1 : end;
+  }
+  *n_out = n;
+  return 0;
+}

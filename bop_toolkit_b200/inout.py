@@ -124,12 +124,9 @@ def load_scene_gt(path):
   return sg
 
 
-def load_bop_results(path, version='bop19'):
-  """BOP19 results CSV -> list of dicts (inout.py:221-261): header line skipped, each line
-  `scene_id,im_id,obj_id,score,R(9 space-sep),t(3 space-sep),time`."""
+def _load_bop_results_py(path):
+  """Line-by-line parse exactly as the reference does it (inout.py:221-261)."""
   results = []
-  if version != 'bop19':
-    raise ValueError('Unknown version of BOP results.')
   header = 'scene_id,im_id,obj_id,score,R,t,time'
   with open(path, 'r') as f:
     for line_id, line in enumerate(f):
@@ -145,6 +142,45 @@ def load_bop_results(path, version='bop19'):
         't': np.array(list(map(float, elems[5].split())), np.float64).reshape((3, 1)),
         'time': float(elems[6])})
   return results
+
+
+def load_bop_results(path, version='bop19'):
+  """BOP19 results CSV -> list of dicts (inout.py:221-261): header line skipped, each line
+  `scene_id,im_id,obj_id,score,R(9 space-sep),t(3 space-sep),time`.
+  A plainly formatted file is parsed by the native reader (bop_parse_results_csv_host: the
+  per-line numpy calls of the reference cost ~10 us per estimate); 'R' / 't' are then views into
+  one array each -- read-only for the callers.  Anything irregular is parsed line by line the
+  reference's way, which also raises the reference's errors."""
+  if version != 'bop19':
+    raise ValueError('Unknown version of BOP results.')
+  try:
+    from . import _lib
+    L = _lib.lib()
+  except (ImportError, OSError):
+    return _load_bop_results_py(path)
+  import ctypes
+  with open(path, 'rb') as f:
+    raw = f.read()
+  cap = raw.count(b'\n') + 1
+  ids = np.empty((cap, 3), np.int64)
+  score, tm = np.empty(cap, np.float64), np.empty(cap, np.float64)
+  R, t = np.empty((cap, 3, 3), np.float64), np.empty((cap, 3, 1), np.float64)
+  n = ctypes.c_int64()
+  rc = L.bop_parse_results_csv_host(raw, len(raw), cap, ids.ctypes.data, score.ctypes.data,
+                                    R.ctypes.data, t.ctypes.data, tm.ctypes.data, ctypes.byref(n))
+  if rc != 0:
+    return _load_bop_results_py(path)
+  n = n.value
+  import gc
+  was_on = gc.isenabled()
+  gc.disable()        # 1e5..1e6 small containers: the generational collector would rescan them
+  try:
+    return [{'scene_id': a, 'im_id': b, 'obj_id': c, 'score': s, 'R': Ri, 't': ti, 'time': tt}
+            for (a, b, c), s, Ri, ti, tt in zip(ids[:n].tolist(), score[:n].tolist(), list(R[:n]),
+                                                list(t[:n]), tm[:n].tolist())]
+  finally:
+    if was_on:
+      gc.enable()
 
 
 def save_bop_results(path, results, version='bop19'):

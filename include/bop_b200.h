@@ -339,6 +339,13 @@ int bop_write_error_file_host(const char* path, int64_t n_rec, const int64_t* im
 /* float.__repr__(v) as json.dumps writes it, NUL-terminated into out32 (>= 32 bytes). */
 int bop_format_double_host(double v, char* out32);
 
+/* The numbers of a BOP19 results CSV (inout.load_bop_results, bop_toolkit_lib/inout.py:221-261)
+ * into flat arrays of `cap` rows: ids [n][3] = scene_id, im_id, obj_id; score [n]; R [n][9];
+ * t [n][3]; time [n].  Returns 0 on success, 1 when a line is anything but plainly formatted
+ * numbers (the caller then parses the file the reference's way and raises its errors).        */
+int bop_parse_results_csv_host(const char* text, size_t nbytes, int64_t cap, int64_t* ids,
+                               double* score, double* R, double* t, double* time, int64_t* n_out);
+
 #ifdef __cplusplus
 }
 #endif

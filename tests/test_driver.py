@@ -233,3 +233,38 @@ def test_native_error_file_writer_equals_python(tmp_path):
   assert ece._record_arrays(sp, errs) is not None
   sp.records[3]['score'] = 1          # an int score prints as `1`: not the native writer's job
   assert ece._record_arrays(sp, errs) is None
+
+
+def test_native_results_reader_equals_reference_parse(tmp_path):
+  """inout.load_bop_results through bop_parse_results_csv_host == the reference's line-by-line
+  parse (types, shapes, values bit for bit); irregular files take the Python path and raise the
+  reference's errors."""
+  from bop_toolkit_b200 import _lib, inout
+  _lib.build()
+  rng = np.random.default_rng(2)
+  res = [{'scene_id': int(rng.integers(1, 60)), 'im_id': int(rng.integers(0, 3000)), 'obj_id': int(rng.integers(1, 31)),
+          'score': float(rng.random()) if i % 5 else 1.0, 'R': rng.normal(size=(3, 3)),
+          't': rng.normal(size=(3, 1)) * 10.0 ** rng.integers(-3, 5), 'time': [0.25, -1, 1e-5][i % 3]}
+         for i in range(3000)]
+  path = str(tmp_path / 'm_lm-test.csv')
+  inout.save_bop_results(path, res)
+  a, b = inout.load_bop_results(path), inout._load_bop_results_py(path)
+  assert len(a) == len(b) == 3000
+  for x, y in zip(a, b):
+    assert list(x) == list(y)
+    for k in ('scene_id', 'im_id', 'obj_id', 'score', 'time'):
+      assert x[k] == y[k] and type(x[k]) is type(y[k])
+    assert x['R'].shape == (3, 3) and x['t'].shape == (3, 1) and x['R'].dtype == np.float64
+    assert np.array_equal(x['R'], y['R']) and np.array_equal(x['t'], y['t'])
+  # forms only Python reads (underscores, leading '+') fall back and still load
+  open(path, 'w').write('scene_id,im_id,obj_id,score,R,t,time\r\n 1, 2 ,3,+0.5,1 0 0 0 1 0 0 0 1e0,1 2 3,-1\r\n'
+                        '4,5,6,1_0,1 0 0 0 1 0 0 0 1, 1 2 3 ,inf')
+  r = inout.load_bop_results(path)
+  assert [e['score'] for e in r] == [0.5, 10.0] and r[1]['time'] == float('inf')
+  for bad in ('1,2,3,0.5,1 0 0 0 1 0 0 0 1,1 2 3\n', '1,2,3,0.5,1 0 0 0 1 0 0 0 1,1 2 3,0.1\n\n',
+              '1,2,3,0.5,1 0 0 0 1 0 0 0,1 2 3,0.1', '1,2,x,0.5,1 0 0 0 1 0 0 0 1,1 2 3,0.1'):
+    open(path, 'w').write(bad)
+    with pytest.raises(ValueError):
+      inout.load_bop_results(path)
+  open(path, 'w').write('scene_id,im_id,obj_id,score,R,t,time')
+  assert inout.load_bop_results(path) == []
