@@ -134,9 +134,11 @@ def load_context(p, dataset, split, split_type, ctx):
 def scene_gt_and_info(ctx, scene_id):
   if scene_id not in ctx['scene_gt']:
     dp_split = ctx['dp_split']
-    ctx['scene_gt'][scene_id] = inout.load_scene_gt(dp_split['scene_gt_tpath'].format(scene_id=scene_id))
-    ctx['scene_gt_info'][scene_id] = inout.load_json(
-      dp_split['scene_gt_info_tpath'].format(scene_id=scene_id), keys_to_int=True)
+    # scene_gt through the error stage's parse cache: a one-process evaluation reads it once
+    from .eval_calc_errors import _memo
+    ctx['scene_gt'][scene_id] = _memo(inout.load_scene_gt, dp_split['scene_gt_tpath'].format(scene_id=scene_id))
+    ctx['scene_gt_info'][scene_id] = inout.load_json_scene(
+      dp_split['scene_gt_info_tpath'].format(scene_id=scene_id))
   return ctx['scene_gt'][scene_id], ctx['scene_gt_info'][scene_id]
 
 

@@ -21,6 +21,15 @@ def load_json(path, keys_to_int=False):
     return json.load(f, object_hook=conv) if keys_to_int else json.load(f)
 
 
+def load_json_scene(path):
+  """Per-scene BOP files (scene_camera / scene_gt / scene_gt_info: {im_id: ...}) with the image
+  ids as ints.  Same result as load_json(path, keys_to_int=True) -- only the top level of these
+  files has digit keys -- without an object hook on each of the ~1e4 inner dicts."""
+  with open(path, 'r') as f:
+    d = json.load(f)
+  return {int(k) if k.lstrip('-').isdigit() else k: v for k, v in d.items()}
+
+
 def dumps_errors_layout(content):
   """Text layout of inout.save_json (inout.py:85-113): one element per line, keys sorted,
   2-space indent, no trailing newline; inf serialises as `Infinity`."""
@@ -100,7 +109,7 @@ def save_json(path, content):
 def load_scene_camera(path):
   """scene_camera.json -> {im_id: {'cam_K': 3x3, 'cam_R_w2c': 3x3, 'cam_t_w2c': 3x1, ...}}
   (inout.py:140-160)."""
-  sc = load_json(path, keys_to_int=True)
+  sc = load_json_scene(path)
   for cam in sc.values():
     if 'cam_K' in cam:
       cam['cam_K'] = np.array(cam['cam_K'], dtype=np.float64).reshape((3, 3))
@@ -114,7 +123,7 @@ def load_scene_camera(path):
 def load_scene_gt(path):
   """scene_gt.json -> {im_id: [{'obj_id', 'cam_R_m2c': 3x3, 'cam_t_m2c': 3x1}, ...]}
   (inout.py:182-198)."""
-  sg = load_json(path, keys_to_int=True)
+  sg = load_json_scene(path)
   for gts in sg.values():
     for gt in gts:
       if 'cam_R_m2c' in gt:
