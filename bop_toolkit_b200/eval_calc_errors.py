@@ -189,6 +189,26 @@ def flatten_scene(p, scene_id, scene_targets, scene_ests, scene_gt):
 
 # ------------------------------------------------------------------------------ host I/O
 _MEMO = {}
+_FLAT = {}
+
+
+def flatten_scene_cached(p, scene_id, scene_targets, scene_ests, scene_gt, files):
+  """flatten_scene, remembered per (input files, scene, n_top, skip_missing): the pairs of a scene
+  do not depend on the error type, and a BOP19 evaluation flattens every scene three times.  The
+  flat arrays are shared (read-only); the record skeletons are fresh on every call because
+  fill_records writes the errors into them and the caller keeps them."""
+  key = tuple((f, os.stat(f).st_mtime_ns, os.stat(f).st_size) for f in files) + \
+    (scene_id, p['n_top'], bool(p['skip_missing']))
+  base = _FLAT.get(key)
+  if base is None:
+    if len(_FLAT) >= 256:
+      _FLAT.clear()
+    base = _FLAT[key] = flatten_scene(p, scene_id, scene_targets, scene_ests, scene_gt)
+  sp = ScenePairs()
+  sp.__dict__.update(base.__dict__)
+  sp.records = [{'im_id': r['im_id'], 'obj_id': r['obj_id'], 'est_id': r['est_id'], 'score': r['score'],
+                 'errors': dict.fromkeys(r['errors'])} for r in base.records]
+  return sp
 
 
 def _memo(fn, path, *args):
@@ -626,7 +646,11 @@ def calc_errors(p, device=None, log=misc.log, write=True):
     for scene_id, scene_targets in targets_org.items():
       scene_camera = _memo(inout.load_scene_camera, dp_split['scene_camera_tpath'].format(scene_id=scene_id))
       scene_gt = _memo(inout.load_scene_gt, dp_split['scene_gt_tpath'].format(scene_id=scene_id))
-      sp = flatten_scene(p, scene_id, scene_targets, ests_org.get(scene_id, {}), scene_gt)
+      sp = flatten_scene_cached(
+        p, scene_id, scene_targets, ests_org.get(scene_id, {}), scene_gt,
+        (os.path.join(p['results_path'], result_filename),
+         os.path.join(dp_split['base_path'], p['targets_filename']),
+         dp_split['scene_gt_tpath'].format(scene_id=scene_id)))
       sel = _shard_pairs(sp, rank, world)
       engine.register_scene(scene_id, sp, sel)
       plan.append((scene_id, scene_camera, sp, sel))

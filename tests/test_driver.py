@@ -268,3 +268,32 @@ def test_native_results_reader_equals_reference_parse(tmp_path):
       inout.load_bop_results(path)
   open(path, 'w').write('scene_id,im_id,obj_id,score,R,t,time')
   assert inout.load_bop_results(path) == []
+
+
+def test_flatten_cache_hands_out_fresh_records(dataset):
+  """flatten_scene_cached: same arrays and skeletons as flatten_scene, but records that a second
+  pass can fill without touching what the first pass returned."""
+  from bop_toolkit_b200 import dataset_params, eval_calc_errors as ece, inout
+  p = _params(dataset, 'mssd', -1, '/nonexistent')
+  dp = dataset_params.get_split_params(p['datasets_path'], 'lm', 'test')
+  tpath = os.path.join(dp['base_path'], p['targets_filename'])
+  rpath = os.path.join(p['results_path'], p['result_filenames'][0])
+  torg, eorg = {}, {}
+  for t in inout.load_json(tpath):
+    torg.setdefault(t['scene_id'], {}).setdefault(t['im_id'], {})[t['obj_id']] = t
+  for e in inout.load_bop_results(rpath):
+    eorg.setdefault(e['scene_id'], {}).setdefault(e['im_id'], {}).setdefault(e['obj_id'], []).append(e)
+  scene_id = sorted(torg)[0]
+  gpath = dp['scene_gt_tpath'].format(scene_id=scene_id)
+  gt = inout.load_scene_gt(gpath)
+  ref = ece.flatten_scene(p, scene_id, torg[scene_id], eorg.get(scene_id, {}), gt)
+  a = ece.flatten_scene_cached(p, scene_id, torg[scene_id], eorg.get(scene_id, {}), gt, (rpath, tpath, gpath))
+  ra = ece.fill_records(a, np.full((len(a.rec), 1), 1.0))
+  b = ece.flatten_scene_cached(p, scene_id, torg[scene_id], eorg.get(scene_id, {}), gt, (rpath, tpath, gpath))
+  assert b.records == ref.records and b.records is not a.records          # unfilled skeletons again
+  rb = ece.fill_records(b, np.full((len(b.rec), 1), 2.0))
+  assert all(v == [1.0] for r in ra for v in r['errors'].values())
+  assert all(v == [2.0] for r in rb for v in r['errors'].values())
+  for k in ('rec', 'gt_id', 'obj_id', 'im_pos', 'pose_est', 'pose_gt'):
+    assert np.array_equal(getattr(b, k), getattr(ref, k))
+  assert b.im_ids == ref.im_ids and b.n_ests == ref.n_ests
