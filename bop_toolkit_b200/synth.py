@@ -184,6 +184,8 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
     with open(os.path.join(ds, folder, 'models_info.json'), 'w') as f:
       json.dump(info, f)
   targets, lines = [], ['scene_id,im_id,obj_id,score,R,t,time']
+  from concurrent.futures import ThreadPoolExecutor
+  pool, writes = ThreadPoolExecutor(max_workers=8), []
   fmt = lambda a: ' '.join(repr(float(x)) for x in np.asarray(a).reshape(-1))
   for si, scene_id in enumerate(scene_ids):
     sdir = os.path.join(ds, split, '%06d' % scene_id)
@@ -206,8 +208,9 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
         comp = np.where((d > 0) & ((comp == 0) | (d < comp)), d, comp)
       gt[str(im_id)] = gts
       depth = degrade_depth(comp, seed=int(rng.integers(1 << 30)), K=Kim)
-      cv2.imwrite(os.path.join(sdir, 'depth', '%06d.png' % im_id),
-                  np.clip(np.round(depth / scale), 0, 65535).astype(np.uint16))
+      # PNG encoding runs on worker threads (cv2 releases the GIL); the files do not depend on it
+      writes.append(pool.submit(cv2.imwrite, os.path.join(sdir, 'depth', '%06d.png' % im_id),
+                                np.clip(np.round(depth / scale), 0, 65535).astype(np.uint16)))
       present = sorted(set(int(o) for o in chosen))
       for oid in present:
         targets.append({'im_id': im_id, 'inst_count': chosen.count(oid), 'obj_id': oid,
@@ -229,10 +232,15 @@ def write_bop_dataset(root, render_fn, dataset='lmo', split='test', scene_ids=(2
           lines.append('%d,%d,%d,%r,%s,%s,%r' % (scene_id, im_id, oid, score, fmt(R_e), fmt(t_e), 0.25))
       lines.append('%d,%d,%d,%r,%s,%s,%r' % (scene_id, im_id, 99, 0.9, fmt(np.eye(3)),
                                              fmt([0, 0, 800.0]), 0.25))   # non-target object
+    for w in writes:
+      if not w.result():
+        raise IOError('cannot write a depth image under ' + sdir)
+    del writes[:]
     with open(os.path.join(sdir, 'scene_camera.json'), 'w') as f:
       json.dump(cam, f)
     with open(os.path.join(sdir, 'scene_gt.json'), 'w') as f:
       json.dump(gt, f)
+  pool.shutdown(wait=True)
   with open(os.path.join(ds, 'test_targets_bop19.json'), 'w') as f:
     json.dump(targets, f)
   result_filename = '%s_%s-%s.csv' % (method, dataset, split)
