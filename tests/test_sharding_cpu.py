@@ -86,3 +86,61 @@ def test_gather_records_world2(tmp_path):
   i = r0['ids'][order]
   assert np.allclose(e[:, 0], i[:, 1] + 0.01 * i[:, 3])
   assert np.all(np.isinf(e[i[:, 3] == 2, 1]))
+
+
+def test_gpu_depth_source_grouping_on_cpu():
+  """Host logic of eval_calc_errors.GpuDepthSource with a stand-in decoder (no GPU): images are
+  decoded in groups that cut across scenes, requests are served as views or concatenations in
+  request order, groups behind the reader are dropped, late registrations re-stage a group."""
+  import torch
+  from bop_toolkit_b200 import eval_calc_errors as ece
+
+  class FakeBatch(object):
+    def __init__(self):
+      self.staged, self.decoded = [], []
+
+    def png_stage(self, paths, threads, slot):
+      self.staged.append((list(paths), slot))
+      return (list(paths),)
+
+    def decode_depth_staged(self, staged, h, w, device):
+      paths = staged[0]
+      self.decoded.append(list(paths))
+      ids = torch.tensor([int(p.split('_')[-1]) for p in paths], dtype=torch.int16)
+      return ids.view(-1, 1, 1).expand(len(paths), h, w).contiguous()
+
+  fb = FakeBatch()
+  src = ece.GpuDepthSource(fb, 'cpu', 2, 3, group=5)
+  uid = {}
+  for scene, n in ((1, 3), (2, 4), (3, 6)):          # 13 images -> groups of 5, 5, 3
+    ims = list(range(10, 10 + n))
+    for i in ims:
+      uid[(scene, i)] = len(uid)
+    src.register(scene, ims, ['s%d_%d' % (scene, uid[(scene, i)]) for i in ims])
+  src.register(1, [10], ['ignored_99'])               # already known: not added twice
+  assert len(src.paths) == 13
+
+  def ids(t):
+    return t[:, 0, 0].tolist()
+  a = src.get(1, [10, 11, 12])
+  assert ids(a) == [0, 1, 2] and a.shape == (3, 2, 3)
+  assert a.data_ptr() == src.live[0].data_ptr()       # consecutive inside one group: a view
+  assert [len(p) for p, _ in fb.staged] == [5, 5]     # group 1 is staged while group 0 is in use
+  b = src.get(2, [10, 11, 12, 13])                    # spans groups 0 and 1
+  assert ids(b) == [3, 4, 5, 6] and sorted(src.live) == [0, 1]
+  c = src.get(3, [12, 10])                            # not consecutive: gathered in request order
+  assert ids(c) == [9, 7] and sorted(src.live) == [1]        # group 0 dropped
+  d = src.get(3, [11, 13, 14, 15])                    # groups 1 and 2
+  assert ids(d) == [8, 10, 11, 12] and sorted(src.live) == [1, 2]
+  assert [len(p) for p in fb.decoded] == [5, 5, 3]
+  assert [slot for _, slot in fb.staged] == [0, 1, 0]
+  import pytest
+  with pytest.raises(ValueError):
+    src.get(3, [15, 11])                              # across groups, backwards
+  # a scene announced late lands in the last, partly filled group: that group is decoded again
+  src.register(4, [1, 2], ['s4_13', 's4_14'])
+  e = src.get(4, [1, 2])
+  assert ids(e) == [13, 14] and [len(p) for p in fb.decoded][-1] == 5
+  assert src.get(4, []).shape == (0, 2, 3)
+  src.close()
+  assert src.live == {} and src.pool is None
