@@ -48,19 +48,39 @@ class VsdParams(ctypes.Structure):
     ('width', ctypes.c_int32), ('gate', ctypes.c_int32), ('depth_dtype', ctypes.c_int32)]
 
 
+def _source_hash(paths, cmd):
+  import hashlib
+  h = hashlib.sha256(' '.join(cmd).encode())
+  for p in paths:
+    with open(p, 'rb') as f:
+      h.update(os.path.basename(p).encode() + b'\0' + f.read())
+  return h.hexdigest()
+
+
 def build(force=False, verbose=False):
-  """Compiles the CUDA sources for sm_100a into csrc/libbop_b200.so (in-tree)."""
+  """Compiles the CUDA sources for sm_100a into csrc/libbop_b200.so (in-tree).  Whether the
+  library is current is decided by a hash of the sources and the compile command kept beside it
+  (libbop_b200.so.src): file times do not survive copying the tree to another machine."""
   srcs = [os.path.join(CSRC, s) for s in SOURCES]
   deps = srcs + [os.path.join(CSRC, h) for h in HEADERS]
-  if not force and os.path.exists(SO_PATH):
-    so_m = os.path.getmtime(SO_PATH)
-    if all(os.path.getmtime(d) <= so_m for d in deps):
-      return SO_PATH
   cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
          '-Xcompiler', '-fPIC', '-shared', '-o', SO_PATH] + srcs
+  want = _source_hash(deps, [c for c in cmd if c != SO_PATH and c not in srcs] + SOURCES)
+  stamp = SO_PATH + '.src'
+  if not force and os.path.exists(SO_PATH) and os.path.exists(stamp):
+    with open(stamp) as f:
+      if f.read().strip() == want:
+        return SO_PATH
+  import shutil
+  if shutil.which('nvcc') is None and os.path.exists(SO_PATH) and not force:
+    return SO_PATH          # a machine without the toolkit runs what was built elsewhere
   if verbose:
     cmd.insert(1, '-Xptxas=-v')
+  if os.path.exists(stamp):
+    os.remove(stamp)
   subprocess.check_call(cmd, cwd=CSRC)
+  with open(stamp, 'w') as f:
+    f.write(want)
   return SO_PATH
 
 
