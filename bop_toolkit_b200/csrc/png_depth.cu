@@ -96,6 +96,7 @@ png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__
       o = __shfl_sync(BOP_FULL_MASK, o, 0);
       len = __shfl_sync(BOP_FULL_MASK, len, 0);
       dist = __shfl_sync(BOP_FULL_MASK, dist, 0);
+      __syncwarp();   // lane 0's stores are ordered before the other lanes' loads
       // every source byte lies in the already written window [o - dist, o)
       const uint8_t* srcb = out + o - dist;
       if (dist >= len) {
