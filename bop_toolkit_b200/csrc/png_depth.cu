@@ -53,7 +53,8 @@ __device__ __forceinline__ void ring_load(uint32_t* ring, const uint32_t* __rest
 __global__ void __launch_bounds__(kInflateWarps * 32)
 png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__ offsets,
                    const int32_t* __restrict__ comp_bytes, int n, uint8_t* raw, size_t stride,
-                   uint32_t expect, int32_t* __restrict__ status) {
+                   uint32_t expect, int32_t* __restrict__ status,
+                   uint32_t* __restrict__ adler_out) {
   __shared__ Tables tabs[kInflateWarps];
   __shared__ __align__(16) uint32_t rings[kInflateWarps][kRingWords];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -111,6 +112,7 @@ png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__
   if (lane == 0) {
     if (ev == EV_DONE && s.o != expect) ev = EV_SHORT;
     status[img] = ev;
+    adler_out[img] = ev == EV_DONE ? s.adler : 0u;
   }
 }
 
@@ -123,7 +125,8 @@ __device__ __forceinline__ int paeth(int a, int b, int c) {
 // Shared memory: per warp two rows of 2*width bytes (current and previous), 16-byte aligned.
 __global__ void __launch_bounds__(kUnfilterWarps * 32)
 png_unfilter_kernel(const uint8_t* __restrict__ raw, size_t stride, int n, int height, int width,
-                    uint16_t* __restrict__ depth, int32_t* __restrict__ status) {
+                    uint16_t* __restrict__ depth, int32_t* __restrict__ status,
+                    const uint32_t* __restrict__ adler_expect) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int img = blockIdx.x * kUnfilterWarps + warp;
@@ -138,9 +141,24 @@ png_unfilter_kernel(const uint8_t* __restrict__ raw, size_t stride, int n, int h
   uint16_t* dst = depth + (size_t)img * height * width;
   const int seg = (width + 31) >> 5;      // pixels per lane for the Sub scan
   int bad = 0;
+  // Adler-32 (RFC 1950) of the inflated bytes, a row at a time: for a block of L bytes
+  // A' = A + sum b_i, B' = B + L A + sum (L - i) b_i  (mod 65521); what libpng / zlib verify on the host.
+  uint32_t adA = 1u, adB = 0u;
+  const uint32_t L = (uint32_t)rowb + 1u;
   for (int r = 0; r < height; ++r, src += rowb + 1, dst += width) {
     const int ft = src[0];
-    for (int i = lane; i < rowb; i += 32) cur[i] = src[1 + i];
+    uint32_t sa = 0u, sw = 0u;
+    if (lane == 0) { sa = (uint32_t)ft; sw = L * (uint32_t)ft; }
+    for (int i = lane; i < rowb; i += 32) {
+      const uint32_t b = src[1 + i];
+      cur[i] = (uint8_t)b;
+      sa += b;
+      sw += (uint32_t)(rowb - i) * b;
+    }
+    sa = __reduce_add_sync(BOP_FULL_MASK, sa);
+    sw = __reduce_add_sync(BOP_FULL_MASK, sw % 65521u);
+    adB = (uint32_t)(((unsigned long long)adB + (unsigned long long)(L % 65521u) * adA + sw) % 65521ull);
+    adA = (adA + sa) % 65521u;
     __syncwarp();
     if (ft == 1) {
       // Sub: per byte lane a prefix sum mod 256 along the row -> segment sums, warp scan, replay
@@ -198,7 +216,10 @@ png_unfilter_kernel(const uint8_t* __restrict__ raw, size_t stride, int n, int h
     __syncwarp();
     uint8_t* tmp = cur; cur = prev; prev = tmp;
   }
-  if (bad && lane == 0) status[img] = EV_BAD_FILTER;
+  if (lane == 0) {
+    if (bad) status[img] = EV_BAD_FILTER;
+    else if (((adB << 16) | adA) != adler_expect[img]) status[img] = EV_BAD_CHECKSUM;
+  }
 }
 
 // ---- host side: PNG container ---------------------------------------------------------------
@@ -316,7 +337,7 @@ extern "C" int bop_png_scan_host(void* file_bytes, size_t nbytes, bop_png_info* 
 
 extern "C" size_t bop_png_decode_workspace_bytes(int n, int height, int width) {
   if (n <= 0 || height <= 0 || width <= 0) return 256;
-  return (size_t)n * image_stride(height, width) + 256;
+  return (size_t)n * image_stride(height, width) + 256 + round_up((size_t)n * 4, 256);
 }
 
 extern "C" int bop_png_decode_dev(const void* comp, const int64_t* offsets, const int32_t* comp_bytes,
@@ -336,15 +357,16 @@ extern "C" int bop_png_decode_dev(const void* comp, const int64_t* offsets, cons
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   uint8_t* raw = reinterpret_cast<uint8_t*>(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   const size_t stride = image_stride(height, width);
+  uint32_t* adler = reinterpret_cast<uint32_t*>(raw + (size_t)n * stride);
   const uint32_t expect = (uint32_t)((size_t)height * (2 * (size_t)width + 1));
   bop_prof_begin(BOP_PROF_PNG, s);
   png_inflate_kernel<<<(n + kInflateWarps - 1) / kInflateWarps, kInflateWarps * 32, 0, s>>>(
-    static_cast<const uint8_t*>(comp), offsets, comp_bytes, n, raw, stride, expect, status);
+    static_cast<const uint8_t*>(comp), offsets, comp_bytes, n, raw, stride, expect, status, adler);
   BOP_LAUNCH_CHECK();
   if (smem > 48 * 1024)
     BOP_CUDA(cudaFuncSetAttribute(png_unfilter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   png_unfilter_kernel<<<(n + kUnfilterWarps - 1) / kUnfilterWarps, kUnfilterWarps * 32, smem, s>>>(
-    raw, stride, n, height, width, depth_out, status);
+    raw, stride, n, height, width, depth_out, status, adler);
   BOP_LAUNCH_CHECK();
   bop_prof_end(BOP_PROF_PNG, s);
   return 0;
@@ -381,6 +403,14 @@ extern "C" int bop_png_decode_selftest_host(const void* idat, int32_t comp_bytes
   delete t;
   if (ev == EV_DONE && s.o != expect) ev = EV_SHORT;
   if (ev != EV_DONE) return ev;
+  {
+    uint32_t A = 1u, B = 0u;
+    for (size_t i = 0; i < expect; ++i) {
+      A = (A + raw[i]) % 65521u;
+      B = (B + A) % 65521u;
+    }
+    if (((B << 16) | A) != s.adler) return EV_BAD_CHECKSUM;
+  }
   std::vector<uint8_t> prev(rowb, 0), cur(rowb);
   for (int r = 0; r < height; ++r) {
     const uint8_t* src = raw.data() + (size_t)r * (rowb + 1);

@@ -41,7 +41,8 @@ enum {
   EV_OVERFLOW = -6,      // more output than the image holds
   EV_TRUNCATED = -7,     // input ended inside the stream
   EV_SHORT = -8,         // stream ended before the image was complete (set by the caller)
-  EV_BAD_FILTER = -9     // PNG row filter type above 4 (set by the unfilter pass)
+  EV_BAD_FILTER = -9,    // PNG row filter type above 4 (set by the unfilter pass)
+  EV_BAD_CHECKSUM = -10  // Adler-32 of the inflated bytes differs from the stream's trailer
 };
 
 // Per-stream decode tables: shared memory on the device (3.7 KB per warp).
@@ -91,6 +92,7 @@ struct State {
   int final_block;
   uint32_t stored_left;   // bytes of a stored block still to copy
   uint32_t m_len, m_dist;
+  uint32_t adler;         // the stream's Adler-32 trailer (RFC 1950), valid after EV_DONE
 };
 
 // Canonical-code decode one bit at a time (zlib's contrib/puff method): used for the code-length
@@ -223,6 +225,7 @@ BOP_HD int inflate_begin(State& s, const uint32_t* in, uint32_t nwords, uint32_t
   s.in_block = 0;
   s.final_block = 0;
   s.m_len = s.m_dist = 0;
+  s.adler = 0;
   s.br.refill();
   const uint32_t cmf = s.br.bits(8), flg = s.br.bits(8);
   if ((cmf & 15u) != 8u || (cmf >> 4) > 7u || (flg & 32u) || ((cmf << 8) | flg) % 31u) return EV_BAD_HEADER;
@@ -258,7 +261,19 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
       continue;
     }
     if (!s.in_block) {
-      if (s.final_block) { ev = EV_DONE; break; }
+      if (s.final_block) {
+        // the trailer: four bytes, big-endian, on the next byte boundary
+        if (br.starved()) { ev = EV_INPUT; break; }
+        br.drop(br.cnt & 7);
+        uint32_t a = 0;
+        for (int k = 0; k < 4; ++k) {
+          br.refill();
+          a = (a << 8) | br.bits(8);
+        }
+        s.adler = a;
+        ev = br.overrun() ? (int)EV_TRUNCATED : (int)EV_DONE;
+        break;
+      }
       if (br.starved()) { ev = EV_INPUT; break; }
       br.refill();
       if (br.overrun()) { ev = EV_TRUNCATED; break; }

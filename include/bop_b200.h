@@ -291,7 +291,7 @@ int bop_vsd_set_exact(int exact);
  * greyscale PNG) as called per image by scripts/eval_calc_errors.py:236-243.  The host only
  * reads the files and strips the PNG container; zlib inflate and the PNG row filters run on
  * the GPU, one warp per image, and leave uint16 samples in HBM in the layout the VSD entry
- * points take as BOP_DEPTH_U16.  Chunk CRCs and the zlib Adler-32 are not verified.         */
+ * points take as BOP_DEPTH_U16.  The zlib Adler-32 is verified on the device; chunk CRCs are not.         */
 #define BOP_PNG_IO_ERROR          (-101)  /* file missing / unreadable                         */
 #define BOP_PNG_NOT_PNG           (-102)  /* bad signature or IHDR                             */
 #define BOP_PNG_TRUNCATED         (-103)  /* chunk runs past the end of the file, no IDAT      */

@@ -174,13 +174,35 @@ def test_corrupt_streams_fail_cleanly(tmp_path):
       continue
     out = np.empty((H, W), np.uint16)
     rc = _lib.lib().bop_png_decode_selftest_host(cb, nb.value, H, W, out.ctypes.data)
-    assert -9 <= rc <= 0
+    assert -10 <= rc <= 0
     detected += rc != 0
   assert detected > 30          # most single-bit flips desynchronise the Huffman stream
   # truncated stream
   cb, info, nb = _scan(cases[1][0])
   out = np.empty((H, W), np.uint16)
   assert _lib.lib().bop_png_decode_selftest_host(cb, nb // 2, H, W, out.ctypes.data) < 0
+
+
+def _flip_stored_payload(src_path, dst_path):
+  """A level-0 (stored blocks) file with one payload bit flipped: every block header stays valid,
+  only the Adler-32 trailer can tell."""
+  b = bytearray(open(src_path, 'rb').read())
+  pos = b.index(b'IDAT') + 4 + 2 + 5 + 20000      # zlib header, first stored-block header, into the data
+  b[pos] ^= 0x10
+  open(dst_path, 'wb').write(bytes(b))
+
+
+def test_adler32_mismatch_is_reported(tmp_path):
+  _lib.build()
+  cases = make_cases(str(tmp_path))
+  stored = [c for c in cases if '_l0_' in c[0]][0]
+  bad = str(tmp_path / 'bad_adler.png')
+  _flip_stored_payload(stored[0], bad)
+  cb, info, nb = _scan(bad)
+  out = np.empty((H, W), np.uint16)
+  assert _lib.lib().bop_png_decode_selftest_host(cb, nb, H, W, out.ctypes.data) == -10
+  cb, info, nb = _scan(stored[0])
+  assert _lib.lib().bop_png_decode_selftest_host(cb, nb, H, W, out.ctypes.data) == 0
 
 
 # ------------------------------------------------------------------------------------- GPU
@@ -230,6 +252,11 @@ def test_gpu_decode_errors(tmp_path):
   open(cut, 'wb').write(bytes(b))
   with pytest.raises(IOError):
     batch.decode_depth_pngs([cases[0][0], cut], H, W, 'cuda:0')
+  stored = [c for c in make_cases(str(tmp_path)) if '_l0_' in c[0]][0]
+  bad = str(tmp_path / 'bad_adler.png')
+  _flip_stored_payload(stored[0], bad)
+  with pytest.raises(IOError, match='status -10'):      # valid structure, wrong Adler-32
+    batch.decode_depth_pngs([stored[0], bad], H, W, 'cuda:0')
   # a 16-bit file the device path does not take (RGB): decoded by OpenCV, first channel
   rgb16 = str(tmp_path / 'rgb16.png')
   cv2.imwrite(rgb16, np.dstack([cases[0][1]] * 3))
