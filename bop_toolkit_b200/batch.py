@@ -713,3 +713,17 @@ def depth_bytes_fetched(device, depth_dtype_code):
 
 def kernel_launch_count():
   return int(_lib.lib().bop_kernel_launch_count())
+
+
+def debug_triangle_list(models, n_pairs, height, width, pair, pose):
+  """Test hook: the geometry pass's triangle list of (pair, pose) from the last vsd_batch call with
+  these sizes on models.device -> int32 [n, 6] snapped window positions (1/256 px)."""
+  dev = models.device
+  ws = _workspaces[(dev.type, dev.index)].buf
+  cap = 2 * ((models.max_geom + 7) & ~7)
+  xy = np.zeros((cap, 6), dtype=np.int32)
+  cnt = ctypes.c_int(0)
+  _lib.check(_lib.lib().bop_vsd_debug_triangle_list(
+    ws.data_ptr(), int(n_pairs), int(height), int(width), models.max_geom, int(pair), int(pose),
+    xy.ctypes.data, cap, ctypes.byref(cnt)))
+  return xy[:min(cap, cnt.value)]

@@ -7,7 +7,7 @@
 //   * window position u = fx X/Z + cx, v = fy Y/Z + cy; image pixel (r, c) samples the ray through
 //     (u, v) = (c + 0.5, r + 0.5);
 //   * value = nearest-surface camera Z at the sample point (1/Z is affine in screen space), depth
-//     test LESS, no culling, no blending; background = 0;
+//     test LESS, no culling, no blending; background = 0 (the tile holds max 1/Z, see z_merge_if);
 //   * like every OpenGL implementation, window positions are snapped to a sub-pixel grid before
 //     rasterisation (GL_SUBPIXEL_BITS; 8 bits here = 1/256 px), which makes the edge functions
 //     exact integers: coverage is watertight by construction and the top-left rule resolves
@@ -134,41 +134,62 @@ __device__ __forceinline__ float rcp_fast(float x) {
   return r;
 }
 
-// Depth at pixel (x, y) of a triangle's plane (see TriSetup).  256 x - vx is an exact float.
+// 1/Z at pixel (x, y) of a triangle's plane (see TriSetup).  256 x - vx is an exact float.
 __device__ __forceinline__ float plane_row(float pb, float iz0, int y, int vy) {
   return __fmaf_rn(pb, (float)((y << kSubBits) - vy), iz0);
 }
-__device__ __forceinline__ float plane_depth(float pa, float rowbase, float fdx) {
-  return rcp_fast(__fmaf_rn(pa, fdx, rowbase));
+__device__ __forceinline__ float plane_iz(float pa, float rowbase, float fdx) {
+  return __fmaf_rn(pa, fdx, rowbase);
 }
 
-// z-test + merge.  The tile starts at +inf bits (0x7f800000): negative, NaN and +inf candidates
-// compare >= that as unsigned integers, so no range check is needed.
-__device__ __forceinline__ void z_merge(unsigned* __restrict__ p, float Z) {
-  const unsigned zb = __float_as_uint(Z);
-  if (zb < *p) atomicMin(p, zb);
+// The z-tile keeps, per pixel, the LARGEST 1/Z drawn so far as float bits (0 = nothing drawn):
+// depth test LESS on Z is GREATER on 1/Z, and because the reciprocal is monotone
+// min_t rcp(iz_t) == rcp(max_t iz_t) bit for bit, so ONE reciprocal per pixel when the tile is
+// read (tile_depth) replaces one per covered candidate in the raster loops.  Signed integer max:
+// positive floats order like their bit patterns, and a non-positive 1/Z (rounding of a plane that
+// crosses zero; outside the parity domain) is negative or zero as an integer and never wins.
+// The store is a predicated shared-memory reduction (cover >= 0 <=> the three biased edge
+// functions are all non-negative): no branch in the per-candidate loop.
+__device__ __forceinline__ void z_merge_if(unsigned saddr, float iz, int cover) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, 0;\n\t@p red.shared.max.s32 [%0], %1;\n\t}"
+      :: "r"(saddr), "r"(__float_as_int(iz)), "r"(cover) : "memory");
+}
+__device__ __forceinline__ unsigned smem_addr(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+// Depth (camera Z) of a tile entry; 0 where nothing was drawn (or the depth is not finite).
+__device__ __forceinline__ float tile_depth(unsigned bits) {
+  if ((int)bits <= 0) return 0.f;
+  const float z = rcp_fast(__uint_as_float(bits));
+  return __float_as_uint(z) < BOP_INF_BITS_F32 ? z : 0.f;
 }
 
 // Rasterises a small triangle (32-bit path) into the z-tile.  One thread; incremental edge
-// stepping; the depth plane is evaluated only at covered pixels (1 FFMA + 1 MUFU.RCP).
+// stepping, 8 instructions per candidate pixel.  The triangle lists are sorted by candidate-
+// rectangle size (assemble_kernel), so the 32 lanes of a warp run both loops with (nearly) the
+// same trip counts.
 __device__ __forceinline__ void tri_raster_small(const TriSetup& T, unsigned* __restrict__ z, int zx0,
                                                  int zy0, int zstride) {
   int r0 = T.C[0], r1 = T.C[1], r2 = T.C[2];
   const float fdx0 = (float)((T.bx0 << kSubBits) - T.vx);
   float fdy = (float)((T.by0 << kSubBits) - T.vy);
-  unsigned* zrow = z + (T.by0 - zy0) * zstride - zx0;
-  for (int y = T.by0; y <= T.by1; ++y) {
+  unsigned zrow = smem_addr(z + (T.by0 - zy0) * zstride + (T.bx0 - zx0));
+  const int w = T.bx1 - T.bx0 + 1;
+  for (int h = T.by1 - T.by0 + 1; h > 0; --h) {
     int e0 = r0, e1 = r1, e2 = r2;
     const float rowbase = __fmaf_rn(T.pb, fdy, T.iz0);
     float fdx = fdx0;
-    for (int x = T.bx0; x <= T.bx1; ++x) {
-      if ((e0 | e1 | e2) >= 0) z_merge(zrow + x, plane_depth(T.pa, rowbase, fdx));
+    unsigned zp = zrow;
+    for (int i = w; i > 0; --i) {
+      z_merge_if(zp, plane_iz(T.pa, rowbase, fdx), e0 | e1 | e2);
       e0 += T.A[0]; e1 += T.A[1]; e2 += T.A[2];
       fdx += (float)kSubOne;
+      zp += 4;
     }
     r0 += T.B[0]; r1 += T.B[1]; r2 += T.B[2];
     fdy += (float)kSubOne;
-    zrow += zstride;
+    zrow += 4 * zstride;
   }
 }
 
@@ -180,6 +201,7 @@ __device__ __forceinline__ void tri_raster_warp(const TriSetup& T, int lane, uns
   const int lw_log = bw > 16 ? 5 : (bw > 8 ? 4 : (bw > 4 ? 3 : 2));
   const int lx = lane & ((1 << lw_log) - 1), ly = lane >> lw_log;
   const int sx = 1 << lw_log, sy = 32 >> lw_log;
+  const unsigned zb = smem_addr(z);
   for (int y = T.by0 + ly; y <= T.by1; y += sy) {
     const int dy = y - T.by0;
     const float rowbase = plane_row(T.pb, T.iz0, y, T.vy);
@@ -188,9 +210,8 @@ __device__ __forceinline__ void tri_raster_warp(const TriSetup& T, int lane, uns
       const int e0 = T.C[0] + T.A[0] * dx + T.B[0] * dy;
       const int e1 = T.C[1] + T.A[1] * dx + T.B[1] * dy;
       const int e2 = T.C[2] + T.A[2] * dx + T.B[2] * dy;
-      if ((e0 | e1 | e2) >= 0)
-        z_merge(z + (y - zy0) * zstride + (x - zx0),
-                plane_depth(T.pa, rowbase, (float)((x << kSubBits) - T.vx)));
+      z_merge_if(zb + 4u * (unsigned)((y - zy0) * zstride + (x - zx0)),
+                 plane_iz(T.pa, rowbase, (float)((x << kSubBits) - T.vx)), e0 | e1 | e2);
     }
   }
 }
@@ -235,16 +256,18 @@ __device__ __forceinline__ void tri_raster_large(const TriSetup64& T, int lane, 
                                                  int zstride) {
   const int bw = T.bx1 - T.bx0 + 1;
   const int n = bw * (T.by1 - T.by0 + 1);
+  const unsigned zb = smem_addr(z);
   for (int c = lane; c < n; c += nlanes) {
     const int yy = c / bw, xx = c - yy * bw;
     const long long e0 = T.C[0] + T.A[0] * xx + T.B[0] * yy;
     const long long e1 = T.C[1] + T.A[1] * xx + T.B[1] * yy;
     const long long e2 = T.C[2] + T.A[2] * xx + T.B[2] * yy;
-    if ((e0 | e1 | e2) >= 0) {
+    {
       // Same plane expression as the 32-bit paths.
       const int x = T.bx0 + xx, y = T.by0 + yy;
-      z_merge(z + (y - zy0) * zstride + (x - zx0),
-              plane_depth(T.pa, plane_row(T.pb, T.iz0, y, T.vy), (float)((x << kSubBits) - T.vx)));
+      z_merge_if(zb + 4u * (unsigned)((y - zy0) * zstride + (x - zx0)),
+                 plane_iz(T.pa, plane_row(T.pb, T.iz0, y, T.vy), (float)((x << kSubBits) - T.vx)),
+                 ((e0 | e1 | e2) >= 0) ? 0 : -1);
     }
   }
 }

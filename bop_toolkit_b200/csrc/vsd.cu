@@ -40,11 +40,12 @@ struct PairDesc {
   double diameter;
   int x0, y0, w, h;       // union ROI; x0 and w are multiples of 4
   int obj, im;
-  int n_poses, pad;
+  int n_poses;
+  int nbs;                // row bands the triangle lists are sorted by (0: not sorted by band)
 };
 
 struct WorkItem {
-  int pair, row0, nrows, pad;
+  int pair, row0, nrows, band;
 };
 
 struct PlanCounters {
@@ -78,244 +79,324 @@ __device__ __forceinline__ void make_posecam(const double* pose, double fx, doub
 }
 
 // ---------------------------------------------------------------------------------
-// Pass A (geometry): one CTA per (item, pose).
-//   1. project every vertex ONCE into a 16-byte PVert record (snapped window position + 1/Z) held
-//      in shared memory (global scratch for models above kSmemVerts) and reduce the exact
-//      projected bounding box;
-//   2. assemble the triangles: gather the three records of every face, drop what can never
-//      produce a pixel -- a vertex behind the camera plane, no pixel centre inside the image under
-//      its bounding box, zero area, back-facing on a verified closed mesh (bop_model_dev.cull,
-//      only while the camera is outside the model) -- and append the survivors to a compact list
-//      (warp ballot + one shared atomic per warp).  The order of the list is arbitrary; the z-merge
-//      of the raster pass is order-independent.
-// The raster pass then streams the list with coalesced loads and every lane holds a live
-// triangle (about 40 % of the faces of a closed model survive).
+// Geometry pass: one CTA per item (pose pair, or single pose for render / GT info).
+//   1. project every vertex of every pose (16-byte PVert: snapped window position + 1/Z) and reduce
+//      the exact projected bounding boxes; the records of the pose being assembled live in shared
+//      memory (global scratch for models above kSmemVerts);
+//   2. plan: union ROI of the poses, split into row bands that fit the z-tile; one work item per
+//      band is appended to the work list (this used to be a separate kernel);
+//   3. per pose, assemble the triangles: gather the three records of every face, drop what can
+//      never produce a pixel -- a vertex behind the camera plane, no pixel centre inside the image
+//      under its bounding box, zero area, back-facing on a verified closed mesh (bop_model_dev.cull,
+//      only while the camera is outside the model) -- and write the survivors as a list SORTED by
+//      (row band, size class of the candidate-pixel rectangle).  A triangle that touches more than
+//      one band goes to a "shared" segment behind the bands.  The raster pass of band b streams
+//      segment b and the shared segment of both poses: it never sees a triangle of another band,
+//      and 32 consecutive entries have (nearly) equal loop trip counts, so the lanes of a raster
+//      warp stay converged.  Counting sort in shared memory: classify + histogram, prefix, scatter.
 // cam_mode 0: K is [n_im][9] indexed through im_idx (VSD); 1: cam is [n][4] fx,fy,cx,cy (render).
-// tri out:  [n][n_poses][tri_cap] records in three streams, tri_cnt[n][n_poses] valid
-// bbox out: [n][n_poses][4] = x0,y0,x1,y1 inclusive, clipped to the image; empty => x1 < x0.
+// tri out:  [n][n_poses][tri_cap] records in three streams, tri_cnt[n][n_poses] valid;
+// band_off: [n][n_poses][kBandOffN] start of every band segment, then of the shared segment.
 // ---------------------------------------------------------------------------------
 constexpr int kAsmThreads = 512;
-constexpr int kSmemVerts = 12288;   // projected vertices the assemble kernel keeps in shared memory (192 KB)
+constexpr int kSmemVerts = 12288;   // projected vertices the geometry kernel keeps in shared memory (192 KB)
+constexpr int kClasses = 256;
+constexpr int kMaxSortBands = 15;   // ROIs with more bands are not sorted by band (every band streams the whole list)
+constexpr int kBandOffN = kMaxSortBands + 2;
+constexpr int kMaxBins = (kMaxSortBands + 1) * kClasses;
 
-__device__ __forceinline__ bool tri_can_draw(const int4& r0, const int4& r1, const int4& r2, int W, int H,
-                                             int cull) {
-  if (!(r0.w & r1.w & r2.w)) return false;
+// Sort class of a triangle that can draw something, 0 otherwise.  The class is the size of the
+// candidate-pixel rectangle (rows, columns; each capped at 15), COMPLEMENTED so that ascending
+// class order lists the most expensive triangles first: the cheap 1x1 batches fill the tail
+// before the raster pass's barrier.  by0 / by1: first and last candidate row.
+__device__ __forceinline__ int tri_class(const int4& r0, const int4& r1, const int4& r2, int W, int H,
+                                         int cull, int& by0, int& by1) {
+  if (!(r0.w & r1.w & r2.w)) return 0;
   const int minx = min(r0.x, min(r1.x, r2.x)), maxx = max(r0.x, max(r1.x, r2.x));
   const int miny = min(r0.y, min(r1.y, r2.y)), maxy = max(r0.y, max(r1.y, r2.y));
-  if (min(W - 1, maxx >> kSubBits) < max(0, (minx + kSubOne - 1) >> kSubBits)) return false;
-  if (min(H - 1, maxy >> kSubBits) < max(0, (miny + kSubOne - 1) >> kSubBits)) return false;
+  const int w = min(W - 1, maxx >> kSubBits) - max(0, (minx + kSubOne - 1) >> kSubBits) + 1;
+  by0 = max(0, (miny + kSubOne - 1) >> kSubBits);
+  by1 = min(H - 1, maxy >> kSubBits);
+  const int h = by1 - by0 + 1;
+  if (w <= 0 || h <= 0) return 0;
   const long long area2 = (long long)(r1.x - r0.x) * (r2.y - r0.y) - (long long)(r1.y - r0.y) * (r2.x - r0.x);
-  if (area2 == 0) return false;
-  return cull != (area2 > 0 ? -1 : 1);
+  if (area2 == 0) return 0;
+  if (cull == (area2 > 0 ? -1 : 1)) return 0;
+  return kClasses - (min(h, 15) * 16 + min(w, 15));   // 1 (>= 15 x 15) .. 239 (1 x 1)
 }
 
+struct GeomArgs {
+  const bop_model_dev* models;
+  const int32_t* obj_idx;
+  const double* pose_a;
+  const double* pose_b;
+  const int32_t* im_idx;
+  const double* K;
+  const double* diameters;
+  int cam_mode, n_poses, H, W, gate, tile_px;
+  int pv_stride, tri_cap;
+  PVert* pv_global;
+  int4* tri_a;
+  int4* tri_b;
+  float* tri_c;
+  unsigned* stage;
+  int* tri_cnt;
+  int* band_off;
+  PairDesc* desc;
+  WorkItem* work;
+  PlanCounters* ctr;
+  unsigned max_items;
+  int cx_off, cy_off;
+};
+
 __global__ void __launch_bounds__(kAsmThreads, 2)
-assemble_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
-                const double* __restrict__ pose_a, const double* __restrict__ pose_b,
-                const int32_t* __restrict__ im_idx, const double* __restrict__ K,
-                const double* __restrict__ diameters, int cam_mode, int n_poses, int H, int W, int gate,
-                int pv_stride, PVert* __restrict__ pv_global, int tri_cap, int4* __restrict__ tri_a,
-                int4* __restrict__ tri_b, float* __restrict__ tri_c, int* __restrict__ tri_cnt,
-                int4* __restrict__ bbox, int cx_off, int cy_off) {
-  extern __shared__ int4 s_pv[];
-  __shared__ int s_box[4];
+geometry_kernel(const __grid_constant__ GeomArgs g) {
+  extern __shared__ int4 s_dyn[];   // [n_pv] projected vertices (smem path), then [kMaxBins] ints
+  __shared__ int s_box[2][4];
   __shared__ int s_n;
-  const int gw = blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int item = gw / n_poses, which = gw - item * n_poses;
-  const bop_model_dev M = models[obj_idx[item]];
-  const double* pose = (which == 0 ? pose_a : pose_b) + 12 * (size_t)item;
-  if (gate && n_poses == 2) {   // uniform over the CTA
-    const double* pe = pose_a + 12 * (size_t)item;
-    const double* pg = pose_b + 12 * (size_t)item;
-    const double diam = diameters ? diameters[item] : M.diameter;
-    if (!sphere_projections_overlap(0.5 * diam, pe + 9, pg + 9)) {
-      if (tid == 0) { bbox[gw] = make_int4(0, 0, -1, -1); tri_cnt[gw] = 0; }
-      return;
-    }
-  }
-  if (tid == 0) { s_box[0] = s_box[1] = INT_MAX; s_box[2] = s_box[3] = INT_MIN; s_n = 0; }
+  __shared__ int s_plan[4];         // y0, band rows, nb, nbs (bands the lists are sorted by; 0 = unsorted)
+  __shared__ int s_wsum[kAsmThreads / 32];
+  const int item = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_poses = g.n_poses, W = g.W, H = g.H;
+  const bop_model_dev M = g.models[g.obj_idx[item]];
+  const bool smem_pv = M.n_pts <= kSmemVerts;
+  int4* const s_pv = s_dyn;
+  int* const s_bins = (int*)(s_dyn + (smem_pv ? min(g.pv_stride, kSmemVerts) : 0));
+  const double* pose[2] = {g.pose_a + 12 * (size_t)item, g.pose_b + 12 * (size_t)item};
+  const double diam = g.diameters ? g.diameters[item] : M.diameter;
   double fx, fy, cx, cy;
-  if (cam_mode == 0) {
-    const double* Kp = K + 9 * (size_t)im_idx[item];
+  int im;
+  if (g.cam_mode == 0) {
+    im = g.im_idx[item];
+    const double* Kp = g.K + 9 * (size_t)im;
     fx = Kp[0]; fy = Kp[4]; cx = Kp[2]; cy = Kp[5];
   } else {
-    const double* c = K + 4 * (size_t)item;
+    im = item;
+    const double* c = g.K + 4 * (size_t)item;
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
-  PoseCamF P;
-  make_posecam(pose, fx, fy, cx + cx_off, cy + cy_off, P);
-  const float4* __restrict__ verts = (const float4*)M.verts4;
-  if (M.n_pts > pv_stride || M.n_faces > tri_cap) __trap();   // max_geom below the model's size: fail loudly
-  int4* const gpv = (int4*)(pv_global + (size_t)gw * pv_stride);
+  if (M.n_pts > g.pv_stride || M.n_faces > g.tri_cap || M.n_faces >= (1 << 24)) __trap();   // max_geom below the model's size: fail loudly
+  bool gated = false;
+  if (g.gate && n_poses == 2)   // uniform over the CTA
+    gated = !sphere_projections_overlap(0.5 * diam, pose[0] + 9, pose[1] + 9);
+  if (tid < 8) (&s_box[0][0])[tid] = (tid & 2) ? INT_MIN : INT_MAX;
   __syncthreads();
+  const float4* __restrict__ verts = (const float4*)M.verts4;
   // The projected-vertex records are addressed through a compile-time switch so that the common
   // case compiles to shared-memory loads / stores (LDS / STS) instead of generic ones.
-#define PV(i) (*(SMEM ? &s_pv[i] : &gpv[i]))
+#define PV(p, i) (*(SMEM ? &s_pv[i] : &gpv[(size_t)(p) * g.pv_stride + (i)]))
   auto body = [&](auto smem_tag) {
   constexpr bool SMEM = decltype(smem_tag)::value;
-  int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
-  for (int i0 = tid; i0 < M.n_pts; i0 += 4 * kAsmThreads) {
-    float4 vin[4];   // four loads in flight before the first store (pvs may alias as far as nvcc knows)
+  int4* const gpv = (int4*)(g.pv_global + (size_t)item * n_poses * g.pv_stride);
+  // Projects every vertex of pose p; keep: store the records (always on the global path, where
+  // both poses have their own scratch).
+  auto project_pose = [&](int p, bool keep, bool want_box) {
+    PoseCamF P;
+    make_posecam(pose[p], fx, fy, cx + g.cx_off, cy + g.cy_off, P);
+    int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
+    for (int i0 = tid; i0 < M.n_pts; i0 += 4 * kAsmThreads) {
+      float4 vin[4];   // four loads in flight before the first store
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int i = i0 + k * kAsmThreads;
-      vin[k] = i < M.n_pts ? __ldg(verts + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+      for (int k = 0; k < 4; ++k) {
+        const int i = i0 + k * kAsmThreads;
+        vin[k] = i < M.n_pts ? __ldg(verts + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int i = i0 + k * kAsmThreads;
-      if (i < M.n_pts) {
-        const PVert v = project_vertex(P, vin[k]);
-        PV(i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
-        if (v.valid) {
-          minx = min(minx, v.x); maxx = max(maxx, v.x);
-          miny = min(miny, v.y); maxy = max(maxy, v.y);
+      for (int k = 0; k < 4; ++k) {
+        const int i = i0 + k * kAsmThreads;
+        if (i < M.n_pts) {
+          const PVert v = project_vertex(P, vin[k]);
+          if (keep) PV(p, i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
+          if (v.valid) {
+            minx = min(minx, v.x); maxx = max(maxx, v.x);
+            miny = min(miny, v.y); maxy = max(maxy, v.y);
+          }
         }
       }
     }
-  }
-  minx = __reduce_min_sync(BOP_FULL_MASK, minx); miny = __reduce_min_sync(BOP_FULL_MASK, miny);
-  maxx = __reduce_max_sync(BOP_FULL_MASK, maxx); maxy = __reduce_max_sync(BOP_FULL_MASK, maxy);
-  if (lane == 0 && maxx >= minx) {
-    atomicMin(&s_box[0], minx); atomicMin(&s_box[1], miny);
-    atomicMax(&s_box[2], maxx); atomicMax(&s_box[3], maxy);
-  }
-  __syncthreads();   // records (shared or this CTA's global scratch) and the box are complete
-  if (tid == 0) {
-    int4 b = make_int4(0, 0, -1, -1);
-    if (s_box[2] >= s_box[0]) {
-      b.x = max(0, (s_box[0] + kSubOne - 1) >> kSubBits);
-      b.y = max(0, (s_box[1] + kSubOne - 1) >> kSubBits);
-      b.z = min(W - 1, s_box[2] >> kSubBits);
-      b.w = min(H - 1, s_box[3] >> kSubBits);
-      if (b.z < b.x || b.w < b.y) b = make_int4(0, 0, -1, -1);
+    if (want_box) {
+      minx = __reduce_min_sync(BOP_FULL_MASK, minx); miny = __reduce_min_sync(BOP_FULL_MASK, miny);
+      maxx = __reduce_max_sync(BOP_FULL_MASK, maxx); maxy = __reduce_max_sync(BOP_FULL_MASK, maxy);
+      if (lane == 0 && maxx >= minx) {
+        atomicMin(&s_box[p][0], minx); atomicMin(&s_box[p][1], miny);
+        atomicMax(&s_box[p][2], maxx); atomicMax(&s_box[p][3], maxy);
+      }
     }
-    bbox[gw] = b;
+  };
+  if (!gated) {
+    project_pose(0, true, true);
+    if (n_poses == 2) project_pose(1, !SMEM, true);
   }
-  // Culling is only output-preserving while the camera centre is outside the mesh: require it
-  // outside the model's bounding sphere (|t| = distance of the camera from the model origin).
-  int cull = M.cull;
-  if (cull) {
-    const double r = (double)M.cull_min_dist;
-    if (!(pose[9] * pose[9] + pose[10] * pose[10] + pose[11] * pose[11] > r * r)) cull = 0;
+  __syncthreads();
+  // ---- plan (thread 0): descriptor, union ROI, row bands, work items -------------------------
+  if (tid == 0) {
+    PairDesc D;
+    D.obj = g.obj_idx[item];
+    D.im = im;
+    D.diameter = diam;
+    D.n_poses = n_poses;
+    D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
+    make_posecam(pose[0], fx, fy, cx + g.cx_off, cy + g.cy_off, D.pose[0]);
+    if (n_poses == 2) make_posecam(pose[1], fx, fy, cx + g.cx_off, cy + g.cy_off, D.pose[1]);
+    else D.pose[1] = D.pose[0];
+    int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
+    for (int p = 0; p < n_poses; ++p) {
+      if (s_box[p][2] < s_box[p][0]) continue;
+      const int bx0 = max(0, (s_box[p][0] + kSubOne - 1) >> kSubBits), by0 = max(0, (s_box[p][1] + kSubOne - 1) >> kSubBits);
+      const int bx1 = min(W - 1, s_box[p][2] >> kSubBits), by1 = min(H - 1, s_box[p][3] >> kSubBits);
+      if (bx1 < bx0 || by1 < by0) continue;
+      x0 = min(x0, bx0); y0 = min(y0, by0); x1 = max(x1, bx1); y1 = max(y1, by1);
+    }
+    int nb = 0, band = 1;
+    if (x1 >= x0) {
+      x0 &= ~3;
+      const int w = ((x1 + 1 - x0) + 3) & ~3;
+      const int h = y1 + 1 - y0;
+      D.x0 = x0; D.y0 = y0; D.w = w; D.h = h;
+      const int cap_rows = min(kMaxBandRows, max(1, g.tile_px / w));
+      nb = (h + cap_rows - 1) / cap_rows;
+      band = (h + nb - 1) / nb;  // balanced bands
+    } else {
+      D.x0 = D.y0 = D.w = D.h = 0; y0 = 0;
+    }
+    const int nbs = (nb >= 2 && nb <= kMaxSortBands && M.n_faces < (1 << 20)) ? nb : 0;
+    D.nbs = nbs;
+    g.desc[item] = D;
+    s_plan[0] = y0; s_plan[1] = band; s_plan[2] = nb; s_plan[3] = nbs;
+    if (nb > 0) {
+      const unsigned start = atomicAdd(&g.ctr->total, (unsigned)nb);
+      for (int b = 0; b < nb; ++b) {
+        if (start + b >= g.max_items) break;  // cannot happen with the documented workspace size
+        WorkItem wi;
+        wi.pair = item;
+        wi.row0 = b * band;
+        wi.nrows = min(band, D.h - b * band);
+        wi.band = b;
+        g.work[start + b] = wi;
+      }
+    }
   }
+  __syncthreads();
+  const int roi_y0 = s_plan[0], band_rows = s_plan[1], nb = s_plan[2], nbs = s_plan[3];
+  const int nseg = nbs + 1;                 // band segments + the shared segment (unsorted: one segment)
+  const int nbins = nseg * kClasses;
+  const int fbits = nbs ? 20 : 24;          // stage entry = key << fbits | face
   const int4* __restrict__ faces = (const int4*)M.faces4;
   const int F = M.n_faces;
-  const size_t out0 = (size_t)gw * tri_cap;
-  // Two faces per thread and iteration: both index loads and all six record gathers are in
-  // flight before the first test, and one shared atomic serves both ballots.
-  int4 na4 = make_int4(0, 0, 0, 0), nb4 = na4;   // indices of the NEXT iteration (prefetched)
-  if (tid < F) na4 = __ldg(faces + tid);
-  if (tid + kAsmThreads < F) nb4 = __ldg(faces + tid + kAsmThreads);
-  for (int f0 = 0; f0 < F; f0 += 2 * kAsmThreads) {
-    const int fa = f0 + tid, fb = fa + kAsmThreads;
-    const int4 ia = na4, ib = nb4;
-    if (fa + 2 * kAsmThreads < F) na4 = __ldg(faces + fa + 2 * kAsmThreads);
-    if (fb + 2 * kAsmThreads < F) nb4 = __ldg(faces + fb + 2 * kAsmThreads);
-    bool acc_a = false, acc_b = false;
-    int4 a0, a1, a2, b0, b1, b2;
-    if (fa < F) { a0 = PV(ia.x); a1 = PV(ia.y); a2 = PV(ia.z); }
-    if (fb < F) { b0 = PV(ib.x); b1 = PV(ib.y); b2 = PV(ib.z); }
-    if (fa < F) acc_a = tri_can_draw(a0, a1, a2, W, H, cull);
-    if (fb < F) acc_b = tri_can_draw(b0, b1, b2, W, H, cull);
-    const unsigned ma = __ballot_sync(BOP_FULL_MASK, acc_a), mb = __ballot_sync(BOP_FULL_MASK, acc_b);
-    if (ma | mb) {
-      const int na = __popc(ma);
-      int base = 0;
-      if (lane == 0) base = atomicAdd(&s_n, na + __popc(mb));
-      base = __shfl_sync(BOP_FULL_MASK, base, 0);
-      const unsigned lt = (1u << lane) - 1u;
-      if (acc_a) {
-        const int slot = base + __popc(ma & lt);
-        if (slot >= tri_cap) __trap();   // caller passed a max_geom below (n_faces + 1) / 2: fail loudly
-        tri_a[out0 + slot] = make_int4(a0.x, a0.y, a1.x, a1.y);
-        tri_b[out0 + slot] = make_int4(a2.x, a2.y, a0.z, a1.z);
-        tri_c[out0 + slot] = __int_as_float(a2.z);
+  const unsigned lt = (1u << lane) - 1u;
+  for (int p = 0; p < n_poses; ++p) {
+    const int gw = item * n_poses + p;
+    int* const boff = g.band_off + (size_t)gw * kBandOffN;
+    if (nb == 0) {   // gated, or nothing inside the image
+      if (tid == 0) g.tri_cnt[gw] = 0;
+      if (tid < kBandOffN) boff[tid] = 0;
+      continue;
+    }
+    if (p > 0) {
+      __syncthreads();   // the scatter of pose p - 1 has finished with the records and the cursors
+      if (SMEM) project_pose(p, true, false);
+    }
+    for (int i = tid; i < nbins; i += kAsmThreads) s_bins[i] = 0;
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    // Culling is only output-preserving while the camera centre is outside the mesh: require it
+    // outside the model's bounding sphere (|t| = distance of the camera from the model origin).
+    int cull = M.cull;
+    if (cull) {
+      const double r = (double)M.cull_min_dist;
+      const double* t = pose[p] + 9;
+      if (!(t[0] * t[0] + t[1] * t[1] + t[2] * t[2] > r * r)) cull = 0;
+    }
+    const size_t out0 = (size_t)gw * g.tri_cap;
+    // Classify: two faces per thread and iteration (both index loads and all six record gathers
+    // are in flight before the first test).  Survivors are staged as (key << fbits | face) in
+    // arrival order and counted per key (one shared atomic per distinct key and warp).
+    auto key_of = [&](int cls, int by0, int by1) {
+      if (cls == 0 || nbs == 0) return cls;
+      const int b0 = (by0 - roi_y0) / band_rows, b1 = (by1 - roi_y0) / band_rows;
+      return (b0 == b1 ? b0 : nbs) * kClasses + cls;
+    };
+    int4 na4 = make_int4(0, 0, 0, 0), nb4 = na4;   // indices of the NEXT iteration (prefetched)
+    if (tid < F) na4 = __ldg(faces + tid);
+    if (tid + kAsmThreads < F) nb4 = __ldg(faces + tid + kAsmThreads);
+    for (int f0 = 0; f0 < F; f0 += 2 * kAsmThreads) {
+      const int fa = f0 + tid, fb = fa + kAsmThreads;
+      const int4 ia = na4, ib = nb4;
+      if (fa + 2 * kAsmThreads < F) na4 = __ldg(faces + fa + 2 * kAsmThreads);
+      if (fb + 2 * kAsmThreads < F) nb4 = __ldg(faces + fb + 2 * kAsmThreads);
+      int ka = 0, kb = 0;
+      int4 a0, a1, a2, b0, b1, b2;
+      if (fa < F) { a0 = PV(p, ia.x); a1 = PV(p, ia.y); a2 = PV(p, ia.z); }
+      if (fb < F) { b0 = PV(p, ib.x); b1 = PV(p, ib.y); b2 = PV(p, ib.z); }
+      int y0a = 0, y1a = 0, y0b = 0, y1b = 0;
+      if (fa < F) ka = key_of(tri_class(a0, a1, a2, W, H, cull, y0a, y1a), y0a, y1a);
+      if (fb < F) kb = key_of(tri_class(b0, b1, b2, W, H, cull, y0b, y1b), y0b, y1b);
+      const unsigned ma = __ballot_sync(BOP_FULL_MASK, ka != 0), mb = __ballot_sync(BOP_FULL_MASK, kb != 0);
+      if (ma | mb) {   // warp-uniform
+        const int na = __popc(ma);
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_n, na + __popc(mb));
+        base = __shfl_sync(BOP_FULL_MASK, base, 0);
+        if (base + na + __popc(mb) > g.tri_cap) __trap();   // caller passed a max_geom below (n_faces + 1) / 2: fail loudly
+        if (ka) g.stage[out0 + base + __popc(ma & lt)] = ((unsigned)ka << fbits) | (unsigned)fa;
+        if (kb) g.stage[out0 + base + na + __popc(mb & lt)] = ((unsigned)kb << fbits) | (unsigned)fb;
+        const unsigned pa = __match_any_sync(BOP_FULL_MASK, ka), pb = __match_any_sync(BOP_FULL_MASK, kb);
+        if (ka && (pa & lt) == 0) atomicAdd(&s_bins[ka], __popc(pa));
+        if (kb && (pb & lt) == 0) atomicAdd(&s_bins[kb], __popc(pb));
       }
-      if (acc_b) {
-        const int slot = base + na + __popc(mb & lt);
-        if (slot >= tri_cap) __trap();
-        tri_a[out0 + slot] = make_int4(b0.x, b0.y, b1.x, b1.y);
-        tri_b[out0 + slot] = make_int4(b2.x, b2.y, b0.z, b1.z);
-        tri_c[out0 + slot] = __int_as_float(b2.z);
+    }
+    __syncthreads();
+    // Exclusive prefix over the bins (each thread owns nbins / 512 consecutive bins; warp scan +
+    // one pass over the warp totals): s_bins becomes the write cursor of every key.
+    {
+      const int per = (nbins + kAsmThreads - 1) / kAsmThreads;
+      const int first = tid * per;
+      int sum = 0;
+      for (int k = 0; k < per; ++k)
+        if (first + k < nbins) sum += s_bins[first + k];
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(BOP_FULL_MASK, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) s_wsum[warp] = incl;
+      __syncthreads();
+      int wbase = 0;
+      for (int k = 0; k < warp; ++k) wbase += s_wsum[k];
+      int run = wbase + incl - sum;
+      for (int k = 0; k < per; ++k)
+        if (first + k < nbins) { const int c = s_bins[first + k]; s_bins[first + k] = run; run += c; }
+    }
+    __syncthreads();
+    const int n_surv = s_n;
+    if (tid < kBandOffN) boff[tid] = tid < nseg ? s_bins[tid * kClasses] : n_surv;   // read before the scatter moves the cursors
+    if (tid == 0) g.tri_cnt[gw] = n_surv;
+    __syncthreads();
+    // Scatter: every staged survivor fetches its face again (dense: all lanes hold a survivor),
+    // takes a slot under its key (one shared atomic per distinct key and warp) and writes its record.
+    for (int i0 = 0; i0 < n_surv; i0 += kAsmThreads) {
+      const int i = i0 + tid;
+      const unsigned e = i < n_surv ? g.stage[out0 + i] : 0u;
+      const int k = (int)(e >> fbits);
+      const unsigned peers = __match_any_sync(BOP_FULL_MASK, k);
+      const int leader = __ffs(peers) - 1;
+      int slot = 0;
+      if (k && lane == leader) slot = atomicAdd(&s_bins[k], __popc(peers));
+      slot = __shfl_sync(BOP_FULL_MASK, slot, leader) + __popc(peers & lt);
+      if (k) {
+        const int4 idx = __ldg(faces + (e & ((1u << fbits) - 1u)));
+        const int4 r0 = PV(p, idx.x), r1 = PV(p, idx.y), r2 = PV(p, idx.z);
+        g.tri_a[out0 + slot] = make_int4(r0.x, r0.y, r1.x, r1.y);
+        g.tri_b[out0 + slot] = make_int4(r2.x, r2.y, r0.z, r1.z);
+        g.tri_c[out0 + slot] = __int_as_float(r2.z);
       }
     }
   }
   };
-  if (M.n_pts <= kSmemVerts) body(std::true_type{}); else body(std::false_type{});
+  if (smem_pv) body(std::true_type{}); else body(std::false_type{});
 #undef PV
-  __syncthreads();
-  if (tid == 0) tri_cnt[gw] = s_n;
-}
-
-// ---------------------------------------------------------------------------------
-// Pass B: one thread per item: build the descriptor, split the union ROI into row bands that fit
-// the z-tile and append them to the work list (one atomicAdd per item).
-// ---------------------------------------------------------------------------------
-__global__ void plan_kernel(const bop_model_dev* __restrict__ models,
-                            const int32_t* __restrict__ obj_idx, const double* __restrict__ pose_a,
-                            const double* __restrict__ pose_b, const int32_t* __restrict__ im_idx,
-                            const double* __restrict__ K, const double* __restrict__ diameters,
-                            int cam_mode, int n, int n_poses, int H,
-                            int W, int tile_px, const int4* __restrict__ bbox,
-                            PairDesc* __restrict__ desc, WorkItem* __restrict__ work,
-                            PlanCounters* __restrict__ ctr, unsigned max_items, int cx_off,
-                            int cy_off) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  PairDesc D;
-  const int obj = obj_idx[i];
-  D.obj = obj;
-  D.diameter = diameters ? diameters[i] : models[obj].diameter;
-  D.n_poses = n_poses;
-  D.pad = 0;
-  double fx, fy, cx, cy;
-  if (cam_mode == 0) {
-    D.im = im_idx[i];
-    const double* Kp = K + 9 * (size_t)D.im;
-    fx = Kp[0]; fy = Kp[4]; cx = Kp[2]; cy = Kp[5];
-  } else {
-    D.im = i;
-    const double* c = K + 4 * (size_t)i;
-    fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
-  }
-  D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
-  make_posecam(pose_a + 12 * (size_t)i, fx, fy, cx + cx_off, cy + cy_off, D.pose[0]);
-  if (n_poses == 2) make_posecam(pose_b + 12 * (size_t)i, fx, fy, cx + cx_off, cy + cy_off, D.pose[1]);
-  else D.pose[1] = D.pose[0];
-  int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
-  for (int p = 0; p < n_poses; ++p) {
-    const int4 b = bbox[i * n_poses + p];
-    if (b.z >= b.x) {
-      x0 = min(x0, b.x); y0 = min(y0, b.y); x1 = max(x1, b.z); y1 = max(y1, b.w);
-    }
-  }
-  int nb = 0, band = 0;
-  if (x1 >= x0) {
-    x0 &= ~3;
-    const int w = ((x1 + 1 - x0) + 3) & ~3;
-    const int h = y1 + 1 - y0;
-    D.x0 = x0; D.y0 = y0; D.w = w; D.h = h;
-    const int cap_rows = min(kMaxBandRows, max(1, tile_px / w));
-    nb = (h + cap_rows - 1) / cap_rows;
-    band = (h + nb - 1) / nb;  // balanced bands
-  } else {
-    D.x0 = D.y0 = D.w = D.h = 0;
-  }
-  desc[i] = D;
-  if (nb > 0) {
-    const unsigned start = atomicAdd(&ctr->total, (unsigned)nb);
-    for (int b = 0; b < nb; ++b) {
-      if (start + b >= max_items) break;  // cannot happen with the documented workspace size
-      WorkItem wi;
-      wi.pair = i;
-      wi.row0 = b * band;
-      wi.nrows = min(band, D.h - b * band);
-      wi.pad = 0;
-      work[start + b] = wi;
-    }
-  }
 }
 
 }  // namespace
@@ -337,11 +418,20 @@ struct PixParams {
   // float32 decision path (step cost): thresholds and their undecidable bands (see vsd_pixel_fast)
   float tau_f[BOP_MAX_TAUS], tau_eps[BOP_MAX_TAUS];
   int fast;          // 1: try the float32 decision path first
+  // Histogram form of the step-cost sweep (taus ascending): a pixel adds 1 to the bin
+  // cnt = #(tau_k <= d) instead of 1 to every counter k < cnt.  tau_tab = [-3e38, taus..., 3e38...]
+  // so that tau_tab[cnt] <= d < tau_tab[cnt + 1]; cnt is guessed from the spacing of the first two
+  // taus (exact for the evenly spaced BOP sweep) and verified against the table.
+  float tau_tab[BOP_MAX_TAUS + 2];
+  float guess_scale, guess_off;
+  int hist;          // 1: the HIST kernel variant may be used
 };
 
 constexpr int MODE_STEP = 0, MODE_TLINEAR = 1, MODE_RENDER = 2, MODE_MASK = 3, MODE_GTINFO = 4;
 
-template <int MODE, int NT>
+constexpr int kHistBits = 5;   // per-thread bin width: a thread sees <= 31 pixels per work item (checked on the host)
+
+template <int MODE, int NT, bool HIST = false>
 struct Acc {
   int uni = 0, inter = 0;
   int c[NT];
@@ -351,13 +441,20 @@ struct Acc {
   }
 };
 template <int NT>
-struct Acc<MODE_TLINEAR, NT> {
+struct Acc<MODE_TLINEAR, NT, false> {
   int uni = 0, inter = 0;
   double c[NT];
   __device__ Acc() {
 #pragma unroll
     for (int k = 0; k < NT; ++k) c[k] = 0.0;
   }
+};
+// Step cost, ascending taus: NT + 1 bins of kHistBits bits in one 64-bit register.
+template <int NT>
+struct Acc<MODE_STEP, NT, true> {
+  static_assert((NT + 1) * kHistBits <= 64, "histogram does not fit 64 bits");
+  int uni = 0, inter = 0;
+  unsigned long long hist = 0ull;
 };
 
 // misc.depth_im_to_dist_im_fast (misc.py:158-161): sqrt((X*d)^2 + (Y*d)^2 + d^2) in float64,
@@ -370,9 +467,10 @@ __device__ __forceinline__ double dist_of(double X, double Y, float d) {
 
 // One pixel of pose_error.vsd lines 48-91.  dt/de/dg: depth_test, rendered est, rendered gt.
 // NT >= pp.n_taus is the compile-time length of the tau sweep; pp.taus[k >= n_taus] = +inf adds nothing.
-template <int MODE, int NT>
+template <int MODE, int NT, bool HIST = false>
 __device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double Y, float dt,
-                                          float de, float dg, double diameter, Acc<MODE, NT>& acc) {
+                                          float de, float dg, double diameter,
+                                          Acc<MODE, NT, HIST>& acc) {
   const bool he = de != 0.f, hg = dg != 0.f;   // d_model > 0 on the distance image
   if (!he && !hg) return;
   const double Dt = dist_of(X, Y, dt);
@@ -397,13 +495,20 @@ __device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double 
     acc.inter += 1;
     double d = fabs(__dsub_rn(Dg, De));
     if (pp.normalized) d = __ddiv_rn(d, diameter);
+    if constexpr (HIST) {
+      int cnt = 0;
 #pragma unroll
-    for (int k = 0; k < NT; ++k) {
-      if (MODE == MODE_TLINEAR) {
-        double c = __ddiv_rn(d, pp.taus[k]);
-        acc.c[k] += (c > 1.0) ? 1.0 : c;
-      } else {
-        acc.c[k] += (d >= pp.taus[k]) ? 1 : 0;
+      for (int k = 0; k < NT; ++k) cnt += (d >= pp.taus[k]) ? 1 : 0;
+      acc.hist += 1ull << (kHistBits * cnt);
+    } else {
+#pragma unroll
+      for (int k = 0; k < NT; ++k) {
+        if constexpr (MODE == MODE_TLINEAR) {
+          double c = __ddiv_rn(d, pp.taus[k]);
+          acc.c[k] += (c > 1.0) ? 1.0 : c;
+        } else {
+          acc.c[k] += (d >= pp.taus[k]) ? 1 : 0;
+        }
       }
     }
   }
@@ -420,10 +525,11 @@ __device__ __forceinline__ void vsd_pixel(const PixParams& pp, double X, double 
 // Returns false without touching acc when anything is undecidable; the caller then runs
 // vsd_pixel.  Decided pixels get exactly the counts vsd_pixel would give them.
 // s2x = fl32(1 + X^2) of the column, yy = fl32(Y^2) of the row.
-template <int NT>
-__device__ __forceinline__ bool vsd_pixel_fast(const PixParams& pp, float s2x, float yy, float dt,
-                                               float de, float dg, float inv_diam,
-                                               Acc<MODE_STEP, NT>& acc) {
+// HIST: s_tau = PixParams::tau_tab in shared memory (indexed per lane).
+template <int NT, bool HIST>
+__device__ __forceinline__ bool vsd_pixel_fast(const PixParams& pp, const float* __restrict__ s_tau,
+                                               float s2x, float yy, float dt, float de, float dg,
+                                               float inv_diam, Acc<MODE_STEP, NT, HIST>& acc) {
   const bool he = de != 0.f, hg = dg != 0.f;
   if (!he && !hg) return true;
   float s;
@@ -450,13 +556,29 @@ __device__ __forceinline__ bool vsd_pixel_fast(const PixParams& pp, float s2x, f
   if (!(vg || ve)) return true;
   if (vg && ve) {
     const float dn = fabsf(dg - de) * s * inv_diam;
-    bool near = false;
+    if constexpr (HIST) {
+      // cnt = #(tau_k <= dn).  The taus ascend, so only the neighbours tau_tab[cnt] <= dn <
+      // tau_tab[cnt + 1] can lie within their band of dn.
+      int cnt = min(max(__float2int_rd(fmaf(dn, pp.guess_scale, pp.guess_off)), 0), pp.n_taus);
+      float lo = s_tau[cnt], hi = s_tau[cnt + 1];
+      if (!(lo <= dn && dn < hi)) {   // unevenly spaced taus, or a rounding of the guess at a threshold
+        cnt = 0;
 #pragma unroll
-    for (int k = 0; k < NT; ++k) near = near || !(fabsf(dn - pp.tau_f[k]) > pp.tau_eps[k]);
-    if (near) return false;
-    acc.inter += 1;
+        for (int k = 0; k < NT; ++k) cnt += (dn >= pp.tau_f[k]) ? 1 : 0;
+        lo = s_tau[cnt]; hi = s_tau[cnt + 1];
+      }
+      if (!(dn - lo > fmaf(3e-6f, fabsf(lo), 1e-30f)) || !(hi - dn > fmaf(3e-6f, fabsf(hi), 1e-30f))) return false;
+      acc.inter += 1;
+      acc.hist += 1ull << (kHistBits * cnt);
+    } else {
+      bool near = false;
 #pragma unroll
-    for (int k = 0; k < NT; ++k) acc.c[k] += (dn >= pp.tau_f[k]) ? 1 : 0;
+      for (int k = 0; k < NT; ++k) near = near || !(fabsf(dn - pp.tau_f[k]) > pp.tau_eps[k]);
+      if (near) return false;
+      acc.inter += 1;
+#pragma unroll
+      for (int k = 0; k < NT; ++k) acc.c[k] += (dn >= pp.tau_f[k]) ? 1 : 0;
+    }
   }
   acc.uni += 1;
   return true;
@@ -500,6 +622,7 @@ __device__ __forceinline__ void load_depth4(const PixParams& pp, const void* __r
 namespace {
 
 constexpr int kQueueCap = 2048;   // deferred (large) triangles per pose and work item
+constexpr int kPrefetchBytes = 32 * 1152;   // one batch of 32 records (36 B each) per warp, up to 32 warps
 
 struct FusedArgs {
   const bop_model_dev* models;
@@ -512,6 +635,7 @@ struct FusedArgs {
   const int4* tri_b;
   const float* tri_c;
   const int* tri_cnt;
+  const int* band_off;          // [n][n_poses][kBandOffN] segment starts of every list (geometry_kernel)
   int tri_cap;
   const void* depth_test;       // VSD
   const float* depth_scale;     // VSD, u16 input only
@@ -532,7 +656,8 @@ struct FusedArgs {
 // VARIANT 0: <= 512 threads, 1 CTA/SM (up to 128 registers); VARIANT 1: up to 1024 resident
 // threads per SM (64 registers): 1024-thread CTAs or two 512-thread CTAs per SM.
 // NT: compile-time length of the tau sweep (>= pp.n_taus; only the VSD modes use it).
-template <int MODE, int VARIANT, int NT>
+// HIST: step cost accumulated as a histogram over ascending taus (see PixParams).
+template <int MODE, int VARIANT, int NT, bool HIST>
 __global__ void __launch_bounds__(VARIANT == 0 ? 512 : 1024, 1)
 fused_kernel(const __grid_constant__ FusedArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -543,19 +668,25 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
   float* const s2x = (float*)(yh + kMaxBandRows);                 // [wpad]          fl32(1 + X^2)
   float* const yyf = s2x + wpad;                                  // [kMaxBandRows]  fl32(Y^2)
   int* const queue = (int*)(yyf + kMaxBandRows);                  // [kQueueCap]
+  int4* const prefetch = (int4*)(queue + kQueueCap);              // [nwarps] x 1152 B of triangle records in flight
 
   __shared__ PairDesc sD;
   __shared__ WorkItem sW;
   __shared__ unsigned s_ticket;
   __shared__ int s_q;
   __shared__ int s_next;
-  __shared__ int s_nt[2];   // assembled triangles of pose 0 / 1 of the current pair
-  __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS];
+  // The triangles of a work item: the band's segment and the shared segment of pose 0, then of
+  // pose 1 (geometry_kernel), addressed as one virtual index range.
+  __shared__ int s_seg0[4];   // first list entry of each segment
+  __shared__ int s_segc[5];   // virtual index where each segment starts; [4] = total
+  __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS + 1];
   __shared__ double s_sum[BOP_MAX_TAUS];
+  __shared__ float s_tau[BOP_MAX_TAUS + 2];
 
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
   const unsigned total = min(a.ctr->total, a.max_items);
+  if (HIST && tid < BOP_MAX_TAUS + 2) s_tau[tid] = a.pp.tau_tab[tid];
 
   for (;;) {
     __syncthreads();
@@ -566,7 +697,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       s_q = 0;
       s_next = 0;
     }
-    if (tid < 2 + BOP_MAX_TAUS) s_cnt[tid] = 0ull;
+    if (tid < 2 + BOP_MAX_TAUS + 1) s_cnt[tid] = 0ull;
     if (tid < BOP_MAX_TAUS) s_sum[tid] = 0.0;
     __syncthreads();
     if (s_ticket >= total) break;
@@ -575,10 +706,21 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int* src = (const int*)(a.desc + sW.pair);
       int* dst = (int*)&sD;
       for (int i = tid; i < (int)(sizeof(PairDesc) / 4); i += nthr) dst[i] = src[i];
-      if (tid >= nthr - 2) {   // last two threads: triangle counts (n_poses is 1 or 2)
-        const int p = tid - (nthr - 2);
-        const int np = src[offsetof(PairDesc, n_poses) / 4];
-        s_nt[p] = p < np ? a.tri_cnt[(size_t)sW.pair * np + p] : 0;
+      if (tid == nthr - 1) {   // segment table (n_poses is 1 or 2)
+        const int np = src[offsetof(PairDesc, n_poses) / 4], nbs = src[offsetof(PairDesc, nbs) / 4];
+        int c = 0;
+        for (int sg = 0; sg < 4; ++sg) {
+          const int p = sg >> 1;
+          int lo = 0, hi = 0;
+          if (p < np) {
+            const int* off = a.band_off + ((size_t)sW.pair * np + p) * kBandOffN;
+            if (nbs == 0) { if (!(sg & 1)) { lo = off[0]; hi = off[1]; } }
+            else if (sg & 1) { lo = off[nbs]; hi = off[nbs + 1]; }
+            else { lo = off[sW.band]; hi = off[sW.band + 1]; }
+          }
+          s_seg0[sg] = lo; s_segc[sg] = c; c += hi - lo;
+        }
+        s_segc[4] = c;
       }
     }
     __syncthreads();
@@ -587,12 +729,13 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const int cy0 = sD.y0 + sW.row0, cy1 = cy0 + nrows - 1;
     const int npx = nrows * w;
     const int n_poses = sD.n_poses;
-    // Clear the z-tiles to +inf and build the x-ray table (misc.py:137: (xs - cx) / fx).
+    // Clear the z-tiles (0 = nothing drawn; they hold max 1/Z, raster.cuh) and build the x-ray
+    // table (misc.py:137: (xs - cx) / fx).
     {
-      const uint4 inf4 = make_uint4(BOP_INF_BITS_F32, BOP_INF_BITS_F32, BOP_INF_BITS_F32, BOP_INF_BITS_F32);
+      const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
       for (int p = 0; p < n_poses; ++p) {
         uint4* z4 = (uint4*)(zt + (size_t)p * a.tile_px);
-        for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = inf4;
+        for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = zero4;
       }
       if (MODE == MODE_STEP || MODE == MODE_TLINEAR) {
         for (int c = tid; c < w; c += nthr) {
@@ -613,21 +756,50 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     // no barrier is needed between them).  Triangles with many candidate pixels are deferred to
     // a queue and drawn warp-cooperatively afterwards.
     const size_t t_base = (size_t)sW.pair * n_poses * a.tri_cap;
-    const int nT0 = s_nt[0];
-    const int nT = nT0 + s_nt[1];
-    // Warps claim 32 consecutive triangles at a time from a shared ticket: triangle cost varies
-    // (1 .. small_tri_px candidate pixels), static striding leaves warps idle at the barrier.
-    for (;;) {
-      int base = 0;
-      if (lane == 0) base = atomicAdd(&s_next, 32);
-      base = __shfl_sync(BOP_FULL_MASK, base, 0);
-      if (base >= nT) break;
+    const int c1 = s_segc[1], c2 = s_segc[2], c3 = s_segc[3], nT = s_segc[4];
+    // virtual index -> (pose, list entry)
+    auto locate = [&](int g, int& p) -> size_t {
+      const int sg = (g >= c1 ? 1 : 0) + (g >= c2 ? 1 : 0) + (g >= c3 ? 1 : 0);
+      p = sg >> 1;
+      return t_base + (size_t)p * a.tri_cap + (size_t)(s_seg0[sg] + (g - s_segc[sg]));
+    };
+    // Warps claim 32 consecutive triangles at a time from a shared ticket (triangle cost varies
+    // by class; static striding would leave warps idle at the barrier).  The records of the NEXT
+    // batch are fetched by cp.async into a per-warp staging area (every lane copies and later
+    // reads its own 36 bytes) while the current batch is rasterised, so the L2 / HBM latency of
+    // the list is hidden without spending registers on it.
+    auto ticket = [&]() {
+      int b = 0;
+      if (lane == 0) b = atomicAdd(&s_next, 32);
+      return __shfl_sync(BOP_FULL_MASK, b, 0);
+    };
+    int4* const pre_a = prefetch + (size_t)warp * 64 + lane;   // [warp][2][32] int4, then [warp][32] float
+    int4* const pre_b = pre_a + 32;
+    float* const pre_c = (float*)(prefetch + (size_t)nwarps * 64) + warp * 32 + lane;
+    const unsigned sa = smem_addr(pre_a), sb = smem_addr(pre_b), sc = smem_addr(pre_c);
+    int pose_next = 0;
+    auto fetch = [&](int base) {
       const int g = base + lane;
       if (g < nT) {
-        const int p = g >= nT0 ? 1 : 0;
-        const size_t ti = t_base + (size_t)p * a.tri_cap + (g - p * nT0);
-        const int4 ra = ld_stream_i4(a.tri_a + ti), rb = ld_stream_i4(a.tri_b + ti);
-        const float rc = ld_stream_f1(a.tri_c + ti);
+        const size_t ti = locate(g, pose_next);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(a.tri_a + ti) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sb), "l"(a.tri_b + ti) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sc), "l"(a.tri_c + ti) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int base = ticket();
+    if (base < nT) fetch(base);
+    while (base < nT) {
+      const int next = ticket();
+      const int g = base + lane;
+      const int p = pose_next;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      const int4 ra = *pre_a, rb = *pre_b;
+      const float rc = *pre_c;
+      if (next < nT) fetch(next);   // the staging area is free again: this lane has its record in registers
+      base = next;
+      if (g < nT) {
         const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
         const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
         const PVert v2 = {rb.x, rb.y, rc, 1};
@@ -656,8 +828,8 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int nq = min(s_q, kQueueCap);
       for (int qi = warp; qi < nq; qi += nwarps) {
         const int g = queue[qi];
-        const int p = g >= nT0 ? 1 : 0;
-        const size_t ti = t_base + (size_t)p * a.tri_cap + (g - p * nT0);
+        int p;
+        const size_t ti = locate(g, p);
         const int4 ra = __ldg(a.tri_a + ti), rb = __ldg(a.tri_b + ti);
         const float rc = __ldg(a.tri_c + ti);
         const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
@@ -679,10 +851,10 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     if (MODE == MODE_RENDER) {
       float* out = a.depth_out + (size_t)sD.im * a.pp.H * a.pp.W;
       for (int i = tid; i < npx; i += nthr) {
-        const unsigned zb = zt[i];
-        if (zb != BOP_INF_BITS_F32) {
+        const float zv = tile_depth(zt[i]);
+        if (zv != 0.f) {
           const int r = i / w, c = i - r * w;
-          out[(size_t)(cy0 + r) * a.pp.W + (cx0 + c)] = __uint_as_float(zb);
+          out[(size_t)(cy0 + r) * a.pp.W + (cx0 + c)] = zv;
         }
       }
       continue;
@@ -694,7 +866,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       int ne = 0, ng = 0, ni = 0, nu = 0;
       int bb[8] = {INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MAX, INT_MAX, INT_MIN, INT_MIN};
       for (int i = tid; i < npx; i += nthr) {
-        const bool e = zt[i] != BOP_INF_BITS_F32, g = zt[a.tile_px + i] != BOP_INF_BITS_F32;
+        const bool e = tile_depth(zt[i]) != 0.f, g = tile_depth(zt[a.tile_px + i]) != 0.f;
         if (!(e || g)) continue;
         const int r = i / w, x = cx0 + (i - r * w), y = cy0 + r;
         nu += 1; ni += (e && g) ? 1 : 0;
@@ -728,8 +900,8 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const size_t im_base = (size_t)sD.im * a.pp.H * (size_t)a.pp.W;
       const size_t out_base = (size_t)sW.pair * a.pp.H * (size_t)a.pp.W;
       for (int i = tid; i < npx; i += nthr) {
-        const unsigned zb = zt[i];
-        if (zb == BOP_INF_BITS_F32) continue;
+        const float zv = tile_depth(zt[i]);
+        if (zv == 0.f) continue;
         const int r = i / w, x = cx0 + (i - r * w) - a.mx, y = cy0 + r - a.my;
         n_all += 1;
         bb[0] = min(bb[0], x); bb[1] = min(bb[1], y); bb[2] = max(bb[2], x); bb[3] = max(bb[3], y);
@@ -740,7 +912,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         else dt = __fmul_rn((float)__ldg((const unsigned short*)a.depth_test + im_base + off), scale);
         const double X = __ddiv_rn(__dsub_rn((double)x, sD.kcx), sD.kfx);
         const double Y = __ddiv_rn(__dsub_rn((double)y, sD.kcy), sD.kfy);
-        const double Dt = dist_of(X, Y, dt), Dg = dist_of(X, Y, __uint_as_float(zb));
+        const double Dt = dist_of(X, Y, dt), Dg = dist_of(X, Y, zv);
         if (Dt > 0.0) n_valid += 1;
         const bool vis = (__fsub_rn((float)Dg, (float)Dt) <= a.pp.delta_f32) || Dt == 0.0;
         if (a.mask_full) a.mask_full[out_base + off] = 255;
@@ -767,7 +939,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
 
     // ---- pixel pass ------------------------------------------------------------------
-    Acc<MODE, NT> acc;
+    Acc<MODE, NT, HIST> acc;
     int n_loaded = 0;
     const int w4 = w >> 2;
     const int ngroups = nrows * w4;
@@ -779,11 +951,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const int r = g / w4, c4 = g - r * w4;
       const uint4 ze = *(const uint4*)(zt + r * w + 4 * c4);
       const uint4 zg = *(const uint4*)(zt + a.tile_px + r * w + 4 * c4);
-      const bool e_empty = (ze.x & ze.y & ze.z & ze.w) == BOP_INF_BITS_F32 &&
-                           (ze.x | ze.y | ze.z | ze.w) == BOP_INF_BITS_F32;
-      const bool g_empty = (zg.x & zg.y & zg.z & zg.w) == BOP_INF_BITS_F32 &&
-                           (zg.x | zg.y | zg.z | zg.w) == BOP_INF_BITS_F32;
-      if (e_empty && g_empty)
+      if (((ze.x | ze.y | ze.z | ze.w) | (zg.x | zg.y | zg.z | zg.w)) == 0u)
         continue;   // no model pixel in this group: depth_test is not even loaded
       const int row = cy0 + r, col = cx0 + 4 * c4;
       float dt[4];
@@ -794,14 +962,12 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       const unsigned zgv[4] = {zg.x, zg.y, zg.z, zg.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const float de = zev[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zev[k]);
-        const float dg = zgv[k] == BOP_INF_BITS_F32 ? 0.f : __uint_as_float(zgv[k]);
-        if (MODE == MODE_STEP) {
-          if (fast && vsd_pixel_fast<NT>(a.pp, s2x[4 * c4 + k], yy, dt[k], de, dg, inv_diam,
-                                         *(Acc<MODE_STEP, NT>*)&acc))
+        const float de = tile_depth(zev[k]), dg = tile_depth(zgv[k]);
+        if constexpr (MODE == MODE_STEP) {
+          if (fast && vsd_pixel_fast<NT, HIST>(a.pp, s_tau, s2x[4 * c4 + k], yy, dt[k], de, dg, inv_diam, acc))
             continue;
         }
-        vsd_pixel<MODE, NT>(a.pp, xh[4 * c4 + k], yh[r], dt[k], de, dg, diameter, acc);
+        vsd_pixel<MODE, NT, HIST>(a.pp, xh[4 * c4 + k], yh[r], dt[k], de, dg, diameter, acc);
       }
     }
     // ---- reduce: warp shuffle -> shared atomics -> one global atomic per counter ---------
@@ -812,21 +978,40 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         if (in) atomicAdd(&s_cnt[1], (unsigned long long)in);
         if (nl) atomicAdd(&a.ctr->depth_groups, (unsigned long long)nl);
       }
+      if constexpr (HIST) {
+        // bins 1 .. n_taus (bin 0 = below every tau adds to no counter)
 #pragma unroll
-      for (int k = 0; k < NT; ++k) {
-        if (k < a.pp.n_taus) {
-          if (MODE == MODE_TLINEAR) {
-            const double s = warp_sum((double)acc.c[k]);
-            if (lane == 0 && s != 0.0) atomicAdd(&s_sum[k], s);
-          } else {
-            const int s = warp_sum((int)acc.c[k]);
-            if (lane == 0 && s) atomicAdd(&s_cnt[2 + k], (unsigned long long)s);
+        for (int c = 1; c <= NT; ++c) {
+          if (c <= a.pp.n_taus) {
+            const int s = warp_sum((int)((acc.hist >> (kHistBits * c)) & ((1u << kHistBits) - 1u)));
+            if (lane == 0 && s) atomicAdd(&s_cnt[2 + c], (unsigned long long)s);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < NT; ++k) {
+          if (k < a.pp.n_taus) {
+            if constexpr (MODE == MODE_TLINEAR) {
+              const double s = warp_sum((double)acc.c[k]);
+              if (lane == 0 && s != 0.0) atomicAdd(&s_sum[k], s);
+            } else {
+              const int s = warp_sum((int)acc.c[k]);
+              if (lane == 0 && s) atomicAdd(&s_cnt[2 + k], (unsigned long long)s);
+            }
           }
         }
       }
     }
     __syncthreads();
-    if (tid < 2 + BOP_MAX_TAUS && s_cnt[tid])
+    if constexpr (HIST) {
+      // counter k = #(d >= tau_k) = bins k + 1 .. n_taus
+      if (tid < 2 + a.pp.n_taus) {
+        unsigned long long v = 0ull;
+        if (tid < 2) v = s_cnt[tid];
+        else for (int c = tid - 1; c <= a.pp.n_taus; ++c) v += s_cnt[2 + c];
+        if (v) atomicAdd(a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS) + tid, v);
+      }
+    } else if (tid < 2 + BOP_MAX_TAUS && s_cnt[tid])
       atomicAdd(a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS) + tid, s_cnt[tid]);
     if (MODE == MODE_TLINEAR && tid < a.pp.n_taus && s_sum[tid] != 0.0)
       atomicAdd(a.tl_sums + (size_t)sW.pair * BOP_MAX_TAUS + tid, s_sum[tid]);
@@ -965,7 +1150,7 @@ pixel_pass_kernel(const void* __restrict__ depth_test, const float* __restrict__
   const float* pg = depth_gt + (size_t)pair * H * W;
   const bool vec = pp.vec_ok != 0;
 
-  Acc<MODE, BOP_MAX_TAUS> acc;
+  Acc<MODE, BOP_MAX_TAUS, false> acc;
 #pragma unroll 2
   for (int j = 0; j < kK2GroupsPerThread; ++j) {
     const int g = g0 + j * kK2Threads + threadIdx.x;
@@ -996,7 +1181,7 @@ pixel_pass_kernel(const void* __restrict__ depth_test, const float* __restrict__
     for (int k = 0; k < 4; ++k) {
       if (de[k] != 0.f || dg[k] != 0.f) {
         const double X = __ddiv_rn(__dsub_rn((double)(col + k), cx), fx);
-        vsd_pixel<MODE, BOP_MAX_TAUS>(pp, X, Y, dt[k], de[k], dg[k], diameter, acc);
+        vsd_pixel<MODE, BOP_MAX_TAUS, false>(pp, X, Y, dt[k], de[k], dg[k], diameter, acc);
       }
     }
   }
@@ -1042,7 +1227,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 constexpr size_t kGeomBudgetBytes = (size_t)8 << 30;   // assembled-triangle scratch per chunk
 
 struct WsLayout {
-  size_t ctr, counts, tl, bbox, mbox, desc, work, tri_cnt, tri_a, tri_b, tri_c, pv, total;
+  size_t ctr, counts, tl, bbox, mbox, desc, work, tri_cnt, band_off, tri_a, tri_b, tri_c, stage, pv, total;
   unsigned max_items;
   int chunk;       // items processed per pass (the batch is split so that the scratch fits the budget)
   int pv_stride;   // PVert records per (item, pose) (global fallback for models above kSmemVerts)
@@ -1056,7 +1241,7 @@ WsLayout ws_layout(int n, int H, int W, int n_poses, int max_geom) {
   L.tri_cap = 2 * L.pv_stride;
   const bool pv_global = max_geom > kSmemVerts;
   const size_t per_item_pv = pv_global ? (size_t)n_poses * L.pv_stride * sizeof(PVert) : 0;
-  const size_t per_item = per_item_pv + (size_t)n_poses * L.tri_cap * 36;
+  const size_t per_item = per_item_pv + (size_t)n_poses * L.tri_cap * 40;
   size_t chunk = kGeomBudgetBytes / per_item;
   if (chunk < 1) chunk = 1;
   if (chunk > (size_t)(n > 0 ? n : 1)) chunk = (size_t)(n > 0 ? n : 1);
@@ -1078,15 +1263,18 @@ WsLayout ws_layout(int n, int H, int W, int n_poses, int max_geom) {
   L.desc = off;    off = align_up(off + (size_t)c * sizeof(PairDesc), 256);
   L.work = off;    off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
   L.tri_cnt = off; off = align_up(off + (size_t)c * 2 * sizeof(int), 256);
+  L.band_off = off; off = align_up(off + (size_t)c * 2 * kBandOffN * sizeof(int), 256);
   L.tri_a = off;   off = align_up(off + ntri * sizeof(int4), 256);
   L.tri_b = off;   off = align_up(off + ntri * sizeof(int4), 256);
   L.tri_c = off;   off = align_up(off + ntri * sizeof(float), 256);
+  L.stage = off;   off = align_up(off + ntri * sizeof(unsigned), 256);
   L.pv = off;      off = align_up(off + (size_t)c * per_item_pv, 256);
   L.total = off;
   return L;
 }
 
 bool g_exact_pixels = false;   // bop_vsd_set_exact: disable the float32 decision path (tests)
+bool g_no_hist = false;        // bop_vsd_set_exact(2): float32 decisions with per-tau counters instead of the histogram (tests)
 
 int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams& pp) {
   BOP_REQUIRE(prm, "vsd: null params");
@@ -1107,6 +1295,15 @@ int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams
     if (k < prm->n_taus && !(pp.taus[k] == pp.taus[k])) fast = false;   // NaN tau: exact path only
   }
   pp.fast = fast ? 1 : 0;
+  bool ascending = fast;
+  for (int k = 1; k < prm->n_taus; ++k) ascending = ascending && pp.tau_f[k - 1] <= pp.tau_f[k];
+  for (int k = 0; k < prm->n_taus; ++k) ascending = ascending && fabsf(pp.tau_f[k]) < 1e37f;
+  pp.hist = ascending && !g_no_hist ? 1 : 0;
+  pp.tau_tab[0] = -3e38f;
+  for (int k = 0; k <= BOP_MAX_TAUS; ++k) pp.tau_tab[1 + k] = k < prm->n_taus ? pp.tau_f[k] : 3e38f;
+  const float step = prm->n_taus >= 2 ? pp.tau_f[1] - pp.tau_f[0] : 0.f;
+  pp.guess_scale = step > 0.f ? 1.f / step : 0.f;
+  pp.guess_off = step > 0.f ? 1.f - pp.tau_f[0] / step : 0.f;
   pp.delta_f32 = (float)prm->delta;
   pp.n_taus = prm->n_taus;
   pp.normalized = prm->normalized_by_diameter;
@@ -1135,6 +1332,7 @@ void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
   a.tri_b = (const int4*)(ws + L.tri_b);
   a.tri_c = (const float*)(ws + L.tri_c);
   a.tri_cnt = (const int*)(ws + L.tri_cnt);
+  a.band_off = (const int*)(ws + L.band_off);
   a.tri_cap = L.tri_cap;
 }
 
@@ -1142,29 +1340,29 @@ void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
 // ray tables of a wide image would not leave room for it in shared memory.
 int effective_tile_px(int W) {
   const int wp = (W + 3) & ~3;
-  const long long room = (long long)225 * 1024 - (long long)wp * 12 - (long long)kMaxBandRows * 12 - (long long)kQueueCap * 4;
+  const long long room = (long long)225 * 1024 - (long long)wp * 12 - (long long)kMaxBandRows * 12 - (long long)kQueueCap * 4 - (long long)kPrefetchBytes;
   long long fit = (room / 8) & ~3ll;
   if (fit < kMinTilePx) fit = kMinTilePx;
   return g_tune.tile_px < fit ? g_tune.tile_px : (int)fit;
 }
 
-template <int MODE, int NT>
+template <int MODE, int NT, bool HIST>
 int launch_fused_nt(const FusedArgs& a, int W, cudaStream_t s) {
   const int wp = (W + 3) & ~3;
-  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 12 + (size_t)kMaxBandRows * 12 + (size_t)kQueueCap * 4;
+  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 12 + (size_t)kMaxBandRows * 12 + (size_t)kQueueCap * 4 + (size_t)kPrefetchBytes;
   BOP_REQUIRE(smem <= (size_t)225 * 1024, "fused kernel: z-tile + tables exceed shared memory (lower tile_px)");
   const int grid = sm_count() * g_tune.ctas_per_sm;
   const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : ((MODE == MODE_MASK || MODE == MODE_GTINFO) ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
   const bool dense = g_tune.threads * g_tune.ctas_per_sm > 512;
   if (dense)
-    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 1, NT, HIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   else
-    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 0, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BOP_CUDA(cudaFuncSetAttribute(fused_kernel<MODE, 0, NT, HIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   bop_prof_begin(slot, s);
   if (dense)
-    fused_kernel<MODE, 1, NT><<<grid, g_tune.threads, smem, s>>>(a);
+    fused_kernel<MODE, 1, NT, HIST><<<grid, g_tune.threads, smem, s>>>(a);
   else
-    fused_kernel<MODE, 0, NT><<<grid, g_tune.threads, smem, s>>>(a);
+    fused_kernel<MODE, 0, NT, HIST><<<grid, g_tune.threads, smem, s>>>(a);
   bop_prof_end(slot, s);
   BOP_LAUNCH_CHECK();
   return 0;
@@ -1172,11 +1370,14 @@ int launch_fused_nt(const FusedArgs& a, int W, cudaStream_t s) {
 
 template <int MODE>
 int launch_fused(const FusedArgs& a, int W, cudaStream_t s) {
-  if (MODE == MODE_STEP) {   // the step-cost sweep is unrolled to 4, 10 (the BOP19 default) or 16 taus
-    if (a.pp.n_taus <= 4) return launch_fused_nt<MODE, 4>(a, W, s);
-    if (a.pp.n_taus <= 10) return launch_fused_nt<MODE, 10>(a, W, s);
+  if constexpr (MODE == MODE_STEP) {   // the step-cost sweep is unrolled to 4, 10 (the BOP19 default) or 16 taus
+    // A thread sees at most 4 * ceil(tile_px / 4 / threads) pixels of a work item: the histogram
+    // bins (kHistBits bits per thread) must hold that.
+    const bool hist = a.pp.hist && 4 * ((a.tile_px / 4 + g_tune.threads - 1) / g_tune.threads) < (1 << kHistBits);
+    if (a.pp.n_taus <= 4) return hist ? launch_fused_nt<MODE, 4, true>(a, W, s) : launch_fused_nt<MODE, 4, false>(a, W, s);
+    if (a.pp.n_taus <= 10) return hist ? launch_fused_nt<MODE, 10, true>(a, W, s) : launch_fused_nt<MODE, 10, false>(a, W, s);
   }
-  return launch_fused_nt<MODE, BOP_MAX_TAUS>(a, W, s);
+  return launch_fused_nt<MODE, BOP_MAX_TAUS, false>(a, W, s);
 }
 
 // bbox + plan; shared by VSD and render.
@@ -1187,20 +1388,19 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
                 cudaStream_t s, int cx_off = 0, int cy_off = 0) {
   // counters + counts + tl sums are contiguous at the head of the workspace.
   BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
-  int4* bbox = (int4*)(ws + L.bbox);
-  const int warps = n * n_poses;
+  GeomArgs g;
+  g.models = models; g.obj_idx = obj_idx; g.pose_a = pose_a; g.pose_b = pose_b; g.im_idx = im_idx;
+  g.K = K; g.diameters = diameters; g.cam_mode = cam_mode; g.n_poses = n_poses; g.H = H; g.W = W;
+  g.gate = gate; g.tile_px = effective_tile_px(W); g.pv_stride = L.pv_stride; g.tri_cap = L.tri_cap;
+  g.pv_global = (PVert*)(ws + L.pv); g.tri_a = (int4*)(ws + L.tri_a); g.tri_b = (int4*)(ws + L.tri_b);
+  g.tri_c = (float*)(ws + L.tri_c); g.stage = (unsigned*)(ws + L.stage); g.tri_cnt = (int*)(ws + L.tri_cnt);
+  g.band_off = (int*)(ws + L.band_off); g.desc = (PairDesc*)(ws + L.desc); g.work = (WorkItem*)(ws + L.work);
+  g.ctr = (PlanCounters*)(ws + L.ctr); g.max_items = L.max_items; g.cx_off = cx_off; g.cy_off = cy_off;
   bop_prof_begin(BOP_PROF_VSD_PLAN, s);
-  const size_t asm_smem = (size_t)(L.pv_stride < kSmemVerts ? L.pv_stride : kSmemVerts) * sizeof(PVert);
-  BOP_CUDA(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_smem));
-  assemble_kernel<<<warps, kAsmThreads, asm_smem, s>>>(
-      models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode, n_poses, H, W, gate, L.pv_stride,
-      (PVert*)(ws + L.pv), L.tri_cap, (int4*)(ws + L.tri_a), (int4*)(ws + L.tri_b), (float*)(ws + L.tri_c),
-      (int*)(ws + L.tri_cnt), bbox, cx_off, cy_off);
-  BOP_LAUNCH_CHECK();
-  plan_kernel<<<(n + 127) / 128, 128, 0, s>>>(models, obj_idx, pose_a, pose_b, im_idx, K, diameters, cam_mode,
-                                              n, n_poses, H, W, effective_tile_px(W), bbox,
-                                              (PairDesc*)(ws + L.desc), (WorkItem*)(ws + L.work),
-                                              (PlanCounters*)(ws + L.ctr), L.max_items, cx_off, cy_off);
+  const size_t geom_smem = (size_t)(L.pv_stride < kSmemVerts ? L.pv_stride : kSmemVerts) * sizeof(PVert) +
+                           (size_t)kMaxBins * sizeof(int);
+  BOP_CUDA(cudaFuncSetAttribute(geometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)geom_smem));
+  geometry_kernel<<<n, kAsmThreads, geom_smem, s>>>(g);
   bop_prof_end(BOP_PROF_VSD_PLAN, s);
   BOP_LAUNCH_CHECK();
   return 0;
@@ -1231,7 +1431,8 @@ extern "C" int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int
 // Test hook: exact != 0 makes every pixel take the float64 path (the float32 decision path must
 // give bit-identical counts; tests compare the two).
 extern "C" int bop_vsd_set_exact(int exact) {
-  g_exact_pixels = exact != 0;
+  g_exact_pixels = exact == 1;
+  g_no_hist = exact == 2;
   return 0;
 }
 
@@ -1242,6 +1443,38 @@ extern "C" int bop_vsd_depth_bytes_fetched(const void* workspace, int depth_dtyp
   PlanCounters c;
   BOP_CUDA(cudaMemcpy(&c, workspace, sizeof(c), cudaMemcpyDeviceToHost));
   *bytes = c.depth_groups * (depth_dtype == BOP_DEPTH_U16 ? 8ull : 16ull);
+  return 0;
+}
+
+// Test hook: copies the assembled-triangle list of (pair, pose) left in `workspace` by the most
+// recent bop_vsd_dev call with these sizes to the host: xy[k][6] = snapped window positions
+// (1/256 px) of the three vertices of list entry k.  Synchronises the device.
+extern "C" int bop_vsd_debug_triangle_list(const void* workspace, int n_pairs, int height, int width,
+                                           int max_geom, int pair, int pose, int32_t* xy, int cap,
+                                           int* count) {
+  BOP_REQUIRE(workspace && xy && count && pair >= 0 && pair < n_pairs && (pose == 0 || pose == 1),
+              "bop_vsd_debug_triangle_list: bad arguments");
+  const WsLayout L = ws_layout(n_pairs, height, width, 2, max_geom);
+  BOP_REQUIRE(pair < L.chunk, "bop_vsd_debug_triangle_list: pair outside the last chunk");
+  const unsigned char* ws = (const unsigned char*)workspace;
+  BOP_CUDA(cudaDeviceSynchronize());
+  int n = 0;
+  BOP_CUDA(cudaMemcpy(&n, ws + L.tri_cnt + sizeof(int) * ((size_t)pair * 2 + pose), sizeof(int), cudaMemcpyDeviceToHost));
+  *count = n;
+  if (n > cap) n = cap;
+  if (n <= 0) return 0;
+  int4* ha = (int4*)malloc(sizeof(int4) * (size_t)n * 2);
+  BOP_REQUIRE(ha, "bop_vsd_debug_triangle_list: out of memory");
+  int4* hb = ha + n;
+  const size_t off = ((size_t)pair * 2 + pose) * L.tri_cap;
+  cudaError_t e = cudaMemcpy(ha, ws + L.tri_a + sizeof(int4) * off, sizeof(int4) * n, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(hb, ws + L.tri_b + sizeof(int4) * off, sizeof(int4) * n, cudaMemcpyDeviceToHost);
+  for (int k = 0; e == cudaSuccess && k < n; ++k) {
+    xy[6 * k + 0] = ha[k].x; xy[6 * k + 1] = ha[k].y; xy[6 * k + 2] = ha[k].z; xy[6 * k + 3] = ha[k].w;
+    xy[6 * k + 4] = hb[k].x; xy[6 * k + 5] = hb[k].y;
+  }
+  free(ha);
+  BOP_CUDA(e);
   return 0;
 }
 

@@ -247,6 +247,13 @@ int bop_gt_info_dev(const bop_model_dev* models, const int32_t* obj_idx, const d
  * instead of the caller copying whole images.  bop_vsd_depth_bytes_fetched reports how many
  * bytes of depth_test the most recent pass on `workspace` fetched (synchronises the device). */
 int bop_vsd_depth_bytes_fetched(const void* workspace, int depth_dtype, uint64_t* bytes);
+/* Test hook: the assembled-triangle list (geometry pass) that the most recent bop_vsd_dev call
+ * with these sizes left in `workspace` for (pair, pose; 0 = est, 1 = gt): xy[k][6] = snapped
+ * window positions (1/256 px) of the three vertices of entry k, at most `cap` entries; *count =
+ * length of the list.  The list is sorted by the size of the candidate-pixel rectangle (rows, then
+ * columns, largest first) so that the 32 lanes of a raster warp run the same loop trip counts. */
+int bop_vsd_debug_triangle_list(const void* workspace, int n_pairs, int height, int width,
+                                int max_geom, int pair, int pose, int32_t* xy, int cap, int* count);
 
 /* ---- host-buffer convenience layer -----------------------------------------
  * Upload a model (host arrays, float64 pts as pose_error.* receives them) and get a
@@ -280,9 +287,11 @@ int bop_vsd_host(const bop_model_dev* model_dev, const double* pose_est,
  * tile_px: z-tile capacity in pixels per pose (shared memory = 8*tile_px bytes);
  * threads: CTA size; ctas_per_sm: persistent CTAs per SM.  0 keeps the current value. */
 int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_px);
-/* Test hook: exact != 0 forces the float64 arithmetic of the reference for every pixel of the
+/* Test hook: exact == 1 forces the float64 arithmetic of the reference for every pixel of the
  * step-cost pass; by default a float32 pre-test decides the comparisons that are not close to
- * their thresholds (bit-identical counts either way; tests compare the two). */
+ * their thresholds, and ascending taus are swept as a histogram (one bin per pixel instead of
+ * one counter per tau); exact == 2 keeps the float32 pre-test but uses per-tau counters.
+ * Bit-identical counts in all three modes; tests compare them. */
 int bop_vsd_set_exact(int exact);
 
 

@@ -34,12 +34,32 @@ def project_pts(pts, K, R, t):
   return pts_im[:2, :].T
 
 
+class Precomputer(object):
+  """bop_toolkit_lib/misc.py:110-140: memoises the per-pixel ray factors across calls; they are
+  recomputed only when the image shape or K changes (the reference's class-level cache)."""
+  xs, ys = None, None
+  pre_Xs, pre_Ys = None, None
+  depth_im_shape = None
+  K = None
+
+  @staticmethod
+  def precompute_lazy(depth_im, K):
+    if depth_im.shape != Precomputer.depth_im_shape:
+      Precomputer.depth_im_shape = depth_im.shape
+      Precomputer.xs, Precomputer.ys = np.meshgrid(
+        np.arange(depth_im.shape[1]), np.arange(depth_im.shape[0]))
+      Precomputer.K = None   # the reference's second test is dead code; a new shape must refresh
+    if Precomputer.K is None or not np.all(K == Precomputer.K):
+      Precomputer.K = np.array(K, copy=True)
+      Precomputer.pre_Xs = (Precomputer.xs - K[0, 2]) / np.float64(K[0, 0])
+      Precomputer.pre_Ys = (Precomputer.ys - K[1, 2]) / np.float64(K[1, 1])
+    return Precomputer.pre_Xs, Precomputer.pre_Ys
+
+
 def depth_im_to_dist_im(depth_im, K):
-  """bop_toolkit_lib/misc.py:143-163 (depth_im_to_dist_im_fast; the Precomputer cache of
-  :110-140 is a pure memoisation and is not restated)."""
-  xs, ys = np.meshgrid(np.arange(depth_im.shape[1]), np.arange(depth_im.shape[0]))
-  pre_Xs = (xs - K[0, 2]) / np.float64(K[0, 0])
-  pre_Ys = (ys - K[1, 2]) / np.float64(K[1, 1])
+  """bop_toolkit_lib/misc.py:143-163 (depth_im_to_dist_im_fast, with the Precomputer cache of
+  :110-140 so that a call costs what the reference's does)."""
+  pre_Xs, pre_Ys = Precomputer.precompute_lazy(depth_im, K)
   return np.sqrt(
     np.multiply(pre_Xs, depth_im) ** 2 +
     np.multiply(pre_Ys, depth_im) ** 2 +
