@@ -284,6 +284,15 @@ def make_depth_gpu(batch, torch, ms, obj, pose_gt, t_gt, diam, K, device, seed, 
   return d16
 
 
+def kernel_counters():
+  """Per-pair instruction and DRAM counts of the dominant kernel from ONE committed ncu --set full
+  capture (profiles/kernel_counters.json names the capture); constants, not measured in this run."""
+  try:
+    return json.load(open(os.path.join(ROOT, 'profiles', 'kernel_counters.json')))
+  except Exception:
+    return {}
+
+
 def gpu_arm(args):
   import torch
   import torch.distributed as dist
@@ -308,10 +317,13 @@ def gpu_arm(args):
   K = synth.LM_K
 
   # ---- per-GPU model residency + this rank's shard of pose pairs (weak scaling) -------------
+  # `ms`: the drop-in default, no back-face culling = the reference's GL state (renderer_vispy.py:470).
+  # `ms_cull`: the opt-in cull='auto' (closed, consistently wound meshes only; verified by probe renders).
   models = build_models()
-  ms = batch.ModelSet(device)
+  ms, ms_cull = batch.ModelSet(device), batch.ModelSet(device)
   for m in models:
-    ms.add(m['obj_id'], m['pts'], m['faces'], m['syms'], m['diameter'])
+    ms.add(m['obj_id'], m['pts'], m['faces'], m['syms'], m['diameter'], cull=False)
+    ms_cull.add(m['obj_id'], m['pts'], m['faces'], m['syms'], m['diameter'], cull='auto')
   n_verts, n_faces = models[0]['pts'].shape[0], models[0]['faces'].shape[0]
   n_images = args.images if args.images else P
   assert P % n_images == 0, '--images must divide --pairs'
@@ -347,10 +359,10 @@ def gpu_arm(args):
   h_out = torch.empty((P, len(TAUS) + 2), dtype=torch.float64).pin_memory()
   torch.cuda.synchronize()
 
-  def step_resident():
-    vsd = batch.vsd_batch(ms, d_obj, d_pe, d_pg, d_f32, d_im, d_K, DELTA, TAUS, True, 'step', 'bop19', gate=True)
-    mssd = batch.mssd_batch(ms, d_obj, d_pe, d_pg, gate=True)
-    mspd = batch.mspd_batch(ms, d_obj, d_pe, d_pg, d_Kp)
+  def step_resident(mset=ms):
+    vsd = batch.vsd_batch(mset, d_obj, d_pe, d_pg, d_f32, d_im, d_K, DELTA, TAUS, True, 'step', 'bop19', gate=True)
+    mssd = batch.mssd_batch(mset, d_obj, d_pe, d_pg, gate=True)
+    mspd = batch.mspd_batch(mset, d_obj, d_pe, d_pg, d_Kp)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
     if world > 1:   # the path's one exchange step: all-gather of fixed-width error records
       return sharding.gather_records(ids, errs, counts=[P] * world)[1]
@@ -371,7 +383,7 @@ def gpu_arm(args):
     h_out.copy_(errs, non_blocking=True)
     return errs
 
-  def timed(fn, steps, warmup, sampler):
+  def timed(fn, steps, warmup):
     for _ in range(warmup):
       fn()
     torch.cuda.synchronize()
@@ -396,33 +408,76 @@ def gpu_arm(args):
       dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item()), batch.kernel_launch_count() - l0, (w0, w1), out
 
+  def kernel_parts(steps):
+    s_ms, s_n = ctypes_double(), ctypes_int()
+    parts = {}
+    for name, slot in (('fused', 0), ('geometry', 1), ('mssd', 2), ('mspd', 3)):
+      lib.bop_profile_sum_ms(slot, steps, byref(s_ms), byref(s_n))
+      parts[name] = s_ms.value / max(1, s_n.value)
+    return parts
+
   sampler = ClockSampler(local_rank)
   if rank == 0:
     sampler.start()
     time.sleep(0.3)
+  # (1) eager pass with the library's per-kernel CUDA events: where a step's time goes
   lib.bop_profile_enable(1)
-  ms_res, launches, win_res, out_res = timed(step_resident, args.steps, args.warmup, sampler)
-  s_ms, s_n = ctypes_double(), ctypes_int()
-  lib.bop_profile_sum_ms(0, args.steps, byref(s_ms), byref(s_n))
-  fused_ms = s_ms.value / max(1, s_n.value)
-  parts = {}
-  for name, slot in (('vsd_plan', 1), ('mssd', 2), ('mspd', 3)):
-    lib.bop_profile_sum_ms(slot, args.steps, byref(s_ms), byref(s_n))
-    parts[name] = s_ms.value / max(1, s_n.value)
-  ms_e2e, _, win_e2e, out_e2e = timed(step_e2e, args.steps, args.warmup, sampler)
-  e2e_parts = {}
-  for name, slot in (('fused', 0), ('vsd_plan', 1), ('mssd', 2), ('mspd', 3)):
-    lib.bop_profile_sum_ms(slot, args.steps, byref(s_ms), byref(s_n))
-    e2e_parts[name] = s_ms.value / max(1, s_n.value)
+  ms_eager, launches, _, out_res = timed(step_resident, args.steps, args.warmup)
+  parts = kernel_parts(args.steps)
+  lib.bop_profile_enable(0)
+  # (2) the timed resident pass: the same step captured ONCE into a CUDA graph and replayed, so that
+  # host-side launch jitter (python, driver) cannot starve the GPU between the 8 kernels of a step.
+  # Falls back to the eager loop if capture is not possible (e.g. NCCL inside the step).
+  graph_note = 'eager launches'
+  ms_res, win_res = ms_eager, None
+  use_graph = world == 1 and not os.environ.get('BOP_NO_GRAPH')
+  if use_graph:
+    try:
+      side = torch.cuda.Stream(device)
+      side.wait_stream(torch.cuda.current_stream())
+      with torch.cuda.stream(side):
+        step_resident()
+      torch.cuda.current_stream().wait_stream(side)
+      torch.cuda.synchronize()
+      graph = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(graph):
+        g_out = step_resident()
+      l_graph = launches // max(1, args.steps)
+      ms_res, _, win_res, _ = timed(graph.replay, args.steps, args.warmup)
+      assert torch.equal(g_out, out_res), 'graph replay differs from the eager step'
+      launches = l_graph * args.steps
+      graph_note = 'CUDA graph replay of the step (%d kernels of this library per step)' % l_graph
+    except Exception as e:   # keep the eager number
+      graph_note = 'eager launches (graph capture failed: %s)' % (str(e).splitlines()[0][:120],)
+      ms_res = ms_eager
+  if win_res is None:
+    ms_res, launches, win_res, out_res = timed(step_resident, args.steps, args.warmup)
+  # (3) end to end through host buffers
+  lib.bop_profile_enable(1)
+  ms_e2e, _, win_e2e, out_e2e = timed(step_e2e, args.steps, args.warmup)
+  e2e_parts = kernel_parts(args.steps)
   depth_pulled = batch.depth_bytes_fetched(device, _lib.DEPTH_U16)
-  ms_e2e_copy, _, _, out_e2e_copy = timed(lambda: step_e2e(False), max(1, args.steps // 2), 1, sampler)
+  ms_e2e_copy, _, _, out_e2e_copy = timed(lambda: step_e2e(False), max(1, args.steps // 2), 1)
+  # (4) the opt-in back-face culling on the same step (closed synthetic meshes)
+  ms_cull_t, _, _, out_cull = timed(lambda: step_resident(ms_cull), max(2, args.steps // 2), 2)
+  cull_parts = kernel_parts(max(2, args.steps // 2))
   lib.bop_profile_enable(0)
   same = bool(torch.equal(out_res[:, :len(TAUS) + 2] if world == 1 else out_res[:0], out_e2e if world == 1 else out_e2e[:0]))
+  cull_max_dev = float((out_cull[:, :len(TAUS)] - out_res[:, :len(TAUS)]).abs().max().item()) if world == 1 else None
   clocks = None
   if rank == 0:
     time.sleep(0.2)
     sampler.stop()
     clocks = sampler.summary(win_res[0], win_res[1])
+
+  # (5) BASELINE configs[4]: strong-scaling leg (its own data; every rank takes part)
+  cfg5 = None
+  if args.cfg5_images > 0:
+    del d_f32
+    torch.cuda.empty_cache()
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import cfg5_leg
+    cfg5 = cfg5_leg.run(torch, dist, device, rank, world, args.cfg5_images, steps=1)
 
   if rank != 0:
     if world > 1:
@@ -436,17 +491,24 @@ def gpu_arm(args):
     peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
   except Exception:
     pass
-  peak = float(peaks.get('hbm_gbs', 6650.0))
-  # Algorithmic bytes of the fused VSD kernel per launch: per evaluated pair
-  # 3 reads + 2 z-buffer writes of 4 B x H x W plus the mesh twice; gated pairs move nothing.
+  hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
+  fused_ms = parts['fused']
+  kc = kernel_counters()
+  sm_mhz = (clocks or {}).get('sm_mhz') or float(peaks.get('sm_max_mhz', 1965.0))
+  n_sm = torch.cuda.get_device_properties(device).multi_processor_count
+  # The fused kernel is bound by instruction issue, not by HBM (ncu: DRAM ~10-15 % busy): its
+  # roofline is the SM's thread-instruction rate, SMs x 128 lanes x clock.  achieved = thread
+  # instructions per launch (per-pair count of the committed ncu capture x pairs past the gate)
+  # / the kernel's CUDA-event duration in THIS run.
+  tinst = kc.get('fused_thread_inst_per_pair')
+  winst = kc.get('fused_warp_inst_per_pair')
+  peak_ti = n_sm * 128 * sm_mhz * 1e6 / 1e9                      # G thread-inst/s
+  ach_ti = (tinst * n_active / (fused_ms * 1e-3) / 1e9) if tinst else None
+  # Algorithmic bytes of a NON-fused pipeline: per evaluated pair 3 reads + 2
+  # z-buffer writes of 4 B x H x W plus the mesh twice; gated pairs move nothing.
   alg_pair = 5 * 4 * H * W + 2 * (12 * n_verts + 12 * n_faces)
-  achieved = n_active * alg_pair / (fused_ms * 1e-3) / 1e9
-  traffic = None
-  try:
-    # measured DRAM bytes per evaluated pair (one ncu --set full capture) x pairs in this launch
-    traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['fused_kernel_dram_bytes_per_pair'] * n_active
-  except Exception:
-    pass
+  eff_gbs = n_active * alg_pair / (fused_ms * 1e-3) / 1e9
+  dram_pair = kc.get('fused_dram_bytes_per_pair')
   small = sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_im, h_K, h_scale)) + \
     sum(x.numel() * x.element_size() for x in (h_obj, h_pe, h_pg, h_Kp))
   h2d = small + depth_pulled
@@ -457,11 +519,13 @@ def gpu_arm(args):
     'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
     'ms_per_step': ms_res / args.steps, 'higher_is_better': True, 'scaling': 'weak',
     'vs_baseline': None, 'dtype': 'f32 raster + f64 pixel/vertex arithmetic', 'data': 'synthetic',
-    'config': {'workload': (WORKLOAD % P) if n_images == P else (WORKLOAD % P).replace(
-                 '1 obj/image', '%d shared images x %d estimates' % (n_images, per_im)), 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
+    'config': {'workload': workload_config(P, args.images), 'pairs_per_gpu': P, 'pairs_past_gate': n_active,
+               'culling': 'off (the reference\'s GL state; `cull_auto` below is the opt-in)',
+               'launch': graph_note, 'eager_ms_per_step': ms_eager / args.steps,
                'l2': 'inputs larger than L2: resident pass reads its model pixels out of %.1f GB of depth; '
-                     'e2e pass fetches ~0.28 GB of host depth; both write and re-read ~%.1f GB of assembled-'
-                     'triangle lists per step (L2 = 126 MB)' % (n_images * H * W * 4 / 1e9, P * 2 * 0.4 * n_faces * 36 / 1e9),
+                     'e2e pass fetches ~%.2f GB of host depth; both write and re-read ~%.1f GB of assembled-'
+                     'triangle lists per step (L2 = 126 MB)' % (n_images * H * W * 4 / 1e9, depth_pulled / 1e9,
+                                                                P * 2 * n_faces * 40 / 1e9),
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
                'exchange': 'all-gather of error records per step' if world > 1 else 'none',
                'cpu_affinity': bound},
@@ -471,19 +535,36 @@ def gpu_arm(args):
             'mode': 'pinned host buffers; depth pulled on demand over PCIe by the fused kernel',
             'full_copy': {'value': e2e_copy_v, 'h2d_bytes_per_step': int(h2d_copy),
                           'note': 'same call with whole-image H2D copies of the uint16 depth'}},
+    'cull_auto': {'value': P * world * max(2, args.steps // 2) / (ms_cull_t * 1e-3), 'unit': 'pairs/s',
+                  'ms_per_step': ms_cull_t / max(2, args.steps // 2), 'kernels_ms': cull_parts,
+                  'max_abs_vsd_difference_vs_no_cull': cull_max_dev,
+                  'note': 'same resident step (eager launches) with ModelSet.add(cull="auto"): back faces of closed, '
+                          'consistently wound meshes skipped after probe renders agree; not the drop-in default'},
     'gpu_launches': int(launches),
     'clocks': clocks,
-    'roofline': {'bound': 'hbm', 'kernel': 'fused_kernel<STEP> (raster x2 + pixel pass)',
-                 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                 'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback 6650',
-                 'traffic': traffic, 'kernel_ms': fused_ms, 'algorithmic_bytes_per_pair': alg_pair,
-                 'other_kernels_ms': parts,
-                 'note': 'achieved = algorithmic bytes of a NON-fused pipeline (SURVEY 8d: 3 reads + 2 z-buffer '
-                         'writes of H*W*4 B + mesh) / kernel time, so frac > 1 means the fusion removed that '
-                         'traffic: `traffic` is the DRAM bytes ncu measured (8 % of DRAM bandwidth). The '
-                         'kernel is bound by instruction issue (ncu: issue slots 66 % busy, 17 of 32 lanes '
-                         'active); see DESIGN.md section 4.'},
+    'roofline': {'bound': 'issue', 'kernel': 'fused_kernel<STEP> (raster x2 + pixel pass)',
+                 'achieved': ach_ti, 'peak': peak_ti, 'unit': 'Gthread-inst/s',
+                 'frac': (ach_ti / peak_ti) if ach_ti else None,
+                 'peak_source': '%d SMs x 128 lanes x %.0f MHz (SM clock sampled during the timed region)' % (n_sm, sm_mhz),
+                 'kernel_ms': fused_ms, 'thread_inst_per_pair': tinst, 'warp_inst_per_pair': winst,
+                 'issue_slot_frac': (winst * n_active / (fused_ms * 1e-3) / (n_sm * 4 * sm_mhz * 1e6)) if winst else None,
+                 'lanes_per_inst': (tinst / winst) if tinst and winst else None,
+                 'counters_source': kc.get('source'),
+                 'traffic': (dram_pair * n_active) if dram_pair else None,
+                 'traffic_note': 'DRAM bytes per launch = per-pair bytes of the same committed capture x pairs past the '
+                                 'gate (a profile constant, not measured in this run)',
+                 'hbm': {'physical_gbs': (dram_pair * n_active / (fused_ms * 1e-3) / 1e9) if dram_pair else None,
+                         'peak_gbs': hbm_peak, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback 6650',
+                         'physical_frac': (dram_pair * n_active / (fused_ms * 1e-3) / 1e9 / hbm_peak) if dram_pair else None,
+                         'effective_gbs_vs_unfused': eff_gbs, 'effective_frac_vs_unfused': eff_gbs / hbm_peak,
+                         'algorithmic_bytes_per_pair_unfused': alg_pair,
+                         'note': 'SURVEY 8d counts the bytes of a NON-fused pipeline (3 reads + 2 z-buffer writes of '
+                                 'H*W*4 B + mesh); the fused kernel keeps the rendered images in shared memory, so '
+                                 'its effective rate exceeds the HBM peak and HBM is not its roofline'},
+                 'other_kernels_ms': {k: v for k, v in parts.items() if k != 'fused'}},
   }
+  if cfg5 is not None:
+    line['cfg5'] = cfg5
   if world == 1 and not args.no_cpu_baseline and n_images == P:   # the CPU sample reproduces the per-pair-image workload
     cores = host_cores()
     r = cpu_arm(P, args.cpu_per_core, cores, 1, 1)
@@ -556,6 +637,8 @@ def main():
                   help='0: one image per pair (cfg2 as quoted); N: N shared images x pairs/N estimates each')
   ap.add_argument('--cpu-per-core', type=int, default=32, help='sample pairs per host worker of the CPU arm')
   ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--cfg5-images', type=int, default=20000,
+                  help='images of the cfg5 strong-scaling leg (BASELINE configs[4]); 0 skips it')
   args = ap.parse_args()
   if args.impl == 'reference':
     line = reference_arm(args)

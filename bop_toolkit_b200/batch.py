@@ -107,15 +107,20 @@ class ModelSet(object):
     self.max_syms = 1
     self.info = {}       # obj_id -> dict(n_pts, n_faces, n_syms, diameter)
 
-  def add(self, obj_id, pts, faces=None, syms=None, diameter=0.0, cull='auto'):
+  def add(self, obj_id, pts, faces=None, syms=None, diameter=0.0, cull=None):
     """pts: Nx3 float64 as pose_error.* receives them; faces: Fx3 ints (needed for VSD /
     rendering); syms: list of {'R','t'} or [S,12]; diameter: models_info 'diameter'.
-    cull: 'auto' enables back-face culling in the rasteriser only when the mesh is closed and
-    consistently oriented (closed_and_oriented) AND renders of probe poses with culling have the
-    same silhouettes and depths within 1e-5 relative of renders without (_verify_cull); False
-    never culls (the reference's GL state).  Culling halves the triangle work; on such a mesh the
-    nearest surface along every ray is front-facing, so the depth image can only differ by float
-    rounding where a front and a back face nearly coincide at a silhouette."""
+    cull: False (the default, unless the environment variable BOP_B200_CULL=auto is set) never
+    culls -- the reference's GL state (renderer_vispy.py:470), which every drop-in driver uses.
+    'auto' is an opt-in: it enables back-face culling in the rasteriser only when the mesh is
+    closed and consistently oriented (closed_and_oriented) AND renders of probe poses with
+    culling have the same silhouettes and depths within 1e-5 relative of renders without
+    (_verify_cull).  Culling halves the triangle work; on such a mesh the nearest surface along
+    every ray is front-facing, so the depth image can only differ by float rounding where a front
+    and a back face nearly coincide at a silhouette -- inside the 1e-3 depth tolerance, but not
+    bit-identical, hence not the default."""
+    if cull is None:
+      cull = 'auto' if os.environ.get('BOP_B200_CULL', '').lower() == 'auto' else False
     pts = np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 3))
     n = pts.shape[0]
     if n == 0:
@@ -270,6 +275,8 @@ def re_te_batch(pose_est, pose_gt, device=None):
 
 def _points_call(fn_name, models, obj, pose_est, pose_gt, K, max_n, gate):
   pe, pg, n = _poses(models, pose_est, pose_gt)
+  if n and fn_name in ('bop_mssd_dev', 'bop_mspd_dev'):
+    _require_syms(models, obj)
   oi = _obj_idx(models, obj, n)
   out = torch.empty(n, dtype=torch.float64, device=models.device)
   fn = getattr(_lib.lib(), fn_name)
@@ -287,6 +294,23 @@ def _points_call(fn_name, models, obj, pose_est, pose_gt, K, max_n, gate):
               int(max_n), int(bool(gate)), out.data_ptr(), _stream_ptr())
   _lib.check(rc)
   return out
+
+
+def _require_syms(models, obj):
+  """pose_error.mssd / mspd take min() over the symmetry set (pose_error.py:112-118,137-144): an
+  empty set raises ValueError there, and must not silently score +inf here."""
+  if all(i['n_syms'] > 0 for i in models.info.values()):
+    return          # the usual case: nothing to look up (and no device -> host copy of `obj`)
+  if isinstance(obj, (int, np.integer)):
+    rows = [int(obj)]
+  else:
+    rows = np.unique(obj.cpu().numpy() if isinstance(obj, torch.Tensor) else np.asarray(obj)).tolist()
+  by_row = {r: o for o, r in models._index.items()}
+  for r in rows:
+    if r not in by_row:
+      raise ValueError('model row %d is not in the ModelSet' % r)
+    if models.info[by_row[r]]['n_syms'] == 0:
+      raise ValueError('min() arg is an empty sequence: model %r has no symmetry transformations' % (by_row[r],))
 
 
 def mssd_batch(models, obj, pose_est, pose_gt, gate=False):
@@ -391,6 +415,10 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
     else:
       ii = torch.arange(n, dtype=torch.int32, device=dev)
   else:
+    if not isinstance(im_idx, torch.Tensor) or not im_idx.is_cuda:   # host indices: range check for free
+      chk = np.asarray(im_idx.numpy() if isinstance(im_idx, torch.Tensor) else im_idx)
+      if chk.size and (chk.min() < 0 or chk.max() >= n_im):
+        raise ValueError('im_idx out of range [0, %d)' % n_im)
     ii = to_device(im_idx, torch.int32, dev, (n,))
   sc = None
   if code == _lib.DEPTH_U16:

@@ -376,9 +376,20 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     __syncthreads();
     // Scatter: every staged survivor fetches its face again (dense: all lanes hold a survivor),
     // takes a slot under its key (one shared atomic per distinct key and warp) and writes its record.
+    // Software pipeline over the dependent loads (stage entry -> face indices -> vertex records):
+    // the entry is loaded two iterations ahead, the face indices one iteration ahead.
+    const unsigned fmask = (1u << fbits) - 1u;
+    unsigned e1 = tid < n_surv ? g.stage[out0 + tid] : 0u;
+    unsigned e2 = tid + kAsmThreads < n_surv ? g.stage[out0 + tid + kAsmThreads] : 0u;
+    int4 idx1 = make_int4(0, 0, 0, 0);
+    if (e1) idx1 = __ldg(faces + (e1 & fmask));
     for (int i0 = 0; i0 < n_surv; i0 += kAsmThreads) {
-      const int i = i0 + tid;
-      const unsigned e = i < n_surv ? g.stage[out0 + i] : 0u;
+      const unsigned e = e1;
+      const int4 idx = idx1;
+      e1 = e2;
+      const int i2 = i0 + tid + 2 * kAsmThreads;
+      e2 = i2 < n_surv ? g.stage[out0 + i2] : 0u;
+      if (e1) idx1 = __ldg(faces + (e1 & fmask));
       const int k = (int)(e >> fbits);
       const unsigned peers = __match_any_sync(BOP_FULL_MASK, k);
       const int leader = __ffs(peers) - 1;
@@ -386,7 +397,6 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (k && lane == leader) slot = atomicAdd(&s_bins[k], __popc(peers));
       slot = __shfl_sync(BOP_FULL_MASK, slot, leader) + __popc(peers & lt);
       if (k) {
-        const int4 idx = __ldg(faces + (e & ((1u << fbits) - 1u)));
         const int4 r0 = PV(p, idx.x), r1 = PV(p, idx.y), r2 = PV(p, idx.z);
         g.tri_a[out0 + slot] = make_int4(r0.x, r0.y, r1.x, r1.y);
         g.tri_b[out0 + slot] = make_int4(r2.x, r2.y, r0.z, r1.z);

@@ -305,7 +305,14 @@ class GpuDepthSource(object):
   neighbours, a scene of 5,000 spans two), staging group g+1 on a host thread while group g is
   in use.  Access is expected in registration order; groups behind the current one are freed."""
 
-  def __init__(self, batch, device, height, width, group=4096):
+  def __init__(self, batch, device, height, width, group=None, budget_bytes=None):
+    # A group holds, per image, H*(2W+1) bytes of filtered scanlines + 2*H*W bytes of samples on
+    # the device (and up to two groups are live while a request spans a boundary): size it by
+    # bytes, not by count -- 4,096 images of 640x480 are 5 GB, of 1920x1080 they would be 34 GB.
+    if group is None:
+      budget = int(budget_bytes if budget_bytes is not None else
+                   float(os.environ.get('BOP_B200_DEPTH_GROUP_GB', '5')) * (1 << 30))
+      group = int(min(4096, max(64, budget // (height * (4 * width + 1)))))
     self.batch, self.device, self.h, self.w, self.group = batch, device, height, width, group
     self.paths, self.index = [], {}
     self.live, self.futs = {}, {}
@@ -482,10 +489,19 @@ class ErrorEngine(object):
       chunk = used[c0:c0 + images_per_chunk]
       im_ids = [sp.im_ids[i] for i in chunk]
       paths = self._depth_paths(scene_id, im_ids)
+      depth = None
       if self.depth_source is not None and gpu_depth_decode(paths):
-        depth = self.depth_source.get(scene_id, im_ids)
-        sc = np.asarray([scene_camera[i]['depth_scale'] for i in im_ids], dtype=np.float32)
-      else:
+        try:
+          depth = self.depth_source.get(scene_id, im_ids)
+          sc = np.asarray([scene_camera[i]['depth_scale'] for i in im_ids], dtype=np.float32)
+        except self.torch.cuda.OutOfMemoryError:
+          # no room for a decode group next to the geometry scratch: the rest of the run reads
+          # its depth through the host decoder (same samples, zero-copy pinned path)
+          self.depth_source.close()
+          self.depth_source = None
+          os.environ['BOP_B200_DEPTH_DECODE'] = 'host'
+          self.torch.cuda.empty_cache()
+      if depth is None:
         depth, sc = load_depth_stack(paths, [scene_camera[i]['depth_scale'] for i in im_ids], h, w)
       rows = np.nonzero(np.isin(im_pos, chunk))[0]
       local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
@@ -614,7 +630,11 @@ def calc_errors(p, device=None, log=misc.log, write=True):
   Returns {result_name: {scene_id: records}} (on rank 0; other ranks return the same data)."""
   rank, world = _dist_info()
   if device is None:
-    device = 'cuda:%d' % int(os.environ.get('LOCAL_RANK', '0'))
+    import torch
+    if torch.cuda.is_available() and torch.distributed.is_available() and torch.distributed.is_initialized():
+      device = 'cuda:%d' % torch.cuda.current_device()    # set by sharding.init_from_env (one process per GPU)
+    else:
+      device = 'cuda:%d' % int(os.environ.get('LOCAL_RANK', '0'))
   all_out = {}
   for result_filename in p['result_filenames']:
     log('Processing: {}'.format(result_filename))
@@ -688,12 +708,9 @@ def main(argv=None):
   misc.log('-----------')
   world = int(os.environ.get('WORLD_SIZE', '1'))
   if world > 1:
-    import torch
     import torch.distributed as dist
-    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-    local = int(os.environ.get('LOCAL_RANK', '0'))
-    torch.cuda.set_device(local)
-    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    from . import sharding
+    sharding.init_from_env()
   calc_errors(p)
   if world > 1:
     dist.destroy_process_group()

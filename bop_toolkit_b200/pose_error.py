@@ -6,7 +6,7 @@ Same positional signatures, numpy in / Python float (or list of floats) out, sam
 CUDA path (batch.py -> libbop_b200.so); there is no CPU fallback.  Models passed as `pts`
 arrays are uploaded once and cached by content fingerprint.
 """
-import zlib
+import hashlib
 
 import numpy as np
 import torch
@@ -31,7 +31,7 @@ def _device():
 
 def _fingerprint(arr):
   a = np.ascontiguousarray(arr)
-  return (a.shape, a.dtype.str, zlib.adler32(a.view(np.uint8).reshape(-1)))
+  return (a.shape, a.dtype.str, hashlib.blake2b(a.view(np.uint8).reshape(-1), digest_size=16).digest())
 
 
 def _model_for(pts, syms=None):

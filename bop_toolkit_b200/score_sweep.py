@@ -94,6 +94,9 @@ class ThresholdSweep(object):
       vals = factor * vals
     if len(c_vals):
       vals[~np.array(c_valid, dtype=bool)] = np.inf
+      # match_poses compares with a strict '<' (pose_matching.py:62-70): a NaN error never beats
+      # the best so far, i.e. such a candidate is skipped -- argmin would pick it first instead
+      vals[np.isnan(vals)] = np.inf
     self.rows = dict(scene_id=row_scene, im_id=row_im, obj_id=row_obj, gt_id=row_gt, valid=row_valid)
     self.n_rows = len(row_gt)
     c_est = np.array(c_est, dtype=np.int64)

@@ -8,6 +8,29 @@ import torch
 import torch.distributed as dist
 
 
+def init_from_env():
+  """One process per GPU under torchrun: reads RANK / LOCAL_RANK / WORLD_SIZE, binds the process
+  to its GPU and initialises the process group (NCCL).  -> (rank, world, torch.device).
+  BOP_B200_DIST_BACKEND=gloo is for boxes with fewer GPUs than ranks (tests): ranks then share
+  GPUs (local_rank % device_count) and the record gather goes through gloo."""
+  import os
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  backend = os.environ.get('BOP_B200_DIST_BACKEND', 'nccl')
+  n_dev = torch.cuda.device_count()
+  dev_index = local % max(1, n_dev) if backend != 'nccl' else local
+  torch.cuda.set_device(dev_index)
+  device = torch.device('cuda', dev_index)
+  if world > 1 and not dist.is_initialized():
+    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+    if backend == 'nccl':
+      dist.init_process_group('nccl', device_id=device)
+    else:
+      dist.init_process_group(backend)
+  return rank, world, device
+
+
 def assign_images(costs, world_size):
   """Greedy longest-processing-time assignment of images to ranks.
   costs: [n_images] estimated cost (e.g. pairs x ROI px + N x S).  Returns int32 [n_images]
@@ -55,7 +78,7 @@ def gather_records(ids, errs, group=None, counts=None):
     row[:n, :3].view(torch.int32)[:, :5] = ids
     row[:n, 3:] = errs
   out = torch.empty((ws * m, 3 + T), dtype=torch.float64, device=dev)
-  if dev.type == 'cuda':
+  if dev.type == 'cuda' and dist.get_backend(group) == 'nccl':
     dist.all_gather_into_tensor(out, row, group=group)
   else:
     parts = [torch.empty_like(row) for _ in range(ws)]

@@ -143,7 +143,7 @@ def test_behind_camera_outside_image_and_zero_depth(B, oracle_built):
   K = synth.LM_K
   pts, faces = synth.make_mesh(24, 48, 200.0, seed=5)
   ms = B.ModelSet()
-  ms.add(1, pts, faces, [{'R': np.eye(3), 't': np.zeros((3, 1))}], 200.0)
+  ms.add(1, pts, faces, [{'R': np.eye(3), 't': np.zeros((3, 1))}], 200.0, cull='auto')   # opt-in culling
   assert ms.info[1]['cull'] != 0                     # culled model: the inside view must survive
   R = np.tile(np.eye(3), (5, 1, 1))
   t_g = np.array([[0, 0, 60.0],        # camera INSIDE the object: triangles straddle Z = 0

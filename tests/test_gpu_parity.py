@@ -572,9 +572,12 @@ def test_backface_culling_is_output_preserving(B):
   cam = synth.LM_K.reshape(9)[[0, 4, 2, 5]]
   plain, culled, flipped, opened = B.ModelSet(), B.ModelSet(), B.ModelSet(), B.ModelSet()
   plain.add(1, pts, faces, None, 180.0, cull=False)
-  culled.add(1, pts, faces, None, 180.0)
-  flipped.add(1, pts, faces[:, ::-1].copy(), None, 180.0)       # inside-out winding
-  opened.add(1, pts, faces[:-7], None, 180.0)                   # a hole: not closed
+  culled.add(1, pts, faces, None, 180.0, cull='auto')
+  flipped.add(1, pts, faces[:, ::-1].copy(), None, 180.0, cull='auto')       # inside-out winding
+  opened.add(1, pts, faces[:-7], None, 180.0, cull='auto')                   # a hole: not closed
+  default = B.ModelSet()
+  default.add(1, pts, faces, None, 180.0)
+  assert default.info[1]['cull'] == 0                           # the default is the reference's GL state: no culling
   assert plain.info[1]['cull'] == 0 and opened.info[1]['cull'] == 0
   assert culled.info[1]['cull'] in (1, -1) and flipped.info[1]['cull'] == -culled.info[1]['cull']
   ref = B.render_batch(plain, 0, pg, cam, 480, 640)
