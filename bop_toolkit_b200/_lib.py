@@ -123,6 +123,7 @@ _SIGNATURES = {
   'bop_vsd_set_tuning': (_I, [_I, _I, _I, _I]),
   'bop_vsd_set_exact': (_I, [_I]),
   'bop_vsd_depth_bytes_fetched': (_I, [_P, _I, _P]),
+  'bop_points_set_exact': (_I, [_I]),
   'bop_vsd_debug_triangle_list': (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
   'bop_profile_enable': (_I, [_I]),
   'bop_profile_reset': (_I, []),

@@ -8,11 +8,17 @@
 //   adi   bop_toolkit_lib/pose_error.py:164-184  mean_j min_i ||(R_g p_j + t_g) - (R_e p_i + t_e)||
 //   re    bop_toolkit_lib/pose_error.py:187-202, te :205-214
 //
-// Arithmetic is float64 (the reference's dtype).  The rigid part is folded before the
-// per-vertex loop: (R_e p + t_e) - (R_gs p + t_gs) = dR p + dt with dR, dt formed in
-// float64 per (pair, symmetry) -- this removes the |t| ~ 1 m cancellation from the inner
-// loop and halves its work.  ADI runs in the estimated model frame (distances are
-// invariant under the rigid map R_e^T(. - t_e)), so the search set is the static model.
+// The rigid part is folded in float64 (the reference's dtype) before the per-vertex loop:
+// (R_e p + t_e) - (R_gs p + t_gs) = dR p + dt with dR, dt formed per (pair, symmetry) -- this
+// removes the |t| ~ 1 m cancellation from the inner loop and halves its work.  What is left per
+// vertex has no cancellation against large terms, so for float32-exact model points (every PLY
+// model) MSSD evaluates |dR p + dt|^2 in float32 and MSPD evaluates the difference of the two
+// projections as (D.x n.w - n.x D.w) / (n.w (n.w + D.w)) with n = K [R_gs | t_gs] [p; 1] and
+// D = (K [R_e | t_e] - K [R_gs | t_gs]) [p; 1] in float32: every factor is good to ~1e-7 relative
+// and the error of the result stays below 1e-6 relative (bar: 1e-5).  Models whose points are not
+// float32-representable, ADD / PROJ sums and the final square roots stay in float64.  ADI runs in
+// the estimated model frame (distances are invariant under the rigid map R_e^T(. - t_e)), so the
+// search set is the static model.
 #include "common.cuh"
 
 namespace {
@@ -82,8 +88,12 @@ struct SymMaxSmem {
   double Pe[12];
   unsigned long long symmax[BOP_MAX_SYMS_PER_CTA];
   // Running maximum of every lane per symmetry (32 KB): the cross-lane reduction happens once
-  // per CTA and symmetry instead of once per 128 points and symmetry.
+  // per CTA and symmetry instead of once per 128 points and symmetry.  (The float32 paths keep
+  // their maxima in the same storage, widened to double when written.)
   double run[kWarps][BOP_MAX_SYMS_PER_CTA][32];
+  // float32 copies for the float32 per-vertex paths: xg = dR|dt (MSSD) or P_gs (MSPD); xd = P_e - P_gs (MSPD)
+  float xg[BOP_MAX_SYMS_PER_CTA][12];
+  float xd[BOP_MAX_SYMS_PER_CTA][12];
 };
 
 // 1/x for the projections: the hardware's 20-bit float64 seed (MUFU.RCP64H) + one Newton step,
@@ -98,7 +108,7 @@ __device__ __forceinline__ double rcp_f64(double x) {
   return fma(r, fma(-x, r, 1.0), r);
 }
 
-template <typename PT, int MODE>  // MODE 0 = MSSD, 1 = MSPD
+template <typename PT, int MODE, bool F32>  // MODE 0 = MSSD, 1 = MSPD; F32: float32 per-vertex arithmetic
 __device__ __forceinline__ void
 sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_est,
              const double* __restrict__ pose_gt, const double* __restrict__ Kmat,
@@ -142,6 +152,30 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
     symmax[tid] = 0ull;
+    if (F32) {
+      if (MODE == 0) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) sm.xg[tid][k] = (float)xf[tid][k];
+      } else {
+        // P_e - P_gs = K [R_e - R_gs | t_e - t_gs], folded in float64 (no cancellation is left for float32)
+        const double* Kp = Kmat + 9 * (size_t)pair;
+        double dRt[12];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) dRt[k] = pe[k] - Rgs[k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) dRt[9 + k] = pe[9 + k] - tgs[k];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            sm.xd[tid][r * 4 + c] = (float)(Kp[r * 3 + 0] * dRt[0 * 3 + c] + Kp[r * 3 + 1] * dRt[1 * 3 + c] +
+                                            Kp[r * 3 + 2] * dRt[2 * 3 + c]);
+          sm.xd[tid][r * 4 + 3] = (float)(Kp[r * 3 + 0] * dRt[9] + Kp[r * 3 + 1] * dRt[10] + Kp[r * 3 + 2] * dRt[11]);
+        }
+#pragma unroll
+        for (int k = 0; k < 12; ++k) sm.xg[tid][k] = (float)xf[tid][k];
+      }
+    }
   }
   for (int i = tid; i < kWarps * BOP_MAX_SYMS_PER_CTA * 32; i += kThreads) (&sm.run[0][0][0])[i] = 0.0;
   if (MODE == 1 && tid == 32) {
@@ -160,7 +194,53 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
   const PT* __restrict__ pts = (const PT*)M.pts;
   const int N = M.n_pts;
   const int warp = tid >> 5, lane = tid & 31;
-  if (MODE == 1) {
+  if (MODE == 1 && F32) {
+    // MSPD, float32: per (point, symmetry) n = P_gs [p; 1] and D = (P_e - P_gs) [p; 1] (18 FFMA),
+    // then du = (D.x n.w - n.x D.w) / (n.w (n.w + D.w)) (likewise dv): the projections themselves
+    // (hundreds of pixels) never meet, only their difference is formed, from factors that are
+    // each good to ~1e-7 relative.  One MUFU reciprocal per (point, symmetry).
+    constexpr int kPerLane = 4;
+    const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
+    for (int pass = warp; pass < npass; pass += kWarps) {
+      float px[kPerLane], py[kPerLane], pz[kPerLane];
+      bool ok[kPerLane];
+#pragma unroll
+      for (int k = 0; k < kPerLane; ++k) {
+        const int i = (pass * kPerLane + k) * 32 + lane;
+        ok[k] = i < N;
+        px[k] = py[k] = pz[k] = 0.f;
+        if (ok[k]) {
+          px[k] = (float)__ldg(pts + 3 * (size_t)i + 0);
+          py[k] = (float)__ldg(pts + 3 * (size_t)i + 1);
+          pz[k] = (float)__ldg(pts + 3 * (size_t)i + 2);
+        }
+      }
+      for (int sy = 0; sy < ns; ++sy) {
+        float G[12], D[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) { G[k] = sm.xg[sy][k]; D[k] = sm.xd[sy][k]; }
+        float m2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < kPerLane; ++k) {
+          if (ok[k]) {
+            const float nx = fmaf(G[0], px[k], fmaf(G[1], py[k], fmaf(G[2], pz[k], G[3])));
+            const float ny = fmaf(G[4], px[k], fmaf(G[5], py[k], fmaf(G[6], pz[k], G[7])));
+            const float nw = fmaf(G[8], px[k], fmaf(G[9], py[k], fmaf(G[10], pz[k], G[11])));
+            const float dx = fmaf(D[0], px[k], fmaf(D[1], py[k], fmaf(D[2], pz[k], D[3])));
+            const float dy = fmaf(D[4], px[k], fmaf(D[5], py[k], fmaf(D[6], pz[k], D[7])));
+            const float dw = fmaf(D[8], px[k], fmaf(D[9], py[k], fmaf(D[10], pz[k], D[11])));
+            float inv;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(nw * (nw + dw)));
+            const float du = fmaf(dx, nw, -(nx * dw)) * inv, dv = fmaf(dy, nw, -(ny * dw)) * inv;
+            const float d2 = fmaf(du, du, dv * dv);
+            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
+          }
+        }
+        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], (double)m2);
+      }
+    }
+  }
+  if (MODE == 1 && !F32) {
     // MSPD: the projection of the ESTIMATED pose does not depend on the symmetry, and float64
     // division is the expensive instruction here.  A warp takes 128 points (4 per lane), projects
     // them with P_e once, then sweeps the symmetries: 9 DFMA + ONE reciprocal per (point, symmetry).
@@ -205,7 +285,44 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
   }
-  if (MODE == 0) {
+  if (MODE == 0 && F32) {
+    // MSSD, float32: |dR p + dt|^2 with dR, dt folded in float64 and rounded once.
+    constexpr int kPerLane = 4;
+    const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
+    for (int pass = warp; pass < npass; pass += kWarps) {
+      float px[kPerLane], py[kPerLane], pz[kPerLane];
+      bool ok[kPerLane];
+#pragma unroll
+      for (int k = 0; k < kPerLane; ++k) {
+        const int i = (pass * kPerLane + k) * 32 + lane;
+        ok[k] = i < N;
+        px[k] = py[k] = pz[k] = 0.f;
+        if (ok[k]) {
+          px[k] = (float)__ldg(pts + 3 * (size_t)i + 0);
+          py[k] = (float)__ldg(pts + 3 * (size_t)i + 1);
+          pz[k] = (float)__ldg(pts + 3 * (size_t)i + 2);
+        }
+      }
+      for (int sy = 0; sy < ns; ++sy) {
+        float T[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) T[k] = sm.xg[sy][k];
+        float m2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < kPerLane; ++k) {
+          if (ok[k]) {
+            const float dx = fmaf(T[0], px[k], fmaf(T[1], py[k], fmaf(T[2], pz[k], T[9])));
+            const float dy = fmaf(T[3], px[k], fmaf(T[4], py[k], fmaf(T[5], pz[k], T[10])));
+            const float dz = fmaf(T[6], px[k], fmaf(T[7], py[k], fmaf(T[8], pz[k], T[11])));
+            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
+          }
+        }
+        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], (double)m2);
+      }
+    }
+  }
+  if (MODE == 0 && !F32) {
     // MSSD: same sweep -- a warp keeps 128 points in registers and visits every symmetry, so the
     // points are loaded (and converted to float64) once instead of once per symmetry.
     constexpr int kPerLane = 4;
@@ -257,15 +374,17 @@ template <int MODE>
 __global__ void __launch_bounds__(kThreads, BOP_SYM_CTAS)
 sym_max_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
                const double* __restrict__ pose_est, const double* __restrict__ pose_gt,
-               const double* __restrict__ Kmat, int syms_per_cta, int gate,
+               const double* __restrict__ Kmat, int syms_per_cta, int gate, int exact64,
                unsigned long long* __restrict__ out_bits) {
   __shared__ SymMaxSmem sm;
   const int pair = blockIdx.x;
   const bop_model_dev M = models[obj_idx[pair]];
   if (M.pts_f64)
-    sym_max_body<double, MODE>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
+    sym_max_body<double, MODE, false>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
+  else if (exact64)
+    sym_max_body<float, MODE, false>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
   else
-    sym_max_body<float, MODE>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
+    sym_max_body<float, MODE, true>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
 }
 
 // ---------------------------------------------------------------------------------
@@ -489,6 +608,15 @@ extern "C" int bop_re_te_dev(const double* pose_est, const double* pose_gt, int 
   return 0;
 }
 
+static int g_points_exact = 0;   // bop_points_set_exact: float64 per-vertex arithmetic for MSSD / MSPD (tests)
+
+// Test hook: exact != 0 makes MSSD / MSPD evaluate every vertex in float64 (the reference's dtype)
+// instead of the float32 forms described at the top of this file; tests compare the two.
+extern "C" int bop_points_set_exact(int exact) {
+  g_points_exact = exact != 0;
+  return 0;
+}
+
 static int launch_sym_max(int mode, const bop_model_dev* models, const int32_t* obj_idx,
                           const double* pose_est, const double* pose_gt, const double* K,
                           int n_pairs, int max_syms, int gate, double* out, cudaStream_t s) {
@@ -508,9 +636,9 @@ static int launch_sym_max(int mode, const bop_model_dev* models, const int32_t* 
   dim3 grid(n_pairs, groups);
   bop_prof_begin(mode == 0 ? BOP_PROF_MSSD : BOP_PROF_MSPD, s);
   if (mode == 0)
-    sym_max_kernel<0><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, bits);
+    sym_max_kernel<0><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, g_points_exact, bits);
   else
-    sym_max_kernel<1><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, bits);
+    sym_max_kernel<1><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, spc, gate, g_points_exact, bits);
   bop_prof_end(mode == 0 ? BOP_PROF_MSSD : BOP_PROF_MSPD, s);
   BOP_LAUNCH_CHECK();
   return 0;

@@ -293,6 +293,12 @@ int bop_vsd_set_tuning(int tile_px, int threads, int ctas_per_sm, int small_tri_
  * one counter per tau); exact == 2 keeps the float32 pre-test but uses per-tau counters.
  * Bit-identical counts in all three modes; tests compare them. */
 int bop_vsd_set_exact(int exact);
+/* Test hook: exact != 0 makes bop_mssd_dev / bop_mspd_dev evaluate every vertex in float64 (the
+ * reference's dtype).  By default models whose points are float32-representable are evaluated in
+ * float32 AFTER the rigid parts were folded in float64 (dR p + dt; difference of projections as
+ * (D.x n.w - n.x D.w) / (n.w (n.w + D.w))): no cancellation is left, results agree to ~1e-6
+ * relative (bar of pose_error.mssd / mspd: 1e-5).  Tests compare the two. */
+int bop_points_set_exact(int exact);
 
 
 /* ---- depth-PNG input on the device -------------------------------------------------------

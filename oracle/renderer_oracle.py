@@ -16,8 +16,8 @@ _LIB = None
 
 def build(force=False):
   so = os.path.join(_HERE, 'liboracle.so')
-  src = os.path.join(_HERE, 'raster_oracle.c')
-  if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+  srcs = [os.path.join(_HERE, f) for f in ('raster_oracle.c', 'raycast_oracle.c')]
+  if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
     subprocess.check_call(['make', '-C', _HERE, '-s', 'liboracle.so'])
   return so
 
@@ -39,7 +39,26 @@ def _lib():
       ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
       ctypes.c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
       ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    _LIB.raycast_render_depth.restype = ctypes.c_int
+    _LIB.raycast_render_depth.argtypes = _LIB.oracle_render_depth.argtypes
   return _LIB
+
+
+def raycast_depth(pts, faces, R, t, fx, fy, cx, cy, height, width):
+  """The second restatement (oracle/raycast_oracle.c): per-pixel ray / triangle intersection in
+  camera space.  Exact window positions (no sub-pixel snapping)."""
+  pts = np.ascontiguousarray(pts, dtype=np.float64)
+  faces = np.ascontiguousarray(faces, dtype=np.int32)
+  R = np.ascontiguousarray(R, dtype=np.float64).reshape(9)
+  t = np.ascontiguousarray(t, dtype=np.float64).reshape(3)
+  depth = np.empty((height, width), dtype=np.float32)
+  rc = _lib().raycast_render_depth(
+    pts.ctypes.data, pts.shape[0], faces.ctypes.data, faces.shape[0], R.ctypes.data,
+    t.ctypes.data, float(fx), float(fy), float(cx), float(cy), int(height), int(width),
+    depth.ctypes.data)
+  if rc != 0:
+    raise MemoryError('raycast_render_depth failed')
+  return depth
 
 
 def render_depth(pts, faces, R, t, fx, fy, cx, cy, height, width, subpixel_bits=0):

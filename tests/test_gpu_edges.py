@@ -325,10 +325,12 @@ def test_float32_decision_path_equals_exact(B):
   results = {}
   noisy = np.where(dg > 0, dg + rng.normal(0, 3.0, dg.shape).astype(np.float32), 1500.0).astype(np.float32)
   try:
-    for exact in (1, 0):
+    for exact in (1, 0, 2):      # 1: all float64; 0: float32 pre-test + tau histogram; 2: float32 pre-test + per-tau counters
       _lib.check(lib.bop_vsd_set_exact(exact))
       out = []
-      for depth, tt in ((dt, taus), (dt, [0.05 * (k + 1) for k in range(10)]), (noisy, taus[:3])):
+      unsorted = [taus[k] for k in (3, 0, 7, 1)]              # not ascending: per-tau counters whatever the mode
+      for depth, tt in ((dt, taus), (dt, [0.05 * (k + 1) for k in range(10)]), (noisy, taus[:3]), (dt, unsorted),
+                        (dt, [taus[2], taus[2], taus[5]])):    # duplicate taus
         for mode in ('bop19', 'bop18'):
           for norm in (True, False):
             t2 = tt if norm else [t * 180.0 for t in tt]
@@ -337,8 +339,8 @@ def test_float32_decision_path_equals_exact(B):
       results[exact] = out
   finally:
     _lib.check(lib.bop_vsd_set_exact(0))
-  for a, b in zip(results[1], results[0]):
-    assert np.array_equal(a, b)
+  for a, b, c in zip(results[1], results[0], results[2]):
+    assert np.array_equal(a, b) and np.array_equal(a, c)
   assert results[1][1][:, 1].sum() > 1000                    # the cases do have intersections
   # and the exact run equals the stand-alone float64 pixel pass on the same renders
   e, c = B.vsd_from_depth_batch(torch.from_numpy(de).cuda(), torch.from_numpy(dg).cuda(), dt, im, Ks, 180.0,
@@ -422,3 +424,84 @@ def test_wide_image(B, oracle_built):
     assert np.allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=0, atol=1e-11)
   st = B.mask_overlap_batch(ms, 0, pe, pg, K, H, W)
   assert int(st['counts'][:, 0].min()) > 0
+
+
+def test_point_errors_float32_fold_vs_float64(B):
+  """MSSD / MSPD evaluate float32-exact model points in float32 AFTER folding the rigid parts in
+  float64 (pose_points.cu); bop_points_set_exact(1) forces the reference's float64 per vertex.
+  The two must agree to 1e-6 relative (bar: 1e-5) on close estimates, gross outliers, a skewed K,
+  estimates that ARE a symmetry of the GT (errors ~ 0) and poses partly behind the camera."""
+  from bop_toolkit_b200 import _lib, synth, misc
+  lib = _lib.lib()
+  K = synth.LM_K.copy()
+  K[0, 1] = 3.5                                   # skew
+  pts, faces = synth.make_mesh(40, 80, 220.0, seed=41)
+  syms = misc.get_symmetry_transformations({'diameter': 220.0, 'symmetries_discrete': synth.discrete_z_symmetries(6)}, 0.01)
+  ms = B.ModelSet()
+  ms.add(1, pts, None, syms, 220.0)
+  n = 600
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=42, z_range=(350.0, 1500.0), outlier_frac=0.1)
+  # estimates that are exactly a symmetry of the GT
+  for i in range(0, 40):
+    s_ = syms[i % len(syms)]
+    R_e[i] = R_g[i] @ s_['R']
+    t_e[i] = (R_g[i] @ s_['t']).reshape(3) + t_g[i]
+  # tiny perturbations (sub-micron errors) and poses straddling the camera plane
+  t_e[40:80] = t_g[40:80] + 1e-4
+  R_e[40:80] = R_g[40:80]
+  t_g[80:90, 2] = 60.0
+  t_e[80:90, 2] = 58.0
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  Ks = np.tile(K.reshape(1, 9), (n, 1))
+  out = {}
+  try:
+    for exact in (1, 0):
+      _lib.check(lib.bop_points_set_exact(exact))
+      out[exact] = (B.mssd_batch(ms, 0, pe, pg).cpu().numpy(), B.mspd_batch(ms, 0, pe, pg, Ks).cpu().numpy())
+  finally:
+    _lib.check(lib.bop_points_set_exact(0))
+  for name, a, b in (('mssd', out[1][0], out[0][0]), ('mspd', out[1][1], out[0][1])):
+    fin = np.isfinite(a)
+    assert np.array_equal(fin, np.isfinite(b)), name
+    rel = np.abs(a[fin] - b[fin]) / np.maximum(np.abs(a[fin]), 1e-6)   # 1e-6 mm / px floor for the ~0 cases
+    assert rel.max() <= 1e-6, (name, float(rel.max()), int(np.argmax(rel)))
+  assert out[1][0][:40].max() < 1e-9 and out[0][0][:40].max() < 1e-3      # symmetric poses: ~0 either way
+
+
+def test_triangle_lists_are_sorted_by_band_and_class(B):
+  """The geometry pass writes every (pair, pose) triangle list sorted by (row band, candidate-
+  rectangle class, largest first) -- what keeps the lanes of a raster warp converged.  Checked
+  through the debug hook on a batch with small and multi-band ROIs."""
+  from bop_toolkit_b200 import synth
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(50, 100, 260.0, seed=51)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 260.0)
+  n = 12
+  R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=52, z_range=(380.0, 1400.0), outlier_frac=0.0)
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)
+  depth = np.full((n, 480, 640), 1000.0, np.float32)
+  B.vsd_batch(ms, 0, pe, pg, depth, np.arange(n, dtype=np.int32), np.tile(K.reshape(1, 9), (n, 1)), 15.0, [0.2])
+  n_multi = 0
+  for pair in range(n):
+    for pose in (0, 1):
+      xy = B.debug_triangle_list(ms, n, 480, 640, pair, pose).astype(np.int64)
+      assert len(xy) > 0
+      minx, maxx = xy[:, [0, 2, 4]].min(1), xy[:, [0, 2, 4]].max(1)
+      miny, maxy = xy[:, [1, 3, 5]].min(1), xy[:, [1, 3, 5]].max(1)
+      w = np.minimum(639, maxx >> 8) - np.maximum(0, (minx + 255) >> 8) + 1
+      h = np.minimum(479, maxy >> 8) - np.maximum(0, (miny + 255) >> 8) + 1
+      assert (w > 0).all() and (h > 0).all()                 # only triangles that can draw
+      key = np.minimum(h, 15) * 16 + np.minimum(w, 15)
+      # the list is a sequence of segments (bands, then the shared segment); inside a segment the
+      # class key never increases
+      rises = np.flatnonzero(np.diff(key) > 0)
+      assert len(rises) <= 16, len(rises)
+      n_multi += int(len(rises) > 0)
+      cost = 0
+      k32 = len(w) // 32 * 32
+      W_, H_ = w[:k32].reshape(-1, 32), h[:k32].reshape(-1, 32)
+      for r in range(int(H_.max())):
+        cost += int(np.where(H_ > r, W_, 0).max(1).sum())
+      assert (W_ * H_).sum() >= 0.8 * 32 * cost           # >= 80 % of the lane-slots of the pixel loops are used
+  assert n_multi > 0                                       # some ROI needed more than one band

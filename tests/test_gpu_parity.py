@@ -605,3 +605,49 @@ def test_backface_culling_is_output_preserving(B):
 def torch_equal(a, b):
   import torch
   return bool(torch.equal(a, b))
+
+
+# ------------------------------------------------------------------ analytic known-answer scenes
+@pytest.mark.gpu
+def test_render_known_answer_scenes(B):
+  """The CUDA rasteriser on scenes with a closed-form answer (the same two the oracles are checked
+  on in tests/test_oracle_golden.py): a tilted quad (depth = plane depth along the pixel ray) and
+  two interpenetrating quads (the nearer plane wins).  Pixels whose hit point is within 3 mm of a
+  quad border are left out (edge ownership is implementation-defined)."""
+  def plane_depth(n, d, K, H, W):
+    ys, xs = np.mgrid[0:H, 0:W]
+    rx, ry = (xs + 0.5 - K[0, 2]) / K[0, 0], (ys + 0.5 - K[1, 2]) / K[1, 1]
+    return d / (n[0] * rx + n[1] * ry + n[2]), rx, ry
+  # tilted plane
+  K = np.array([[120.0, 0, 80.0], [0, 118.0, 60.5], [0, 0, 1]])
+  H, W = 120, 160
+  n, d = np.array([0.25, -0.125, 1.0]), 500.0
+  xy = np.array([[-250.0, -200.0], [300.0, -150.0], [280.0, 220.0], [-220.0, 180.0]])
+  pts = np.column_stack([xy, (d - n[0] * xy[:, 0] - n[1] * xy[:, 1]) / n[2]])
+  ms = B.ModelSet()
+  ms.add(1, pts, np.array([[0, 1, 2], [0, 2, 3]]), None, 600.0)
+  pose = B.pack_poses(np.eye(3)[None], np.zeros((1, 3)))
+  cam = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]])
+  got = B.render_batch(ms, 0, pose, cam, H, W)[0].cpu().numpy()
+  want, _, _ = plane_depth(n, d, K, H, W)
+  cov = got > 0
+  assert cov.sum() > 0.5 * H * W
+  assert np.abs(got[cov] - want[cov]).max() <= 1e-5 * want[cov].max()      # bar: 1e-3 relative
+  # interpenetrating quads
+  K = np.array([[100.0, 0, 64.0], [0, 100.0, 48.0], [0, 0, 1]])
+  H, W = 96, 128
+  quad = np.array([[-200.0, -150.0], [200.0, -150.0], [200.0, 150.0], [-200.0, 150.0]])
+  pts = np.vstack([np.column_stack([quad, 400.0 + 0.5 * quad[:, 0]]), np.column_stack([quad, 400.0 - 0.5 * quad[:, 0]])])
+  ms2 = B.ModelSet()
+  ms2.add(1, pts, np.array([[0, 1, 2], [0, 2, 3], [4, 5, 6], [4, 6, 7]]), None, 600.0)
+  cam = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]])
+  got = B.render_batch(ms2, 0, pose, cam, H, W)[0].cpu().numpy()
+  da, rx, ry = plane_depth(np.array([-0.5, 0.0, 1.0]), 400.0, K, H, W)
+  db, _, _ = plane_depth(np.array([0.5, 0.0, 1.0]), 400.0, K, H, W)
+  inside = lambda dz, m: (np.abs(rx * dz) < 200.0 - m) & (np.abs(ry * dz) < 150.0 - m)
+  want = np.minimum(np.where(inside(da, 0.0), da, np.inf), np.where(inside(db, 0.0), db, np.inf))
+  safe = (inside(da, 3.0) | ~inside(da, -3.0)) & (inside(db, 3.0) | ~inside(db, -3.0)) & np.isfinite(want)
+  assert safe.sum() > 0.5 * H * W and (got[safe] > 0).all()
+  assert np.abs(got[safe] - want[safe]).max() <= 1e-5 * want[safe].max()
+  outside = ~inside(da, -3.0) & ~inside(db, -3.0)
+  assert not got[outside].any()
