@@ -2,6 +2,7 @@
 // and the host-buffer (`*_host`) convenience layer declared in include/bop_b200.h.
 #include <atomic>
 #include <string>
+#include <math.h>
 #include <vector>
 
 #include "common.cuh"
@@ -129,7 +130,13 @@ extern "C" int bop_model_upload(const double* pts, int n_pts, const int32_t* fac
   d.pts = p;
   d.pts_f64 = f32_exact ? 0 : 1;
   d.cull = 0;       /* the convenience layer never culls; see batch.ModelSet for the verified path */
-  d.cull_min_dist = 0.f;
+  double r2 = 0.0;   // bounding sphere about the model origin (also bounds w in the MSPD float32 path)
+  for (int i = 0; i < n_pts; ++i) {
+    const double x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+    const double q = x * x + y * y + z * z;
+    if (q > r2) r2 = q;
+  }
+  d.cull_min_dist = (float)(sqrt(r2) * 1.001);
   BOP_CUDA(cudaMalloc(&p, v4.size() * sizeof(float)));
   BOP_CUDA(cudaMemcpy(p, v4.data(), v4.size() * sizeof(float), cudaMemcpyHostToDevice));
   d.verts4 = (const float*)p;

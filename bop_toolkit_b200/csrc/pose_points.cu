@@ -379,9 +379,30 @@ sym_max_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restri
   __shared__ SymMaxSmem sm;
   const int pair = blockIdx.x;
   const bop_model_dev M = models[obj_idx[pair]];
+  bool f32 = !M.pts_f64 && !exact64;
+  if (MODE == 1 && f32) {
+    // The float32 projection difference is good to ~1e-7 x (w at the model centre / smallest w):
+    // keep it for poses whose every vertex has w >= 10 % of the centre's (any sensible pose); a
+    // model that comes close to or crosses the camera plane is ill-conditioned and takes the
+    // float64 path.  |p| <= cull_min_dist for every model point, so w >= k2.t - |k2| r.
+    const double* Kp = Kmat + 9 * (size_t)pair;
+    const double* pe = pose_est + 12 * (size_t)pair;
+    const double* pg = pose_gt + 12 * (size_t)pair;
+    const double kr = sqrt(Kp[6] * Kp[6] + Kp[7] * Kp[7] + Kp[8] * Kp[8]) * (double)M.cull_min_dist;
+    const double we = Kp[6] * pe[9] + Kp[7] * pe[10] + Kp[8] * pe[11];
+    f32 = we - kr >= 0.1 * we;
+    const int s0 = blockIdx.y * syms_per_cta, s1 = min(M.n_syms, s0 + syms_per_cta);
+    for (int sy = s0; sy < s1 && f32; ++sy) {
+      const double* st = M.syms + 12 * (size_t)sy + 9;
+      double tg[3];
+      mat3_vec(pg, st, tg);
+      const double wg = Kp[6] * (tg[0] + pg[9]) + Kp[7] * (tg[1] + pg[10]) + Kp[8] * (tg[2] + pg[11]);
+      f32 = wg - kr >= 0.1 * wg;
+    }
+  }
   if (M.pts_f64)
     sym_max_body<double, MODE, false>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
-  else if (exact64)
+  else if (!f32)
     sym_max_body<float, MODE, false>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);
   else
     sym_max_body<float, MODE, true>(M, pair, pose_est, pose_gt, Kmat, syms_per_cta, gate, out_bits, sm);

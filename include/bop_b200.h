@@ -71,7 +71,9 @@ typedef struct bop_model_dev {
   float          cull_min_dist; /* culling is applied to a pose only if |t| > cull_min_dist, i.e. the
                                camera centre lies outside the model's bounding sphere around its
                                origin (inside a mesh the visible faces ARE the back faces); set it
-                               to max |pts| or more.  0 with cull != 0 culls every pose.          */
+                               to max |pts| or more.  0 with cull != 0 culls every pose.  The
+                               same radius tells bop_mspd_dev whether a pose keeps every vertex
+                               well in front of the camera plane (float32 path) or not (float64). */
 } bop_model_dev;
 
 /* Parameters of pose_error.vsd (bop_toolkit_lib/pose_error.py:17-18). */
