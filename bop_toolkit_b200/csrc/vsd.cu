@@ -176,7 +176,7 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     const double* c = g.K + 4 * (size_t)item;
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
-  if (M.n_pts > g.pv_stride || M.n_faces > g.tri_cap || M.n_faces >= (1 << 24)) __trap();   // max_geom below the model's size: fail loudly
+  if (M.n_pts > g.pv_stride || M.n_faces > g.tri_cap) __trap();   // max_geom below the model's size: fail loudly
   bool gated = false;
   if (g.gate && n_poses == 2)   // uniform over the CTA
     gated = !sphere_projections_overlap(0.5 * diam, pose[0] + 9, pose[1] + 9);
@@ -260,7 +260,7 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     } else {
       D.x0 = D.y0 = D.w = D.h = 0; y0 = 0;
     }
-    const int nbs = (nb >= 2 && nb <= kMaxSortBands && M.n_faces < (1 << 20)) ? nb : 0;
+    const int nbs = (nb >= 2 && nb <= kMaxSortBands) ? nb : 0;
     D.nbs = nbs;
     g.desc[item] = D;
     s_plan[0] = y0; s_plan[1] = band; s_plan[2] = nb; s_plan[3] = nbs;
@@ -281,7 +281,6 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
   const int roi_y0 = s_plan[0], band_rows = s_plan[1], nb = s_plan[2], nbs = s_plan[3];
   const int nseg = nbs + 1;                 // band segments + the shared segment (unsorted: one segment)
   const int nbins = nseg * kClasses;
-  const int fbits = nbs ? 20 : 24;          // stage entry = key << fbits | face
   const int4* __restrict__ faces = (const int4*)M.faces4;
   const int F = M.n_faces;
   const unsigned lt = (1u << lane) - 1u;
@@ -309,9 +308,11 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (!(t[0] * t[0] + t[1] * t[1] + t[2] * t[2] > r * r)) cull = 0;
     }
     const size_t out0 = (size_t)gw * g.tri_cap;
-    // Classify: two faces per thread and iteration (both index loads and all six record gathers
-    // are in flight before the first test).  Survivors are staged as (key << fbits | face) in
-    // arrival order and counted per key (one shared atomic per distinct key and warp).
+    // Pass 1 -- classify: two faces per thread and iteration (both index loads and all six record
+    // gathers are in flight before the first test).  The key of every face (0 = cannot draw) goes
+    // to a per-list key array in face order (coalesced 16-bit stores) and is counted (one shared
+    // atomic per distinct key and warp).
+    unsigned short* const keys = (unsigned short*)(g.stage + out0);
     auto key_of = [&](int cls, int by0, int by1) {
       if (cls == 0 || nbs == 0) return cls;
       const int b0 = (by0 - roi_y0) / band_rows, b1 = (by1 - roi_y0) / band_rows;
@@ -330,25 +331,15 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (fa < F) { a0 = PV(p, ia.x); a1 = PV(p, ia.y); a2 = PV(p, ia.z); }
       if (fb < F) { b0 = PV(p, ib.x); b1 = PV(p, ib.y); b2 = PV(p, ib.z); }
       int y0a = 0, y1a = 0, y0b = 0, y1b = 0;
-      if (fa < F) ka = key_of(tri_class(a0, a1, a2, W, H, cull, y0a, y1a), y0a, y1a);
-      if (fb < F) kb = key_of(tri_class(b0, b1, b2, W, H, cull, y0b, y1b), y0b, y1b);
-      const unsigned ma = __ballot_sync(BOP_FULL_MASK, ka != 0), mb = __ballot_sync(BOP_FULL_MASK, kb != 0);
-      if (ma | mb) {   // warp-uniform
-        const int na = __popc(ma);
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&s_n, na + __popc(mb));
-        base = __shfl_sync(BOP_FULL_MASK, base, 0);
-        if (base + na + __popc(mb) > g.tri_cap) __trap();   // caller passed a max_geom below (n_faces + 1) / 2: fail loudly
-        if (ka) g.stage[out0 + base + __popc(ma & lt)] = ((unsigned)ka << fbits) | (unsigned)fa;
-        if (kb) g.stage[out0 + base + na + __popc(mb & lt)] = ((unsigned)kb << fbits) | (unsigned)fb;
-        const unsigned pa = __match_any_sync(BOP_FULL_MASK, ka), pb = __match_any_sync(BOP_FULL_MASK, kb);
-        if (ka && (pa & lt) == 0) atomicAdd(&s_bins[ka], __popc(pa));
-        if (kb && (pb & lt) == 0) atomicAdd(&s_bins[kb], __popc(pb));
-      }
+      if (fa < F) { ka = key_of(tri_class(a0, a1, a2, W, H, cull, y0a, y1a), y0a, y1a); keys[fa] = (unsigned short)ka; }
+      if (fb < F) { kb = key_of(tri_class(b0, b1, b2, W, H, cull, y0b, y1b), y0b, y1b); keys[fb] = (unsigned short)kb; }
+      const unsigned pa = __match_any_sync(BOP_FULL_MASK, ka), pb = __match_any_sync(BOP_FULL_MASK, kb);
+      if (ka && (pa & lt) == 0) atomicAdd(&s_bins[ka], __popc(pa));
+      if (kb && (pb & lt) == 0) atomicAdd(&s_bins[kb], __popc(pb));
     }
     __syncthreads();
-    // Exclusive prefix over the bins (each thread owns nbins / 512 consecutive bins; warp scan +
-    // one pass over the warp totals): s_bins becomes the write cursor of every key.
+    // Exclusive prefix over the bins (each thread owns ceil(nbins / 512) consecutive bins; warp scan
+    // + one pass over the warp totals): s_bins becomes the write cursor of every key.
     {
       const int per = (nbins + kAsmThreads - 1) / kAsmThreads;
       const int first = tid * per;
@@ -368,39 +359,47 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       int run = wbase + incl - sum;
       for (int k = 0; k < per; ++k)
         if (first + k < nbins) { const int c = s_bins[first + k]; s_bins[first + k] = run; run += c; }
+      if (tid == kAsmThreads - 1) s_n = run;   // the last thread's running total = number of survivors
     }
     __syncthreads();
     const int n_surv = s_n;
+    if (n_surv > g.tri_cap) __trap();   // caller passed a max_geom below (n_faces + 1) / 2: fail loudly
     if (tid < kBandOffN) boff[tid] = tid < nseg ? s_bins[tid * kClasses] : n_surv;   // read before the scatter moves the cursors
     if (tid == 0) g.tri_cnt[gw] = n_surv;
     __syncthreads();
-    // Scatter: every staged survivor fetches its face again (dense: all lanes hold a survivor),
-    // takes a slot under its key (one shared atomic per distinct key and warp) and writes its record.
-    // Software pipeline over the dependent loads (stage entry -> face indices -> vertex records):
-    // the entry is loaded two iterations ahead, the face indices one iteration ahead.
-    const unsigned fmask = (1u << fbits) - 1u;
-    unsigned e1 = tid < n_surv ? g.stage[out0 + tid] : 0u;
-    unsigned e2 = tid + kAsmThreads < n_surv ? g.stage[out0 + tid + kAsmThreads] : 0u;
-    int4 idx1 = make_int4(0, 0, 0, 0);
-    if (e1) idx1 = __ldg(faces + (e1 & fmask));
-    for (int i0 = 0; i0 < n_surv; i0 += kAsmThreads) {
-      const unsigned e = e1;
-      const int4 idx = idx1;
-      e1 = e2;
-      const int i2 = i0 + tid + 2 * kAsmThreads;
-      e2 = i2 < n_surv ? g.stage[out0 + i2] : 0u;
-      if (e1) idx1 = __ldg(faces + (e1 & fmask));
-      const int k = (int)(e >> fbits);
-      const unsigned peers = __match_any_sync(BOP_FULL_MASK, k);
-      const int leader = __ffs(peers) - 1;
-      int slot = 0;
-      if (k && lane == leader) slot = atomicAdd(&s_bins[k], __popc(peers));
-      slot = __shfl_sync(BOP_FULL_MASK, slot, leader) + __popc(peers & lt);
-      if (k) {
-        const int4 r0 = PV(p, idx.x), r1 = PV(p, idx.y), r2 = PV(p, idx.z);
-        g.tri_a[out0 + slot] = make_int4(r0.x, r0.y, r1.x, r1.y);
-        g.tri_b[out0 + slot] = make_int4(r2.x, r2.y, r0.z, r1.z);
-        g.tri_c[out0 + slot] = __int_as_float(r2.z);
+    // Pass 2 -- scatter, again in face order: indices and keys are coalesced loads fetched one
+    // iteration ahead, so nothing in the loop waits on a dependent global load; a surviving face
+    // takes a slot under its key (one shared atomic per distinct key and warp), gathers its three
+    // records from shared memory once more and writes its 36 bytes.
+    na4 = nb4 = make_int4(0, 0, 0, 0);
+    int nka = 0, nkb = 0;
+    if (tid < F) { na4 = __ldg(faces + tid); nka = keys[tid]; }
+    if (tid + kAsmThreads < F) { nb4 = __ldg(faces + tid + kAsmThreads); nkb = keys[tid + kAsmThreads]; }
+    for (int f0 = 0; f0 < F; f0 += 2 * kAsmThreads) {
+      const int fa = f0 + tid, fb = fa + kAsmThreads;
+      const int4 ia = na4, ib = nb4;
+      const int ka = nka, kb = nkb;
+      nka = nkb = 0;
+      if (fa + 2 * kAsmThreads < F) { na4 = __ldg(faces + fa + 2 * kAsmThreads); nka = keys[fa + 2 * kAsmThreads]; }
+      if (fb + 2 * kAsmThreads < F) { nb4 = __ldg(faces + fb + 2 * kAsmThreads); nkb = keys[fb + 2 * kAsmThreads]; }
+      const unsigned pa = __match_any_sync(BOP_FULL_MASK, ka), pb = __match_any_sync(BOP_FULL_MASK, kb);
+      const int la = __ffs(pa) - 1, lb = __ffs(pb) - 1;
+      int sa = 0, sb = 0;
+      if (ka && lane == la) sa = atomicAdd(&s_bins[ka], __popc(pa));
+      if (kb && lane == lb) sb = atomicAdd(&s_bins[kb], __popc(pb));
+      sa = __shfl_sync(BOP_FULL_MASK, sa, la) + __popc(pa & lt);
+      sb = __shfl_sync(BOP_FULL_MASK, sb, lb) + __popc(pb & lt);
+      if (ka) {
+        const int4 r0 = PV(p, ia.x), r1 = PV(p, ia.y), r2 = PV(p, ia.z);
+        g.tri_a[out0 + sa] = make_int4(r0.x, r0.y, r1.x, r1.y);
+        g.tri_b[out0 + sa] = make_int4(r2.x, r2.y, r0.z, r1.z);
+        g.tri_c[out0 + sa] = __int_as_float(r2.z);
+      }
+      if (kb) {
+        const int4 r0 = PV(p, ib.x), r1 = PV(p, ib.y), r2 = PV(p, ib.z);
+        g.tri_a[out0 + sb] = make_int4(r0.x, r0.y, r1.x, r1.y);
+        g.tri_b[out0 + sb] = make_int4(r2.x, r2.y, r0.z, r1.z);
+        g.tri_c[out0 + sb] = __int_as_float(r2.z);
       }
     }
   }
@@ -632,7 +631,7 @@ __device__ __forceinline__ void load_depth4(const PixParams& pp, const void* __r
 namespace {
 
 constexpr int kQueueCap = 2048;   // deferred (large) triangles per pose and work item
-constexpr int kPrefetchBytes = 32 * 1152;   // one batch of 32 records (36 B each) per warp, up to 32 warps
+constexpr int kPrefetchWarpBytes = 1152;     // one batch of 32 records (36 B each) in flight per warp
 
 struct FusedArgs {
   const bop_model_dev* models;
@@ -1348,9 +1347,18 @@ void set_geometry(FusedArgs& a, unsigned char* ws, const WsLayout& L) {
 
 // z-tile capacity actually used for images of width W: the tuned value, lowered when the per-column
 // ray tables of a wide image would not leave room for it in shared memory.
-int effective_tile_px(int W) {
+// Dynamic shared memory one CTA of the fused kernel may use: the SM's 227 KB split over the resident
+// CTAs, minus the kernel's static shared memory and the 1 KB the driver reserves per CTA.
+long long fused_smem_budget() {
+  return (long long)227 * 1024 / g_tune.ctas_per_sm - 3072;
+}
+long long fused_smem_fixed(int W) {   // everything but the z-tiles
   const int wp = (W + 3) & ~3;
-  const long long room = (long long)225 * 1024 - (long long)wp * 12 - (long long)kMaxBandRows * 12 - (long long)kQueueCap * 4 - (long long)kPrefetchBytes;
+  return (long long)wp * 12 + (long long)kMaxBandRows * 12 + (long long)kQueueCap * 4 +
+         (long long)(g_tune.threads / 32) * kPrefetchWarpBytes;
+}
+int effective_tile_px(int W) {
+  const long long room = fused_smem_budget() - fused_smem_fixed(W);
   long long fit = (room / 8) & ~3ll;
   if (fit < kMinTilePx) fit = kMinTilePx;
   return g_tune.tile_px < fit ? g_tune.tile_px : (int)fit;
@@ -1358,8 +1366,8 @@ int effective_tile_px(int W) {
 
 template <int MODE, int NT, bool HIST>
 int launch_fused_nt(const FusedArgs& a, int W, cudaStream_t s) {
-  const int wp = (W + 3) & ~3;
-  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)wp * 12 + (size_t)kMaxBandRows * 12 + (size_t)kQueueCap * 4 + (size_t)kPrefetchBytes;
+  const size_t smem = (size_t)2 * a.tile_px * 4 + (size_t)fused_smem_fixed(W);
+  // (a tuning that asks for more CTAs per SM than its tile allows simply runs with fewer resident)
   BOP_REQUIRE(smem <= (size_t)225 * 1024, "fused kernel: z-tile + tables exceed shared memory (lower tile_px)");
   const int grid = sm_count() * g_tune.ctas_per_sm;
   const int slot = MODE == MODE_RENDER ? BOP_PROF_RENDER : ((MODE == MODE_MASK || MODE == MODE_GTINFO) ? BOP_PROF_MASK : BOP_PROF_VSD_FUSED);
