@@ -63,8 +63,9 @@ def build(force=False, verbose=False):
   (libbop_b200.so.src): file times do not survive copying the tree to another machine."""
   srcs = [os.path.join(CSRC, s) for s in SOURCES]
   deps = srcs + [os.path.join(CSRC, h) for h in HEADERS]
-  cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
-         '-Xcompiler', '-fPIC', '-shared', '-o', SO_PATH] + srcs
+  extra = os.environ.get('BOP_NVCC_FLAGS', '').split()     # e.g. -DBOP_DEBUG_CHECKS (device-side range checks)
+  cmd = ['nvcc', '-O3', '-std=c++17', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo'] + extra + \
+        ['-Xcompiler', '-fPIC', '-shared', '-o', SO_PATH] + srcs
   want = _source_hash(deps, [c for c in cmd if c != SO_PATH and c not in srcs] + SOURCES)
   stamp = SO_PATH + '.src'
   if not force and os.path.exists(SO_PATH) and os.path.exists(stamp):

@@ -36,6 +36,25 @@ void bop_prof_end(int slot, cudaStream_t s);
     if (!(cond)) return bop_set_error_msg(-1, msg);                        \
   } while (0)
 
+// ---- device-side self checks ------------------------------------------------------
+// Built with -DBOP_DEBUG_CHECKS (BOP_NVCC_FLAGS=-DBOP_DEBUG_CHECKS python -c "from bop_toolkit_b200
+// import _lib; _lib.build()"), every index the kernels compute into shared-memory tiles, triangle
+// lists, sort bins and images is range-checked and a violation traps (the launch then fails with
+// an error instead of corrupting memory).  compute-sanitizer is not available on the GPU pool, so
+// this is how the GPU test suite is run "with bounds checking" (profiles/r02_debug_checks.txt).
+#ifdef BOP_DEBUG_CHECKS
+#define BOP_DCHECK(cond)                                                                        \
+  do {                                                                                          \
+    if (!(cond)) {                                                                              \
+      printf("BOP_DCHECK failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__,   \
+             (int)blockIdx.x, (int)threadIdx.x);                                                \
+      __trap();                                                                                 \
+    }                                                                                           \
+  } while (0)
+#else
+#define BOP_DCHECK(cond) do { } while (0)
+#endif
+
 // ---- device helpers -----------------------------------------------------------
 #define BOP_FULL_MASK 0xffffffffu
 #define BOP_INF_BITS_F32 0x7f800000u

@@ -279,6 +279,7 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
   }
   __syncthreads();
   const int roi_y0 = s_plan[0], band_rows = s_plan[1], nb = s_plan[2], nbs = s_plan[3];
+  const float inv_band = 1.0f / (float)band_rows;
   const int nseg = nbs + 1;                 // band segments + the shared segment (unsorted: one segment)
   const int nbins = nseg * kClasses;
   const int4* __restrict__ faces = (const int4*)M.faces4;
@@ -315,7 +316,10 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     unsigned short* const keys = (unsigned short*)(g.stage + out0);
     auto key_of = [&](int cls, int by0, int by1) {
       if (cls == 0 || nbs == 0) return cls;
-      const int b0 = (by0 - roi_y0) / band_rows, b1 = (by1 - roi_y0) / band_rows;
+      // row -> band without an integer division: (y + 0.5) / band_rows is at least 0.5 / 1024 away
+      // from an integer and at most 16, far more than the float error of the product
+      const int b0 = __float2int_rd(((float)(by0 - roi_y0) + 0.5f) * inv_band);
+      const int b1 = __float2int_rd(((float)(by1 - roi_y0) + 0.5f) * inv_band);
       return (b0 == b1 ? b0 : nbs) * kClasses + cls;
     };
     int4 na4 = make_int4(0, 0, 0, 0), nb4 = na4;   // indices of the NEXT iteration (prefetched)
@@ -331,8 +335,15 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (fa < F) { a0 = PV(p, ia.x); a1 = PV(p, ia.y); a2 = PV(p, ia.z); }
       if (fb < F) { b0 = PV(p, ib.x); b1 = PV(p, ib.y); b2 = PV(p, ib.z); }
       int y0a = 0, y1a = 0, y0b = 0, y1b = 0;
-      if (fa < F) { ka = key_of(tri_class(a0, a1, a2, W, H, cull, y0a, y1a), y0a, y1a); keys[fa] = (unsigned short)ka; }
-      if (fb < F) { kb = key_of(tri_class(b0, b1, b2, W, H, cull, y0b, y1b), y0b, y1b); keys[fb] = (unsigned short)kb; }
+      if (fa < F) {
+        BOP_DCHECK((unsigned)ia.x < (unsigned)M.n_pts && (unsigned)ia.y < (unsigned)M.n_pts && (unsigned)ia.z < (unsigned)M.n_pts);
+        ka = key_of(tri_class(a0, a1, a2, W, H, cull, y0a, y1a), y0a, y1a); keys[fa] = (unsigned short)ka;
+      }
+      if (fb < F) {
+        BOP_DCHECK((unsigned)ib.x < (unsigned)M.n_pts && (unsigned)ib.y < (unsigned)M.n_pts && (unsigned)ib.z < (unsigned)M.n_pts);
+        kb = key_of(tri_class(b0, b1, b2, W, H, cull, y0b, y1b), y0b, y1b); keys[fb] = (unsigned short)kb;
+      }
+      BOP_DCHECK(ka >= 0 && ka < nbins && kb >= 0 && kb < nbins);
       const unsigned pa = __match_any_sync(BOP_FULL_MASK, ka), pb = __match_any_sync(BOP_FULL_MASK, kb);
       if (ka && (pa & lt) == 0) atomicAdd(&s_bins[ka], __popc(pa));
       if (kb && (pb & lt) == 0) atomicAdd(&s_bins[kb], __popc(pb));
@@ -389,6 +400,8 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (kb && lane == lb) sb = atomicAdd(&s_bins[kb], __popc(pb));
       sa = __shfl_sync(BOP_FULL_MASK, sa, la) + __popc(pa & lt);
       sb = __shfl_sync(BOP_FULL_MASK, sb, lb) + __popc(pb & lt);
+      BOP_DCHECK(!ka || (sa >= 0 && sa < n_surv));
+      BOP_DCHECK(!kb || (sb >= 0 && sb < n_surv));
       if (ka) {
         const int4 r0 = PV(p, ia.x), r1 = PV(p, ia.y), r2 = PV(p, ia.z);
         g.tri_a[out0 + sa] = make_int4(r0.x, r0.y, r1.x, r1.y);
@@ -738,6 +751,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const int cy0 = sD.y0 + sW.row0, cy1 = cy0 + nrows - 1;
     const int npx = nrows * w;
     const int n_poses = sD.n_poses;
+    BOP_DCHECK(npx <= a.tile_px && nrows <= kMaxBandRows && (w & 3) == 0 && cx0 >= 0 && cy0 >= 0);
     // Clear the z-tiles (0 = nothing drawn; they hold max 1/Z, raster.cuh) and build the x-ray
     // table (misc.py:137: (xs - cx) / fx).
     {
@@ -770,6 +784,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     auto locate = [&](int g, int& p) -> size_t {
       const int sg = (g >= c1 ? 1 : 0) + (g >= c2 ? 1 : 0) + (g >= c3 ? 1 : 0);
       p = sg >> 1;
+      BOP_DCHECK(g >= 0 && g < nT && s_seg0[sg] + (g - s_segc[sg]) < a.tri_cnt[(size_t)sW.pair * n_poses + p]);
       return t_base + (size_t)p * a.tri_cap + (size_t)(s_seg0[sg] + (g - s_segc[sg]));
     };
     // Warps claim 32 consecutive triangles at a time from a shared ticket (triangle cost varies
@@ -816,6 +831,8 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
         if (n != 0) {
           unsigned* const z = zt + (size_t)p * a.tile_px;
+          // the clipped candidate rectangle lies inside this work item's tile
+          BOP_DCHECK(T.bx0 >= cx0 && T.bx1 <= cx1 && T.by0 >= cy0 && T.by1 <= cy1 && (T.by1 - cy0) * w + (T.bx1 - cx0) < a.tile_px);
           if (n > 0 && n <= a.small_tri_px) {
             tri_raster_small(T, z, cx0, cy0, w);
           } else {
@@ -963,6 +980,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
       if (((ze.x | ze.y | ze.z | ze.w) | (zg.x | zg.y | zg.z | zg.w)) == 0u)
         continue;   // no model pixel in this group: depth_test is not even loaded
       const int row = cy0 + r, col = cx0 + 4 * c4;
+      BOP_DCHECK(row >= 0 && row < a.pp.H && col >= 0 && col < a.pp.W);
       float dt[4];
       load_depth4(a.pp, a.depth_test, scale, sD.im, row, col, dt);
       ++n_loaded;

@@ -309,9 +309,9 @@ def _vsd_case(B, n, seed, H=480, W=640, scale=1.0, n_lat=50, n_lon=100):
 
 
 def test_vsd_fused_vs_oracle_full_size(B, oracle_built):
-  """configs[1] shape (640x480, delta 15, taus .05-.5, step), 10 pairs against the oracle."""
+  """configs[1] shape (640x480, delta 15, taus .05-.5, step), 64 pairs against the oracle."""
   from oracle import pose_error_oracle as po
-  n = 10
+  n = 64
   K, pts, faces, R_e, t_e, R_g, t_g, depth, ren = _vsd_case(B, n, seed=30)
   ms = B.ModelSet()
   ms.add(1, pts, faces, None, 200.0)
@@ -437,15 +437,17 @@ def test_c_abi_host_entry_points(B, golden):
 
 
 def test_dense_model_adi_add(B):
-  """configs[3] shape, reduced: 20k-vertex model (ADI is N^2), a few pairs, 64 symmetries."""
+  """configs[3] at full size: a 99,906-vertex model (ADI = 10^10 distances per pair), 64
+  symmetries, three pairs against the oracle (cKDTree ADI, numpy MSSD / MSPD / ADD)."""
   from bop_toolkit_b200 import synth
   from oracle import pose_error_oracle as po
-  pts, faces = synth.make_dense_mesh(20000, 250.0, seed=6)
+  pts, faces = synth.make_dense_mesh(100000, 250.0, seed=6)
+  assert len(pts) > 99000
   syms = po.get_symmetry_transformations({'symmetries_discrete': synth.discrete_z_symmetries(64)}, 0.01)
   assert len(syms) == 64
   ms = B.ModelSet()
   ms.add(1, pts, faces, syms, 250.0)
-  n = 4
+  n = 3
   R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=7, outlier_frac=0.0)
   pe, pg = _poses(B, R_e, t_e), _poses(B, R_g, t_g)
   col = lambda t: t.reshape(3, 1)
