@@ -106,6 +106,8 @@ _SIGNATURES = {
                                    ctypes.c_size_t, _P]),
   'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
                        _P]),
+  'bop_vsd_grouped_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P,
+                               ctypes.c_size_t, _P]),
   'bop_mask_overlap_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P,
                                 ctypes.c_size_t, _P]),
   'bop_mask_stats_workspace_bytes': (ctypes.c_size_t, [_I]),

@@ -389,10 +389,46 @@ def _tau_chunks(taus):
   return [taus[i:i + _lib.BOP_MAX_TAUS] for i in range(0, len(taus), _lib.BOP_MAX_TAUS)]
 
 
+MAX_GROUP = 32   # kMaxGroup in csrc/vsd.cu
+
+
+def group_pairs_by_gt(obj, pose_gt, im_idx, diameter=None):
+  """Pairs that share (object, image, GT pose[, diameter]) -- the k estimates
+  scripts/eval_calc_errors.py:281-289 pairs with one GT pose.  Host arrays in, -> (order, group_off):
+  `order` sorts the pairs so that groups are consecutive (stable: original order inside a group),
+  `group_off` (int32 [n_groups + 1]) cuts the sorted pairs into groups of at most MAX_GROUP, the
+  layout vsd_batch(group_off=...) / bop_vsd_grouped_dev take."""
+  obj = np.asarray(obj).reshape(-1)
+  n = obj.shape[0]
+  pg = np.ascontiguousarray(np.asarray(pose_gt, dtype=np.float64).reshape(n, 12))
+  cols = [pg.view(np.int64).reshape(n, 12), obj.astype(np.int64).reshape(n, 1),
+          np.asarray(im_idx).astype(np.int64).reshape(n, 1)]
+  if diameter is not None:
+    cols.append(np.ascontiguousarray(np.broadcast_to(np.asarray(diameter, np.float64), (n,))).view(np.int64).reshape(n, 1))
+  key = np.ascontiguousarray(np.hstack(cols))
+  _, inv = np.unique(key.view([('', key.dtype)] * key.shape[1]).reshape(n), return_inverse=True)
+  inv = inv.reshape(-1)
+  order = np.argsort(inv, kind='stable')
+  sizes = np.bincount(inv)
+  off = [0]
+  for k in sizes:          # groups above MAX_GROUP are cut
+    k = int(k)
+    while k > 0:
+      step = min(k, MAX_GROUP)
+      off.append(off[-1] + step)
+      k -= step
+  return order, np.asarray(off, dtype=np.int32)
+
+
 def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus,
               normalized_by_diameter=True, cost_type='step', visib_mode='bop19', gate=False,
-              depth_scale=None, return_counts=False, diameter_override=None, zero_copy=False):
+              depth_scale=None, return_counts=False, diameter_override=None, zero_copy=False,
+              group_off=None):
   """pose_error.vsd for P pairs with the fused raster + pixel-pass kernel.
+
+  group_off (host int32 [G + 1], from group_pairs_by_gt): consecutive pairs of a group share
+  object, image, GT pose and diameter; the GT pose's geometry and raster work is then done once
+  per group (bit-identical results).
 
   depth_test: [n_im,H,W] float32 mm (or uint16 raw + depth_scale[n_im]); im_idx: [P] image of
   each pair (None = pair i uses image i); K: [n_im,9].  Returns errors [P,len(taus)] float64
@@ -441,12 +477,21 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
                             gate, code)
       err = torch.empty((n, len(chunk)), dtype=torch.float64, device=dev)
       cnt = torch.empty((n, 2 + len(chunk)), dtype=torch.int64, device=dev) if return_counts else None
-      rc = _lib.lib().bop_vsd_dev(
-        models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
-        sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
-        diam.data_ptr() if diam is not None else None, n, models.max_geom,
-        ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
-        ws.data_ptr(), wsb, _stream_ptr())
+      if group_off is not None:
+        goff = np.ascontiguousarray(group_off, dtype=np.int32)
+        rc = _lib.lib().bop_vsd_grouped_dev(
+          models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
+          sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
+          diam.data_ptr() if diam is not None else None, n, goff.ctypes.data, int(goff.shape[0]) - 1,
+          models.max_geom, ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
+          ws.data_ptr(), wsb, _stream_ptr())
+      else:
+        rc = _lib.lib().bop_vsd_dev(
+          models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
+          sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
+          diam.data_ptr() if diam is not None else None, n, models.max_geom,
+          ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
+          ws.data_ptr(), wsb, _stream_ptr())
       _lib.check(rc)
       outs.append(err)
       cnts.append(cnt)

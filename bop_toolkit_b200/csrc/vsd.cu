@@ -17,6 +17,7 @@
 #include <limits.h>
 #include <stddef.h>
 #include <type_traits>
+#include <vector>
 
 #include "raster.cuh"
 
@@ -34,14 +35,21 @@ struct Tuning {
 };
 Tuning g_tune;
 
+// Pairs that share their GT pose (same object, image, GT pose: the k estimates eval_calc_errors.py
+// :281-289 pairs with one GT) form a GROUP: the GT pose is projected, sorted and rasterised once
+// per group and row band, its z-tile stays in shared memory while the estimates take turns.
+constexpr int kMaxGroup = 32;
+
 struct PairDesc {
-  PoseCamF pose[2];       // 0 = est, 1 = gt
   double kfx, kfy, kcx, kcy;
   double diameter;
-  int x0, y0, w, h;       // union ROI; x0 and w are multiples of 4
+  int x0, y0, w, h;       // ROI of the pair's group (GT pose + every active estimate); x0 and w are multiples of 4
   int obj, im;
   int n_poses;
   int nbs;                // row bands the triangle lists are sorted by (0: not sorted by band)
+  int group_n;            // pairs in the group (meaningful in the group's first pair)
+  int active;             // 0: the pair failed the sphere gate: no work, its counts stay 0
+  int pad0, pad1;
 };
 
 struct WorkItem {
@@ -133,6 +141,7 @@ struct GeomArgs {
   const int32_t* im_idx;
   const double* K;
   const double* diameters;
+  const int32_t* group_off;   // [n_groups + 1] first pair of every group (pairs of a group are consecutive); NULL: every item is its own group
   int cam_mode, n_poses, H, W, gate, tile_px;
   int pv_stride, tri_cap;
   PVert* pv_global;
@@ -152,48 +161,56 @@ struct GeomArgs {
 __global__ void __launch_bounds__(kAsmThreads, 2)
 geometry_kernel(const __grid_constant__ GeomArgs g) {
   extern __shared__ int4 s_dyn[];   // [n_pv] projected vertices (smem path), then [kMaxBins] ints
-  __shared__ int s_box[2][4];
+  __shared__ int s_box[4];          // union of the projected boxes of the group's active poses
   __shared__ int s_n;
   __shared__ int s_plan[4];         // y0, band rows, nb, nbs (bands the lists are sorted by; 0 = unsorted)
   __shared__ int s_wsum[kAsmThreads / 32];
-  const int item = blockIdx.x;
+  __shared__ int s_act[kMaxGroup];  // estimate q of the group passed the sphere gate
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n_poses = g.n_poses, W = g.W, H = g.H;
-  const bop_model_dev M = g.models[g.obj_idx[item]];
+  // The group: pairs first .. first + cnt - 1 share object, image and GT pose.  Its poses: q < cnt is
+  // the estimate of pair first + q (or, for single-pose work, THE pose); q == cnt is the GT pose.
+  const int first = g.group_off ? g.group_off[blockIdx.x] : (int)blockIdx.x;
+  const int cnt = g.group_off ? g.group_off[blockIdx.x + 1] - first : 1;
+  if (cnt < 1 || cnt > kMaxGroup) __trap();
+  const int Q = n_poses == 2 ? cnt + 1 : 1;
+  const bop_model_dev M = g.models[g.obj_idx[first]];
   const bool smem_pv = M.n_pts <= kSmemVerts;
   int4* const s_pv = s_dyn;
   int* const s_bins = (int*)(s_dyn + (smem_pv ? min(g.pv_stride, kSmemVerts) : 0));
-  const double* pose[2] = {g.pose_a + 12 * (size_t)item, g.pose_b + 12 * (size_t)item};
-  const double diam = g.diameters ? g.diameters[item] : M.diameter;
+  auto pose_of = [&](int q) { return (n_poses == 2 && q == cnt) ? g.pose_b + 12 * (size_t)first : g.pose_a + 12 * (size_t)(first + q); };
+  auto slot_of = [&](int q) { return n_poses == 2 ? (q == cnt ? first * 2 + 1 : (first + q) * 2) : first; };
+  const double diam = g.diameters ? g.diameters[first] : M.diameter;
   double fx, fy, cx, cy;
   int im;
   if (g.cam_mode == 0) {
-    im = g.im_idx[item];
+    im = g.im_idx[first];
     const double* Kp = g.K + 9 * (size_t)im;
     fx = Kp[0]; fy = Kp[4]; cx = Kp[2]; cy = Kp[5];
   } else {
-    im = item;
-    const double* c = g.K + 4 * (size_t)item;
+    im = first;
+    const double* c = g.K + 4 * (size_t)first;
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
   if (M.n_pts > g.pv_stride || M.n_faces > g.tri_cap) __trap();   // max_geom below the model's size: fail loudly
-  bool gated = false;
-  if (g.gate && n_poses == 2)   // uniform over the CTA
-    gated = !sphere_projections_overlap(0.5 * diam, pose[0] + 9, pose[1] + 9);
-  if (tid < 8) (&s_box[0][0])[tid] = (tid & 2) ? INT_MIN : INT_MAX;
+  if (tid < cnt)
+    s_act[tid] = (g.gate && n_poses == 2) ? (sphere_projections_overlap(0.5 * diam, pose_of(tid) + 9, pose_of(cnt) + 9) ? 1 : 0) : 1;
+  if (tid < 4) s_box[tid] = (tid & 2) ? INT_MIN : INT_MAX;
   __syncthreads();
+  bool any_active = false;
+  for (int q = 0; q < cnt; ++q) any_active = any_active || s_act[q];
   const float4* __restrict__ verts = (const float4*)M.verts4;
   // The projected-vertex records are addressed through a compile-time switch so that the common
   // case compiles to shared-memory loads / stores (LDS / STS) instead of generic ones.
-#define PV(p, i) (*(SMEM ? &s_pv[i] : &gpv[(size_t)(p) * g.pv_stride + (i)]))
+#define PV(i) (*(SMEM ? &s_pv[i] : &gpv[i]))
   auto body = [&](auto smem_tag) {
   constexpr bool SMEM = decltype(smem_tag)::value;
-  int4* const gpv = (int4*)(g.pv_global + (size_t)item * n_poses * g.pv_stride);
-  // Projects every vertex of pose p; keep: store the records (always on the global path, where
-  // both poses have their own scratch).
-  auto project_pose = [&](int p, bool keep, bool want_box) {
+  int4* gpv = nullptr;   // global path: the records of the pose at hand (every list has its own scratch)
+  // Projects every vertex of pose q; keep: store the records; want_box: reduce the projected box.
+  auto project_pose = [&](int q, bool keep, bool want_box) {
     PoseCamF P;
-    make_posecam(pose[p], fx, fy, cx + g.cx_off, cy + g.cy_off, P);
+    make_posecam(pose_of(q), fx, fy, cx + g.cx_off, cy + g.cy_off, P);
+    gpv = (int4*)(g.pv_global + (size_t)slot_of(q) * g.pv_stride);
     int minx = INT_MAX, miny = INT_MAX, maxx = INT_MIN, maxy = INT_MIN;
     for (int i0 = tid; i0 < M.n_pts; i0 += 4 * kAsmThreads) {
       float4 vin[4];   // four loads in flight before the first store
@@ -207,7 +224,7 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
         const int i = i0 + k * kAsmThreads;
         if (i < M.n_pts) {
           const PVert v = project_vertex(P, vin[k]);
-          if (keep) PV(p, i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
+          if (keep) PV(i) = make_int4(v.x, v.y, __float_as_int(v.iz), v.valid);
           if (v.valid) {
             minx = min(minx, v.x); maxx = max(maxx, v.x);
             miny = min(miny, v.y); maxy = max(maxy, v.y);
@@ -219,59 +236,44 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       minx = __reduce_min_sync(BOP_FULL_MASK, minx); miny = __reduce_min_sync(BOP_FULL_MASK, miny);
       maxx = __reduce_max_sync(BOP_FULL_MASK, maxx); maxy = __reduce_max_sync(BOP_FULL_MASK, maxy);
       if (lane == 0 && maxx >= minx) {
-        atomicMin(&s_box[p][0], minx); atomicMin(&s_box[p][1], miny);
-        atomicMax(&s_box[p][2], maxx); atomicMax(&s_box[p][3], maxy);
+        atomicMin(&s_box[0], minx); atomicMin(&s_box[1], miny);
+        atomicMax(&s_box[2], maxx); atomicMax(&s_box[3], maxy);
       }
     }
   };
-  if (!gated) {
-    project_pose(0, true, true);
-    if (n_poses == 2) project_pose(1, !SMEM, true);
-  }
+  // Boxes of every active pose; the LAST pose (the GT pose, or the single pose) keeps its records
+  // in shared memory for the assembly that follows (the global path keeps them all).
+  if (any_active)
+    for (int q = 0; q < Q; ++q)
+      if (q == Q - 1 || s_act[q]) project_pose(q, q == Q - 1 || !SMEM, true);
   __syncthreads();
-  // ---- plan (thread 0): descriptor, union ROI, row bands, work items -------------------------
+  // ---- plan (thread 0): ROI of the group, row bands, work items -------------------------------
   if (tid == 0) {
-    PairDesc D;
-    D.obj = g.obj_idx[item];
-    D.im = im;
-    D.diameter = diam;
-    D.n_poses = n_poses;
-    D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
-    make_posecam(pose[0], fx, fy, cx + g.cx_off, cy + g.cy_off, D.pose[0]);
-    if (n_poses == 2) make_posecam(pose[1], fx, fy, cx + g.cx_off, cy + g.cy_off, D.pose[1]);
-    else D.pose[1] = D.pose[0];
-    int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
-    for (int p = 0; p < n_poses; ++p) {
-      if (s_box[p][2] < s_box[p][0]) continue;
-      const int bx0 = max(0, (s_box[p][0] + kSubOne - 1) >> kSubBits), by0 = max(0, (s_box[p][1] + kSubOne - 1) >> kSubBits);
-      const int bx1 = min(W - 1, s_box[p][2] >> kSubBits), by1 = min(H - 1, s_box[p][3] >> kSubBits);
-      if (bx1 < bx0 || by1 < by0) continue;
-      x0 = min(x0, bx0); y0 = min(y0, by0); x1 = max(x1, bx1); y1 = max(y1, by1);
-    }
-    int nb = 0, band = 1;
-    if (x1 >= x0) {
-      x0 &= ~3;
-      const int w = ((x1 + 1 - x0) + 3) & ~3;
-      const int h = y1 + 1 - y0;
-      D.x0 = x0; D.y0 = y0; D.w = w; D.h = h;
-      const int cap_rows = min(kMaxBandRows, max(1, g.tile_px / w));
-      nb = (h + cap_rows - 1) / cap_rows;
-      band = (h + nb - 1) / nb;  // balanced bands
-    } else {
-      D.x0 = D.y0 = D.w = D.h = 0; y0 = 0;
+    int x0 = 0, y0 = 0, w = 0, h = 0, nb = 0, band = 1;
+    if (s_box[2] >= s_box[0]) {
+      const int bx0 = max(0, (s_box[0] + kSubOne - 1) >> kSubBits), by0 = max(0, (s_box[1] + kSubOne - 1) >> kSubBits);
+      const int bx1 = min(W - 1, s_box[2] >> kSubBits), by1 = min(H - 1, s_box[3] >> kSubBits);
+      if (bx1 >= bx0 && by1 >= by0) {
+        x0 = bx0 & ~3;
+        w = ((bx1 + 1 - x0) + 3) & ~3;
+        y0 = by0;
+        h = by1 + 1 - by0;
+        const int cap_rows = min(kMaxBandRows, max(1, g.tile_px / w));
+        nb = (h + cap_rows - 1) / cap_rows;
+        band = (h + nb - 1) / nb;  // balanced bands
+      }
     }
     const int nbs = (nb >= 2 && nb <= kMaxSortBands) ? nb : 0;
-    D.nbs = nbs;
-    g.desc[item] = D;
+    s_box[0] = x0; s_box[1] = w; s_box[2] = h;   // (the box is consumed: reuse it to hand the ROI to the descriptor writers)
     s_plan[0] = y0; s_plan[1] = band; s_plan[2] = nb; s_plan[3] = nbs;
     if (nb > 0) {
       const unsigned start = atomicAdd(&g.ctr->total, (unsigned)nb);
       for (int b = 0; b < nb; ++b) {
         if (start + b >= g.max_items) break;  // cannot happen with the documented workspace size
         WorkItem wi;
-        wi.pair = item;
+        wi.pair = first;
         wi.row0 = b * band;
-        wi.nrows = min(band, D.h - b * band);
+        wi.nrows = min(band, h - b * band);
         wi.band = b;
         g.work[start + b] = wi;
       }
@@ -279,24 +281,42 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
   }
   __syncthreads();
   const int roi_y0 = s_plan[0], band_rows = s_plan[1], nb = s_plan[2], nbs = s_plan[3];
+  if (tid < cnt) {   // one descriptor per pair of the group
+    PairDesc D;
+    D.kfx = fx; D.kfy = fy; D.kcx = cx; D.kcy = cy;
+    D.diameter = diam;
+    D.x0 = s_box[0]; D.y0 = roi_y0; D.w = s_box[1]; D.h = s_box[2];
+    D.obj = g.obj_idx[first]; D.im = im;
+    D.n_poses = n_poses; D.nbs = nbs;
+    D.group_n = tid == 0 ? cnt : 0;
+    D.active = s_act[tid];
+    D.pad0 = D.pad1 = 0;
+    g.desc[first + tid] = D;
+  }
   const float inv_band = 1.0f / (float)band_rows;
   const int nseg = nbs + 1;                 // band segments + the shared segment (unsorted: one segment)
   const int nbins = nseg * kClasses;
   const int4* __restrict__ faces = (const int4*)M.faces4;
   const int F = M.n_faces;
   const unsigned lt = (1u << lane) - 1u;
-  for (int p = 0; p < n_poses; ++p) {
-    const int gw = item * n_poses + p;
+  // Assembly: the last pose first (its records are in shared memory already), then the estimates.
+  bool have_records = true;
+  for (int qq = 0; qq < Q; ++qq) {
+    const int q = qq == 0 ? Q - 1 : qq - 1;
+    const int gw = slot_of(q);
     int* const boff = g.band_off + (size_t)gw * kBandOffN;
-    if (nb == 0) {   // gated, or nothing inside the image
+    if (nb == 0 || (q < Q - 1 && !s_act[q])) {   // gated, or nothing inside the image
       if (tid == 0) g.tri_cnt[gw] = 0;
       if (tid < kBandOffN) boff[tid] = 0;
       continue;
     }
-    if (p > 0) {
-      __syncthreads();   // the scatter of pose p - 1 has finished with the records and the cursors
-      if (SMEM) project_pose(p, true, false);
+    __syncthreads();   // the scatter of the previous pose has finished with the records and the cursors
+    if (!have_records) {
+      if (SMEM) project_pose(q, true, false);
+      else gpv = (int4*)(g.pv_global + (size_t)gw * g.pv_stride);
     }
+    have_records = false;
+    const double* const pose_q = pose_of(q);
     for (int i = tid; i < nbins; i += kAsmThreads) s_bins[i] = 0;
     if (tid == 0) s_n = 0;
     __syncthreads();
@@ -305,7 +325,7 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     int cull = M.cull;
     if (cull) {
       const double r = (double)M.cull_min_dist;
-      const double* t = pose[p] + 9;
+      const double* t = pose_q + 9;
       if (!(t[0] * t[0] + t[1] * t[1] + t[2] * t[2] > r * r)) cull = 0;
     }
     const size_t out0 = (size_t)gw * g.tri_cap;
@@ -332,8 +352,8 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       if (fb + 2 * kAsmThreads < F) nb4 = __ldg(faces + fb + 2 * kAsmThreads);
       int ka = 0, kb = 0;
       int4 a0, a1, a2, b0, b1, b2;
-      if (fa < F) { a0 = PV(p, ia.x); a1 = PV(p, ia.y); a2 = PV(p, ia.z); }
-      if (fb < F) { b0 = PV(p, ib.x); b1 = PV(p, ib.y); b2 = PV(p, ib.z); }
+      if (fa < F) { a0 = PV(ia.x); a1 = PV(ia.y); a2 = PV(ia.z); }
+      if (fb < F) { b0 = PV(ib.x); b1 = PV(ib.y); b2 = PV(ib.z); }
       int y0a = 0, y1a = 0, y0b = 0, y1b = 0;
       if (fa < F) {
         BOP_DCHECK((unsigned)ia.x < (unsigned)M.n_pts && (unsigned)ia.y < (unsigned)M.n_pts && (unsigned)ia.z < (unsigned)M.n_pts);
@@ -403,13 +423,13 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
       BOP_DCHECK(!ka || (sa >= 0 && sa < n_surv));
       BOP_DCHECK(!kb || (sb >= 0 && sb < n_surv));
       if (ka) {
-        const int4 r0 = PV(p, ia.x), r1 = PV(p, ia.y), r2 = PV(p, ia.z);
+        const int4 r0 = PV(ia.x), r1 = PV(ia.y), r2 = PV(ia.z);
         g.tri_a[out0 + sa] = make_int4(r0.x, r0.y, r1.x, r1.y);
         g.tri_b[out0 + sa] = make_int4(r2.x, r2.y, r0.z, r1.z);
         g.tri_c[out0 + sa] = __int_as_float(r2.z);
       }
       if (kb) {
-        const int4 r0 = PV(p, ib.x), r1 = PV(p, ib.y), r2 = PV(p, ib.z);
+        const int4 r0 = PV(ib.x), r1 = PV(ib.y), r2 = PV(ib.z);
         g.tri_a[out0 + sb] = make_int4(r0.x, r0.y, r1.x, r1.y);
         g.tri_b[out0 + sb] = make_int4(r2.x, r2.y, r0.z, r1.z);
         g.tri_c[out0 + sb] = __int_as_float(r2.z);
@@ -701,6 +721,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
   // pose 1 (geometry_kernel), addressed as one virtual index range.
   __shared__ int s_seg0[4];   // first list entry of each segment
   __shared__ int s_segc[5];   // virtual index where each segment starts; [4] = total
+  __shared__ int s_slot[4];   // list (pair * n_poses + pose) each segment belongs to
   __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS + 1];
   __shared__ double s_sum[BOP_MAX_TAUS];
   __shared__ float s_tau[BOP_MAX_TAUS + 2];
@@ -723,26 +744,34 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     if (tid < BOP_MAX_TAUS) s_sum[tid] = 0.0;
     __syncthreads();
     if (s_ticket >= total) break;
+    // Segment table of a raster phase: the band's segment and the shared segment of the estimate's
+    // list of pair `pe` (tile 0), then of the GT list of pair `pg` (tile 1); -1 = not in this phase.
+    auto set_segments = [&](int pe, int pg, int np, int nbs) {
+      int c = 0;
+      for (int sg = 0; sg < 4; ++sg) {
+        const int p = sg >> 1;
+        const int pair = p == 0 ? pe : pg;
+        int lo = 0, hi = 0, slot = 0;
+        if (pair >= 0 && p < np) {
+          slot = pair * np + p;
+          const int* off = a.band_off + (size_t)slot * kBandOffN;
+          if (nbs == 0) { if (!(sg & 1)) { lo = off[0]; hi = off[1]; } }
+          else if (sg & 1) { lo = off[nbs]; hi = off[nbs + 1]; }
+          else { lo = off[sW.band]; hi = off[sW.band + 1]; }
+        }
+        s_seg0[sg] = lo; s_segc[sg] = c; s_slot[sg] = slot; c += hi - lo;
+      }
+      s_segc[4] = c;
+    };
     {
-      // Cooperative copy of the pair descriptor (word-wise).
+      // Cooperative copy of the descriptor of the group's first pair (word-wise).
       const int* src = (const int*)(a.desc + sW.pair);
       int* dst = (int*)&sD;
       for (int i = tid; i < (int)(sizeof(PairDesc) / 4); i += nthr) dst[i] = src[i];
-      if (tid == nthr - 1) {   // segment table (n_poses is 1 or 2)
+      if (tid == nthr - 1) {
         const int np = src[offsetof(PairDesc, n_poses) / 4], nbs = src[offsetof(PairDesc, nbs) / 4];
-        int c = 0;
-        for (int sg = 0; sg < 4; ++sg) {
-          const int p = sg >> 1;
-          int lo = 0, hi = 0;
-          if (p < np) {
-            const int* off = a.band_off + ((size_t)sW.pair * np + p) * kBandOffN;
-            if (nbs == 0) { if (!(sg & 1)) { lo = off[0]; hi = off[1]; } }
-            else if (sg & 1) { lo = off[nbs]; hi = off[nbs + 1]; }
-            else { lo = off[sW.band]; hi = off[sW.band + 1]; }
-          }
-          s_seg0[sg] = lo; s_segc[sg] = c; c += hi - lo;
-        }
-        s_segc[4] = c;
+        const int gn = src[offsetof(PairDesc, group_n) / 4];
+        set_segments(gn > 1 ? -1 : sW.pair, sW.pair, np, nbs);   // a group rasterises its GT pose first, alone
       }
     }
     __syncthreads();
@@ -751,12 +780,13 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const int cy0 = sD.y0 + sW.row0, cy1 = cy0 + nrows - 1;
     const int npx = nrows * w;
     const int n_poses = sD.n_poses;
+    const int n_grp = sD.group_n > 1 ? sD.group_n : 1;
     BOP_DCHECK(npx <= a.tile_px && nrows <= kMaxBandRows && (w & 3) == 0 && cx0 >= 0 && cy0 >= 0);
     // Clear the z-tiles (0 = nothing drawn; they hold max 1/Z, raster.cuh) and build the x-ray
     // table (misc.py:137: (xs - cx) / fx).
     {
       const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
-      for (int p = 0; p < n_poses; ++p) {
+      for (int p = (n_grp > 1 ? 1 : 0); p < n_poses; ++p) {   // a group clears the estimate's tile per estimate
         uint4* z4 = (uint4*)(zt + (size_t)p * a.tile_px);
         for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = zero4;
       }
@@ -775,104 +805,126 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     }
     __syncthreads();
 
-    // One loop over the assembled triangles of BOTH poses (they draw into different z-tiles, so
-    // no barrier is needed between them).  Triangles with many candidate pixels are deferred to
-    // a queue and drawn warp-cooperatively afterwards.
-    const size_t t_base = (size_t)sW.pair * n_poses * a.tri_cap;
-    const int c1 = s_segc[1], c2 = s_segc[2], c3 = s_segc[3], nT = s_segc[4];
-    // virtual index -> (pose, list entry)
-    auto locate = [&](int g, int& p) -> size_t {
-      const int sg = (g >= c1 ? 1 : 0) + (g >= c2 ? 1 : 0) + (g >= c3 ? 1 : 0);
-      p = sg >> 1;
-      BOP_DCHECK(g >= 0 && g < nT && s_seg0[sg] + (g - s_segc[sg]) < a.tri_cnt[(size_t)sW.pair * n_poses + p]);
-      return t_base + (size_t)p * a.tri_cap + (size_t)(s_seg0[sg] + (g - s_segc[sg]));
-    };
-    // Warps claim 32 consecutive triangles at a time from a shared ticket (triangle cost varies
-    // by class; static striding would leave warps idle at the barrier).  The records of the NEXT
-    // batch are fetched by cp.async into a per-warp staging area (every lane copies and later
-    // reads its own 36 bytes) while the current batch is rasterised, so the L2 / HBM latency of
-    // the list is hidden without spending registers on it.
-    auto ticket = [&]() {
-      int b = 0;
-      if (lane == 0) b = atomicAdd(&s_next, 32);
-      return __shfl_sync(BOP_FULL_MASK, b, 0);
-    };
-    int4* const pre_a = prefetch + (size_t)warp * 64 + lane;   // [warp][2][32] int4, then [warp][32] float
-    int4* const pre_b = pre_a + 32;
-    float* const pre_c = (float*)(prefetch + (size_t)nwarps * 64) + warp * 32 + lane;
-    const unsigned sa = smem_addr(pre_a), sb = smem_addr(pre_b), sc = smem_addr(pre_c);
-    int pose_next = 0;
-    auto fetch = [&](int base) {
-      const int g = base + lane;
-      if (g < nT) {
-        const size_t ti = locate(g, pose_next);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(a.tri_a + ti) : "memory");
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sb), "l"(a.tri_b + ti) : "memory");
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sc), "l"(a.tri_c + ti) : "memory");
-      }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    int base = ticket();
-    if (base < nT) fetch(base);
-    while (base < nT) {
-      const int next = ticket();
-      const int g = base + lane;
-      const int p = pose_next;
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      const int4 ra = *pre_a, rb = *pre_b;
-      const float rc = *pre_c;
-      if (next < nT) fetch(next);   // the staging area is free again: this lane has its record in registers
-      base = next;
-      if (g < nT) {
-        const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
-        const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
-        const PVert v2 = {rb.x, rb.y, rc, 1};
-        TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
-        if (n != 0) {
-          unsigned* const z = zt + (size_t)p * a.tile_px;
-          // the clipped candidate rectangle lies inside this work item's tile
-          BOP_DCHECK(T.bx0 >= cx0 && T.bx1 <= cx1 && T.by0 >= cy0 && T.by1 <= cy1 && (T.by1 - cy0) * w + (T.bx1 - cx0) < a.tile_px);
-          if (n > 0 && n <= a.small_tri_px) {
-            tri_raster_small(T, z, cx0, cy0, w);
-          } else {
-            const int slot = atomicAdd(&s_q, 1);
-            if (slot < kQueueCap) {
-              queue[slot] = g;
-            } else if (n > 0) {   // queue full: draw it here (slow but correct)
+    // A raster phase: every triangle of the current segment table into the z-tiles.  Ends with all
+    // warps past the barrier behind the deferred queue.
+    auto raster_phase = [&]() {
+      // One loop over the assembled triangles of BOTH poses (they draw into different z-tiles, so
+      // no barrier is needed between them).  Triangles with many candidate pixels are deferred to
+      // a queue and drawn warp-cooperatively afterwards.
+      const int c1 = s_segc[1], c2 = s_segc[2], c3 = s_segc[3], nT = s_segc[4];
+      // virtual index -> (pose, list entry)
+      auto locate = [&](int g, int& p) -> size_t {
+        const int sg = (g >= c1 ? 1 : 0) + (g >= c2 ? 1 : 0) + (g >= c3 ? 1 : 0);
+        p = sg >> 1;
+        BOP_DCHECK(g >= 0 && g < nT && s_seg0[sg] + (g - s_segc[sg]) < a.tri_cnt[s_slot[sg]]);
+        return (size_t)s_slot[sg] * a.tri_cap + (size_t)(s_seg0[sg] + (g - s_segc[sg]));
+      };
+      // Warps claim 32 consecutive triangles at a time from a shared ticket (triangle cost varies
+      // by class; static striding would leave warps idle at the barrier).  The records of the NEXT
+      // batch are fetched by cp.async into a per-warp staging area (every lane copies and later
+      // reads its own 36 bytes) while the current batch is rasterised, so the L2 / HBM latency of
+      // the list is hidden without spending registers on it.
+      auto ticket = [&]() {
+        int b = 0;
+        if (lane == 0) b = atomicAdd(&s_next, 32);
+        return __shfl_sync(BOP_FULL_MASK, b, 0);
+      };
+      int4* const pre_a = prefetch + (size_t)warp * 64 + lane;   // [warp][2][32] int4, then [warp][32] float
+      int4* const pre_b = pre_a + 32;
+      float* const pre_c = (float*)(prefetch + (size_t)nwarps * 64) + warp * 32 + lane;
+      const unsigned sa = smem_addr(pre_a), sb = smem_addr(pre_b), sc = smem_addr(pre_c);
+      int pose_next = 0;
+      auto fetch = [&](int base) {
+        const int g = base + lane;
+        if (g < nT) {
+          const size_t ti = locate(g, pose_next);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(a.tri_a + ti) : "memory");
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sb), "l"(a.tri_b + ti) : "memory");
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(sc), "l"(a.tri_c + ti) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      };
+      int base = ticket();
+      if (base < nT) fetch(base);
+      while (base < nT) {
+        const int next = ticket();
+        const int g = base + lane;
+        const int p = pose_next;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        const int4 ra = *pre_a, rb = *pre_b;
+        const float rc = *pre_c;
+        if (next < nT) fetch(next);   // the staging area is free again: this lane has its record in registers
+        base = next;
+        if (g < nT) {
+          const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
+          const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
+          const PVert v2 = {rb.x, rb.y, rc, 1};
+          TriSetup T;
+          const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+          if (n != 0) {
+            unsigned* const z = zt + (size_t)p * a.tile_px;
+            // the clipped candidate rectangle lies inside this work item's tile
+            BOP_DCHECK(T.bx0 >= cx0 && T.bx1 <= cx1 && T.by0 >= cy0 && T.by1 <= cy1 && (T.by1 - cy0) * w + (T.bx1 - cx0) < a.tile_px);
+            if (n > 0 && n <= a.small_tri_px) {
               tri_raster_small(T, z, cx0, cy0, w);
             } else {
-              TriSetup64 T64;
-              if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+              const int slot = atomicAdd(&s_q, 1);
+              if (slot < kQueueCap) {
+                queue[slot] = g;
+              } else if (n > 0) {   // queue full: draw it here (slow but correct)
+                tri_raster_small(T, z, cx0, cy0, w);
+              } else {
+                TriSetup64 T64;
+                if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, 0, 1, z, cx0, cy0, w);
+              }
             }
           }
         }
       }
-    }
-    __syncthreads();
-    {
-      const int nq = min(s_q, kQueueCap);
-      for (int qi = warp; qi < nq; qi += nwarps) {
-        const int g = queue[qi];
-        int p;
-        const size_t ti = locate(g, p);
-        const int4 ra = __ldg(a.tri_a + ti), rb = __ldg(a.tri_b + ti);
-        const float rc = __ldg(a.tri_c + ti);
-        const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
-        const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
-        const PVert v2 = {rb.x, rb.y, rc, 1};
-        unsigned* const z = zt + (size_t)p * a.tile_px;
-        TriSetup T;
-        const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
-        if (n > 0) {
-          tri_raster_warp(T, lane, z, cx0, cy0, w);
-        } else if (n < 0) {
-          TriSetup64 T64;
-          if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
+      __syncthreads();
+      {
+        const int nq = min(s_q, kQueueCap);
+        for (int qi = warp; qi < nq; qi += nwarps) {
+          const int g = queue[qi];
+          int p;
+          const size_t ti = locate(g, p);
+          const int4 ra = __ldg(a.tri_a + ti), rb = __ldg(a.tri_b + ti);
+          const float rc = __ldg(a.tri_c + ti);
+          const PVert v0 = {ra.x, ra.y, __int_as_float(rb.z), 1};
+          const PVert v1 = {ra.z, ra.w, __int_as_float(rb.w), 1};
+          const PVert v2 = {rb.x, rb.y, rc, 1};
+          unsigned* const z = zt + (size_t)p * a.tile_px;
+          TriSetup T;
+          const int n = tri_setup(v0, v1, v2, cx0, cy0, cx1, cy1, T);
+          if (n > 0) {
+            tri_raster_warp(T, lane, z, cx0, cy0, w);
+          } else if (n < 0) {
+            TriSetup64 T64;
+            if (tri_setup64(v0, v1, v2, T, T64)) tri_raster_large(T64, lane, 32, z, cx0, cy0, w);
+          }
         }
       }
+      __syncthreads();
+
+    };
+    // Phases of a work item.  A single pair: one raster phase (both poses) and its pixel pass.
+    // A group: phase -1 rasterises the GT pose into tile 1, then every active estimate in turn is
+    // rasterised into tile 0 and scored against it.
+    for (int j = (n_grp == 1 ? 0 : -1); j < n_grp; ++j) {
+    const int pair = sW.pair + (j > 0 ? j : 0);
+    if (n_grp > 1 && j >= 0) {
+      if (!a.desc[pair].active) continue;   // uniform over the CTA
+      __syncthreads();                      // the previous estimate's pixel pass is done with tile 0 and the counters
+      if (tid == 0) { s_q = 0; s_next = 0; set_segments(pair, -1, n_poses, sD.nbs); }
+      if (tid < 2 + BOP_MAX_TAUS + 1) s_cnt[tid] = 0ull;
+      if (tid < BOP_MAX_TAUS) s_sum[tid] = 0.0;
+      const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+      uint4* z4 = (uint4*)zt;
+      for (int i = tid; i < (npx >> 2); i += nthr) z4[i] = zero4;
+      __syncthreads();
     }
-    __syncthreads();
+    raster_phase();
+    if (j < 0) continue;
 
     if (MODE == MODE_RENDER) {
       float* out = a.depth_out + (size_t)sD.im * a.pp.H * a.pp.W;
@@ -1036,12 +1088,13 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         unsigned long long v = 0ull;
         if (tid < 2) v = s_cnt[tid];
         else for (int c = tid - 1; c <= a.pp.n_taus; ++c) v += s_cnt[2 + c];
-        if (v) atomicAdd(a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS) + tid, v);
+        if (v) atomicAdd(a.counts + (size_t)pair * (2 + BOP_MAX_TAUS) + tid, v);
       }
     } else if (tid < 2 + BOP_MAX_TAUS && s_cnt[tid])
-      atomicAdd(a.counts + (size_t)sW.pair * (2 + BOP_MAX_TAUS) + tid, s_cnt[tid]);
+      atomicAdd(a.counts + (size_t)pair * (2 + BOP_MAX_TAUS) + tid, s_cnt[tid]);
     if (MODE == MODE_TLINEAR && tid < a.pp.n_taus && s_sum[tid] != 0.0)
-      atomicAdd(a.tl_sums + (size_t)sW.pair * BOP_MAX_TAUS + tid, s_sum[tid]);
+      atomicAdd(a.tl_sums + (size_t)pair * BOP_MAX_TAUS + tid, s_sum[tid]);
+    }   // phases
   }
 }
 
@@ -1254,7 +1307,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 constexpr size_t kGeomBudgetBytes = (size_t)8 << 30;   // assembled-triangle scratch per chunk
 
 struct WsLayout {
-  size_t ctr, counts, tl, bbox, mbox, desc, work, tri_cnt, band_off, tri_a, tri_b, tri_c, stage, pv, total;
+  size_t ctr, counts, tl, bbox, mbox, desc, work, tri_cnt, band_off, goff, tri_a, tri_b, tri_c, stage, pv, total;
   unsigned max_items;
   int chunk;       // items processed per pass (the batch is split so that the scratch fits the budget)
   int pv_stride;   // PVert records per (item, pose) (global fallback for models above kSmemVerts)
@@ -1291,6 +1344,7 @@ WsLayout ws_layout(int n, int H, int W, int n_poses, int max_geom) {
   L.work = off;    off = align_up(off + (size_t)L.max_items * sizeof(WorkItem), 256);
   L.tri_cnt = off; off = align_up(off + (size_t)c * 2 * sizeof(int), 256);
   L.band_off = off; off = align_up(off + (size_t)c * 2 * kBandOffN * sizeof(int), 256);
+  L.goff = off;    off = align_up(off + ((size_t)c + 1) * sizeof(int), 256);
   L.tri_a = off;   off = align_up(off + ntri * sizeof(int4), 256);
   L.tri_b = off;   off = align_up(off + ntri * sizeof(int4), 256);
   L.tri_c = off;   off = align_up(off + ntri * sizeof(float), 256);
@@ -1421,12 +1475,14 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
                 const double* pose_b, const int32_t* im_idx, const double* K,
                 const double* diameters, int cam_mode, int n,
                 int n_poses, int H, int W, int gate, unsigned char* ws, const WsLayout& L,
-                cudaStream_t s, int cx_off = 0, int cy_off = 0) {
+                cudaStream_t s, int cx_off = 0, int cy_off = 0, const int32_t* group_off = nullptr,
+                int n_groups = 0) {
   // counters + counts + tl sums are contiguous at the head of the workspace.
   BOP_CUDA(cudaMemsetAsync(ws, 0, L.bbox, s));
   GeomArgs g;
   g.models = models; g.obj_idx = obj_idx; g.pose_a = pose_a; g.pose_b = pose_b; g.im_idx = im_idx;
   g.K = K; g.diameters = diameters; g.cam_mode = cam_mode; g.n_poses = n_poses; g.H = H; g.W = W;
+  g.group_off = group_off;
   g.gate = gate; g.tile_px = effective_tile_px(W); g.pv_stride = L.pv_stride; g.tri_cap = L.tri_cap;
   g.pv_global = (PVert*)(ws + L.pv); g.tri_a = (int4*)(ws + L.tri_a); g.tri_b = (int4*)(ws + L.tri_b);
   g.tri_c = (float*)(ws + L.tri_c); g.stage = (unsigned*)(ws + L.stage); g.tri_cnt = (int*)(ws + L.tri_cnt);
@@ -1436,7 +1492,7 @@ int launch_plan(const bop_model_dev* models, const int32_t* obj_idx, const doubl
   const size_t geom_smem = (size_t)(L.pv_stride < kSmemVerts ? L.pv_stride : kSmemVerts) * sizeof(PVert) +
                            (size_t)kMaxBins * sizeof(int);
   BOP_CUDA(cudaFuncSetAttribute(geometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)geom_smem));
-  geometry_kernel<<<n, kAsmThreads, geom_smem, s>>>(g);
+  geometry_kernel<<<group_off ? n_groups : n, kAsmThreads, geom_smem, s>>>(g);
   bop_prof_end(BOP_PROF_VSD_PLAN, s);
   BOP_LAUNCH_CHECK();
   return 0;
@@ -1521,12 +1577,16 @@ extern "C" size_t bop_render_workspace_bytes(int n, int height, int width, int m
   return ws_layout(n, height, width, 1, max_geom).total;
 }
 
-extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
-                           const double* pose_est, const double* pose_gt, const void* depth_test,
-                           const float* depth_scale, const int32_t* im_idx, const double* K,
-                           const double* diameters, int n_pairs, int max_geom,
-                           const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
-                           void* workspace, size_t workspace_bytes, void* stream) {
+// pose_error.vsd for a batch of pairs.  group_off_host (host array, [n_groups + 1], NULL = every
+// pair on its own): consecutive pairs [off[g], off[g + 1]) share object, image, GT pose and
+// diameter -- the k estimates scripts/eval_calc_errors.py:281-289 pairs with one GT.  The geometry
+// and raster work of the GT pose is then done once per group instead of once per pair.
+static int vsd_impl(const bop_model_dev* models, const int32_t* obj_idx, const double* pose_est,
+                    const double* pose_gt, const void* depth_test, const float* depth_scale,
+                    const int32_t* im_idx, const double* K, const double* diameters, int n_pairs,
+                    const int32_t* group_off_host, int n_groups, int max_geom,
+                    const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
+                    void* workspace, size_t workspace_bytes, void* stream) {
   if (n_pairs <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && depth_test && im_idx && K && errors_out,
               "bop_vsd_dev: null pointer");
@@ -1536,13 +1596,38 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
   const WsLayout L = ws_layout(n_pairs, pp.H, pp.W, 2, max_geom);
   BOP_REQUIRE(workspace && workspace_bytes >= L.total, "bop_vsd_dev: workspace too small");
   BOP_REQUIRE(((uintptr_t)workspace) % 256 == 0, "bop_vsd_dev: workspace must be 256-byte aligned");
+  if (group_off_host) {
+    BOP_REQUIRE(n_groups >= 1 && group_off_host[0] == 0 && group_off_host[n_groups] == n_pairs,
+                "bop_vsd_grouped_dev: group offsets must start at 0 and end at n_pairs");
+    for (int gI = 0; gI < n_groups; ++gI) {
+      const int k = group_off_host[gI + 1] - group_off_host[gI];
+      BOP_REQUIRE(k >= 1 && k <= kMaxGroup, "bop_vsd_grouped_dev: a group holds 1 .. 32 pairs");
+    }
+  }
   cudaStream_t s = (cudaStream_t)stream;
   unsigned char* ws = (unsigned char*)workspace;
-  for (int c0 = 0; c0 < n_pairs; c0 += L.chunk) {
-    const int nc = n_pairs - c0 < L.chunk ? n_pairs - c0 : L.chunk;
+  std::vector<int32_t> rebased;
+  int g0 = 0;   // first group of the chunk
+  for (int c0 = 0; c0 < n_pairs;) {
+    int nc, ng = 0;
+    if (group_off_host) {   // whole groups, at most L.chunk pairs (a group never exceeds a chunk: chunk >= kMaxGroup or n_pairs)
+      int g1 = g0;
+      while (g1 < n_groups && group_off_host[g1 + 1] - c0 <= (L.chunk > kMaxGroup ? L.chunk : kMaxGroup)) ++g1;
+      BOP_REQUIRE(g1 > g0, "bop_vsd_grouped_dev: workspace chunk smaller than a group");
+      nc = group_off_host[g1] - c0;
+      ng = g1 - g0;
+      rebased.resize((size_t)ng + 1);
+      for (int k = 0; k <= ng; ++k) rebased[k] = group_off_host[g0 + k] - c0;
+      BOP_CUDA(cudaMemcpyAsync(ws + L.goff, rebased.data(), sizeof(int32_t) * ((size_t)ng + 1), cudaMemcpyHostToDevice, s));
+      BOP_CUDA(cudaStreamSynchronize(s));   // `rebased` is reused by the next chunk
+      g0 = g1;
+    } else {
+      nc = n_pairs - c0 < L.chunk ? n_pairs - c0 : L.chunk;
+    }
     if (int rc = launch_plan(models, obj_idx + c0, pose_est + 12 * (size_t)c0, pose_gt + 12 * (size_t)c0,
                              im_idx + c0, K, diameters ? diameters + c0 : nullptr, 0, nc, 2, pp.H,
-                             pp.W, prm->gate, ws, L, s))
+                             pp.W, prm->gate, ws, L, s, 0, 0,
+                             group_off_host ? (const int32_t*)(ws + L.goff) : nullptr, ng))
       return rc;
     FusedArgs a;
     a.models = models;
@@ -1570,8 +1655,32 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
         a.counts, a.tl_sums, nc, pp.n_taus, prm->cost_type, errors_out + (size_t)c0 * pp.n_taus,
         counts_out ? (long long*)counts_out + (size_t)c0 * (2 + pp.n_taus) : nullptr);
     BOP_LAUNCH_CHECK();
+    c0 += nc;
   }
   return 0;
+}
+
+extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                           const double* pose_est, const double* pose_gt, const void* depth_test,
+                           const float* depth_scale, const int32_t* im_idx, const double* K,
+                           const double* diameters, int n_pairs, int max_geom,
+                           const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+  return vsd_impl(models, obj_idx, pose_est, pose_gt, depth_test, depth_scale, im_idx, K, diameters, n_pairs,
+                  nullptr, 0, max_geom, prm, errors_out, counts_out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int bop_vsd_grouped_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                                   const double* pose_est, const double* pose_gt, const void* depth_test,
+                                   const float* depth_scale, const int32_t* im_idx, const double* K,
+                                   const double* diameters, int n_pairs, const int32_t* group_off_host,
+                                   int n_groups, int max_geom, const bop_vsd_params* prm,
+                                   double* errors_out, int64_t* counts_out, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+  BOP_REQUIRE(group_off_host, "bop_vsd_grouped_dev: null group offsets");
+  return vsd_impl(models, obj_idx, pose_est, pose_gt, depth_test, depth_scale, im_idx, K, diameters, n_pairs,
+                  group_off_host, n_groups, max_geom, prm, errors_out, counts_out, workspace, workspace_bytes,
+                  stream);
 }
 
 extern "C" int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,

@@ -505,11 +505,16 @@ class ErrorEngine(object):
         depth, sc = load_depth_stack(paths, [scene_camera[i]['depth_scale'] for i in im_ids], h, w)
       rows = np.nonzero(np.isin(im_pos, chunk))[0]
       local = np.searchsorted(chunk, im_pos[rows]).astype(np.int32)
+      # every estimate of an object meets every GT pose of it (:281-289): the pairs that share a GT
+      # pose go to the kernel as one group (GT geometry and raster work once per group)
+      order, goff = batch.group_pairs_by_gt(oi[rows], pg[rows], local)
+      rows, local = rows[order], local[order]
       err = batch.vsd_batch(self.ms, oi[rows], pe[rows], pg[rows], depth, local,
                             self._K_rows(scene_camera, im_ids), p['vsd_deltas'][self.dataset],
                             p['vsd_taus'], p['vsd_normalized_by_diameter'], 'step', 'bop19',
                             gate=True, depth_scale=sc,
-                            zero_copy=(not depth.is_cuda) and depth.is_pinned())
+                            zero_copy=(not depth.is_cuda) and depth.is_pinned(),
+                            group_off=(goff if len(goff) - 1 < len(rows) else None))
       out[rows] = err.cpu().numpy()
     return out
 

@@ -194,6 +194,20 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
+/* bop_vsd_dev for pairs that share their GT pose: scripts/eval_calc_errors.py:281-289 pairs every
+ * estimate of an object with every GT pose of it, so a GT pose is typically evaluated against
+ * several estimates.  group_off_host (HOST array, [n_groups + 1], group_off_host[0] = 0,
+ * group_off_host[n_groups] = n_pairs) cuts the batch into groups of 1 .. 32 consecutive pairs
+ * with the same obj_idx, im_idx, pose_gt and diameter (the caller sorts; the library trusts it).
+ * The GT pose of a group is projected, sorted and rasterised once; its z-tile stays in shared
+ * memory while the estimates of the group take turns.  Results are bit-identical to bop_vsd_dev
+ * on the same pairs (tests/test_gpu_parity.py::test_vsd_grouped_equals_ungrouped). */
+int bop_vsd_grouped_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                        const double* pose_est, const double* pose_gt, const void* depth_test,
+                        const float* depth_scale, const int32_t* im_idx, const double* K,
+                        const double* diameters, int n_pairs, const int32_t* group_off_host,
+                        int n_groups, int max_geom, const bop_vsd_params* prm, double* errors_out,
+                        int64_t* counts_out, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- mask overlap: pose_error.cus / cou_bb_proj / cou_mask --------------------
  * pose_error.cus (pose_error.py:256-286): 1 - |mask_est & mask_gt| / |mask_est | mask_gt| of the

@@ -653,3 +653,59 @@ def test_render_known_answer_scenes(B):
   assert np.abs(got[safe] - want[safe]).max() <= 1e-5 * want[safe].max()
   outside = ~inside(da, -3.0) & ~inside(db, -3.0)
   assert not got[outside].any()
+
+
+# ------------------------------------------------------------------ pairs that share their GT pose
+@pytest.mark.gpu
+def test_vsd_grouped_equals_ungrouped(B, oracle_built):
+  """bop_vsd_grouped_dev (GT pose projected, sorted and rasterised once per group of estimates)
+  against bop_vsd_dev on the same pairs: bit-identical errors and counts -- groups of 1..5
+  estimates incl. gated ones, estimates outside the image, a group above 32 (cut), step and
+  tlinear cost, close-ups that need several row bands."""
+  from bop_toolkit_b200 import synth
+  K = synth.LM_K
+  rng = np.random.default_rng(5)
+  pts, faces = synth.make_mesh(40, 80, 240.0, seed=61)
+  pts2, faces2 = synth.make_mesh(24, 48, 120.0, seed=62)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 240.0)
+  ms.add(2, pts2, faces2, None, 120.0)
+  n_gt = 40
+  _, _, R_g, t_g = synth.make_pose_pairs(n_gt, seed=63, z_range=(330.0, 1300.0), outlier_frac=0.0)
+  k_of = rng.integers(1, 6, size=n_gt)
+  k_of[3] = 37                                         # above kMaxGroup
+  gt_of = np.repeat(np.arange(n_gt), k_of)
+  P = len(gt_of)
+  R_e = np.empty((P, 3, 3)); t_e = np.empty((P, 3))
+  for i in range(P):
+    g = gt_of[i]
+    ang = np.radians(rng.uniform(0, 20))
+    R_e[i] = R_g[g] @ synth.axis_angle(rng.normal(size=3), ang)
+    t_e[i] = t_g[g] + rng.normal(size=3) * np.array([6.0, 6.0, 20.0])
+  far = rng.choice(P, 12, replace=False)
+  t_e[far[:6], 0] += 700.0                             # fail the sphere gate
+  t_e[far[6:], :2] += 4000.0                           # outside the image, gated too
+  obj = (gt_of % 2).astype(np.int32)                   # model row: alternates per GT
+  im = gt_of.astype(np.int32)
+  depth = np.full((n_gt, 480, 640), 900.0, np.float32)
+  depth += rng.normal(0, 30.0, depth.shape).astype(np.float32)
+  depth[:, ::9, ::7] = 0.0
+  Ks = np.tile(K.reshape(1, 9), (n_gt, 1))
+  pe, pg = B.pack_poses(R_e, t_e), B.pack_poses(R_g[gt_of], t_g[gt_of])
+  perm = rng.permutation(P)                            # the caller's order is arbitrary
+  pe, pg, obj, im = pe[perm], pg[perm], obj[perm], im[perm]
+  order, goff = B.group_pairs_by_gt(obj, pg, im)
+  assert goff[-1] == P and (np.diff(goff) <= 32).all() and len(goff) - 1 >= n_gt + 1
+  taus = [0.05 * (k + 1) for k in range(10)]
+  for cost in ('step', 'tlinear'):
+    e0, c0 = B.vsd_batch(ms, obj, pe, pg, depth, im, Ks, 15.0, taus, True, cost, 'bop19', gate=True,
+                         return_counts=True)
+    e1, c1 = B.vsd_batch(ms, obj[order], pe[order], pg[order], depth, im[order], Ks, 15.0, taus, True, cost,
+                         'bop19', gate=True, return_counts=True, group_off=goff)
+    e0, c0, e1, c1 = e0.cpu().numpy(), c0.cpu().numpy(), e1.cpu().numpy(), c1.cpu().numpy()
+    assert np.array_equal(c0[order], c1), cost
+    if cost == 'step':
+      assert np.array_equal(e0[order], e1)
+    else:
+      assert np.abs(e0[order] - e1).max() <= 1e-12      # float64 sums of the tlinear cost: order of the adds
+    assert (c1[:, 0] > 0).sum() > P // 2 and (e1 == 1.0).all(axis=1).sum() >= 12

@@ -218,6 +218,13 @@ def run(torch, dist, device, rank, world, n_images=20000, steps=1, cull=False, s
   local_of = np.full(n_images, -1, dtype=np.int64)
   local_of[my_images] = np.arange(len(my_images))
   sel = np.nonzero(owner[tab['p_im']] == rank)[0]
+  # the estimates of one GT pose are consecutive in the table (pairs are sorted by instance): groups
+  # for bop_vsd_grouped_dev -- the GT pose is projected, sorted and rasterised once per group
+  inst_sel = tab['p_inst'][sel]
+  cut = np.flatnonzero(np.diff(inst_sel)) + 1
+  group_off = np.concatenate([[0], cut, [len(sel)]]).astype(np.int32) if len(sel) else np.zeros(1, np.int32)
+  if os.environ.get('BOP_CFG5_NO_GROUPS'):
+    group_off = None
   t0 = time.time()
   d16 = make_depth(torch, batch, ms, tab, my_images, device)
   torch.cuda.synchronize()
@@ -238,7 +245,7 @@ def run(torch, dist, device, rank, world, n_images=20000, steps=1, cull=False, s
 
   def step():
     vsd = batch.vsd_batch(ms, obj, pe, pg, d16, im_local, Kd, DELTA, TAUS, True, 'step', 'bop19', gate=True,
-                          depth_scale=scale)
+                          depth_scale=scale, group_off=group_off)
     mssd = batch.mssd_batch(ms, obj, pe, pg, gate=True)
     mspd = batch.mspd_batch(ms, obj, pe, pg, Kp)
     errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
@@ -290,7 +297,7 @@ def run(torch, dist, device, rank, world, n_images=20000, steps=1, cull=False, s
     'AR': ar, 'AR_mean': float(np.mean(list(ar.values()))),
     'records_sha256': records_sha256(ids_np, errs_np),
     'recalls_sha256': hashlib.sha256(np.asarray(flat, dtype=np.float64).tobytes()).hexdigest(),
-    'cull': bool(cull)}
+    'cull': bool(cull), 'gt_groups': (int(len(group_off)) - 1) if group_off is not None else None}
 
 
 def main():
