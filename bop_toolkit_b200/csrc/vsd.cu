@@ -722,6 +722,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
   __shared__ int s_seg0[4];   // first list entry of each segment
   __shared__ int s_segc[5];   // virtual index where each segment starts; [4] = total
   __shared__ int s_slot[4];   // list (pair * n_poses + pose) each segment belongs to
+  __shared__ long long s_base[4];
   __shared__ unsigned long long s_cnt[2 + BOP_MAX_TAUS + 1];
   __shared__ double s_sum[BOP_MAX_TAUS];
   __shared__ float s_tau[BOP_MAX_TAUS + 2];
@@ -759,7 +760,9 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
           else if (sg & 1) { lo = off[nbs]; hi = off[nbs + 1]; }
           else { lo = off[sW.band]; hi = off[sW.band + 1]; }
         }
-        s_seg0[sg] = lo; s_segc[sg] = c; s_slot[sg] = slot; c += hi - lo;
+        s_seg0[sg] = lo; s_segc[sg] = c; s_slot[sg] = slot;
+        s_base[sg] = (long long)slot * a.tri_cap + lo - c;   // list entry of virtual index g = s_base + g
+        c += hi - lo;
       }
       s_segc[4] = c;
     };
@@ -817,7 +820,7 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
         const int sg = (g >= c1 ? 1 : 0) + (g >= c2 ? 1 : 0) + (g >= c3 ? 1 : 0);
         p = sg >> 1;
         BOP_DCHECK(g >= 0 && g < nT && s_seg0[sg] + (g - s_segc[sg]) < a.tri_cnt[s_slot[sg]]);
-        return (size_t)s_slot[sg] * a.tri_cap + (size_t)(s_seg0[sg] + (g - s_segc[sg]));
+        return (size_t)(s_base[sg] + g);
       };
       // Warps claim 32 consecutive triangles at a time from a shared ticket (triangle cost varies
       // by class; static striding would leave warps idle at the barrier).  The records of the NEXT
