@@ -150,7 +150,16 @@ __device__ __forceinline__ float plane_iz(float pa, float rowbase, float fdx) {
 // crosses zero; outside the parity domain) is negative or zero as an integer and never wins.
 // The store is a predicated shared-memory reduction (cover >= 0 <=> the three biased edge
 // functions are all non-negative): no branch in the per-candidate loop.
+#ifndef BOP_ZMERGE_SELECT
+#define BOP_ZMERGE_SELECT 1
+#endif
 __device__ __forceinline__ void z_merge_if(unsigned saddr, float iz, int cover) {
+#if BOP_ZMERGE_SELECT
+  // branch-free variant: an uncovered candidate merges 0, which never wins
+  const int v = __float_as_int(iz) & ~(cover >> 31);
+  asm volatile("red.shared.max.s32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
+  return;
+#endif
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, 0;\n\t@p red.shared.max.s32 [%0], %1;\n\t}"
       :: "r"(saddr), "r"(__float_as_int(iz)), "r"(cover) : "memory");
