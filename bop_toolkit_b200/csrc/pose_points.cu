@@ -177,7 +177,10 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
   }
-  for (int i = tid; i < kWarps * BOP_MAX_SYMS_PER_CTA * 32; i += kThreads) (&sm.run[0][0][0])[i] = 0.0;
+  for (int i = tid; i < kWarps * ns * 32; i += kThreads) {   // only the symmetries this CTA owns
+    const int wi = i / (ns * 32);
+    (&sm.run[wi][0][0])[i - wi * ns * 32] = 0.0;
+  }
   if (MODE == 1 && tid == 32) {
     const double* Kp = Kmat + 9 * (size_t)pair;
 #pragma unroll
