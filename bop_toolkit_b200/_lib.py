@@ -14,6 +14,7 @@ SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu', 'png_depth.cu', 'error_json.cpp
 HEADERS = ['common.cuh', 'raster.cuh', 'png_inflate.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
 
 BOP_MAX_TAUS = 16
+STATIC_MAX_PAIRS = 4096   # BOP_STATIC_MAX_PAIRS (bop_vsd_from_depth_static_dev)
 COST_TYPES = {'step': 0, 'tlinear': 1}
 VISIB_MODES = {'bop19': 0, 'bop18': 1}
 DEPTH_F32, DEPTH_U16 = 0, 1
@@ -104,6 +105,7 @@ _SIGNATURES = {
   'bop_vsd_workspace_bytes': (ctypes.c_size_t, [_I, _I, _I, _I]),
   'bop_vsd_from_depth_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P,
                                    ctypes.c_size_t, _P]),
+  'bop_vsd_from_depth_static_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P]),
   'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
                        _P]),
   'bop_vsd_grouped_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P,

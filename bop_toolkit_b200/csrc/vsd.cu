@@ -16,6 +16,7 @@
 // depths the integer counts -- and hence the errors -- are bit-identical to numpy's.
 #include <limits.h>
 #include <stddef.h>
+#include <mutex>
 #include <type_traits>
 #include <vector>
 
@@ -1768,6 +1769,96 @@ extern "C" int bop_vsd_from_depth_dev(const void* depth_test, const float* depth
   vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, tl, n_pairs, pp.n_taus,
                                                             prm->cost_type, errors_out,
                                                             (long long*)counts_out);
+  BOP_LAUNCH_CHECK();
+  return 0;
+}
+
+// =====================================================================================
+// bop_vsd_from_depth_static_dev: bop_vsd_from_depth_dev for callers that must not allocate
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// No counterpart in the reference.
+//
+// The scratch of the K2 pass -- plan counters, per-pair integer counts [n][2 + BOP_MAX_TAUS] u64
+// and tlinear sums [n][BOP_MAX_TAUS] f64: 272 B per pair -- lives in a file-scope __device__
+// array sized for BOP_STATIC_MAX_PAIRS pairs (1,114,368 B = 1.06 MiB; every GPU that loads the
+// library holds it until the process exits).  In HOST code `g_k2_static_scratch` is only a
+// stand-in for the symbol, not a device address: the address is looked up once per device, with
+// that device current, by cudaGetSymbolAddress and that pointer is what the kernels receive.
+// The function calls no cudaMalloc / cudaFree / allocating library routine (it also leaves the
+// optional per-kernel profiling events alone, which are created on first use).  Every call on a
+// device shares the one array, which keeps the previous call's contents: the part a call uses is
+// cleared at the start of the call (a memset node on the caller's stream), and two calls that
+// OVERLAP on the GPU (different streams, or graphs replayed concurrently) race on it -- keep
+// calls of this entry point on one stream or order them with events.
+// =====================================================================================
+namespace {
+
+constexpr int kStaticMaxPairs = BOP_STATIC_MAX_PAIRS;
+constexpr size_t kStaticCtrBytes = 256;
+constexpr size_t kStaticCountsBytes = (size_t)kStaticMaxPairs * (2 + BOP_MAX_TAUS) * 8;   // multiple of 256
+constexpr size_t kStaticTlBytes = (size_t)kStaticMaxPairs * BOP_MAX_TAUS * 8;             // multiple of 256
+constexpr size_t kStaticScratchBytes = kStaticCtrBytes + kStaticCountsBytes + kStaticTlBytes;
+static_assert(kStaticCountsBytes % 256 == 0 && kStaticTlBytes % 256 == 0, "static scratch layout must stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_k2_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+unsigned char* g_k2_static_ptr[kStaticMaxDevices];   // device address of the array, per device (0 = not looked up yet)
+std::mutex g_k2_static_mutex;
+
+// Device address of g_k2_static_scratch on the CURRENT device (looked up on the first call per device).
+int k2_static_scratch(unsigned char** out) {
+  int dev = -1;
+  BOP_CUDA(cudaGetDevice(&dev));
+  BOP_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "bop_vsd_from_depth_static_dev: device index out of range");
+  std::lock_guard<std::mutex> lock(g_k2_static_mutex);
+  if (!g_k2_static_ptr[dev]) {
+    void* ptr = nullptr;
+    BOP_CUDA(cudaGetSymbolAddress(&ptr, g_k2_static_scratch));
+    BOP_REQUIRE(ptr && ((uintptr_t)ptr) % 256 == 0, "bop_vsd_from_depth_static_dev: bad symbol address");
+    g_k2_static_ptr[dev] = (unsigned char*)ptr;
+  }
+  *out = g_k2_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int bop_vsd_from_depth_static_dev(const void* depth_test, const float* depth_scale,
+                                             const int32_t* im_idx, const double* K,
+                                             const float* depth_est, const float* depth_gt,
+                                             const double* diameters, int n_pairs,
+                                             const bop_vsd_params* prm, double* errors_out,
+                                             int64_t* counts_out, void* stream) {
+  if (n_pairs <= 0) return 0;
+  BOP_REQUIRE(n_pairs <= kStaticMaxPairs,
+              "bop_vsd_from_depth_static_dev: n_pairs exceeds BOP_STATIC_MAX_PAIRS (4096); split the batch or use "
+              "bop_vsd_from_depth_dev with a caller-provided workspace");
+  BOP_REQUIRE(depth_test && im_idx && K && depth_est && depth_gt && diameters && errors_out,
+              "bop_vsd_from_depth_static_dev: null pointer");
+  PixParams pp;
+  if (int rc = fill_pix_params(prm, depth_test, pp)) return rc;
+  pp.vec_ok = pp.vec_ok && ((uintptr_t)depth_est % 16 == 0) && ((uintptr_t)depth_gt % 16 == 0);
+  unsigned char* ws = nullptr;
+  if (int rc = k2_static_scratch(&ws)) return rc;
+  unsigned long long* counts = (unsigned long long*)(ws + kStaticCtrBytes);
+  double* tl = (double*)(ws + kStaticCtrBytes + kStaticCountsBytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  // the array keeps the previous call's contents: clear the counters and this call's rows
+  BOP_CUDA(cudaMemsetAsync(ws, 0, kStaticCtrBytes + (size_t)n_pairs * (2 + BOP_MAX_TAUS) * 8, s));
+  BOP_CUDA(cudaMemsetAsync(tl, 0, (size_t)n_pairs * BOP_MAX_TAUS * 8, s));
+  const int ngroups = pp.H * ((pp.W + 3) >> 2);
+  const int chunk = kK2Threads * kK2GroupsPerThread;
+  dim3 grid(n_pairs, (ngroups + chunk - 1) / chunk);
+  if (prm->cost_type == BOP_COST_TLINEAR)
+    pixel_pass_kernel<MODE_TLINEAR><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
+                                                               depth_gt, diameters, counts, tl, pp);
+  else
+    pixel_pass_kernel<MODE_STEP><<<grid, kK2Threads, 0, s>>>(depth_test, depth_scale, im_idx, K, depth_est,
+                                                            depth_gt, diameters, counts, tl, pp);
+  BOP_LAUNCH_CHECK();
+  vsd_finalize_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(counts, tl, n_pairs, pp.n_taus, prm->cost_type,
+                                                            errors_out, (long long*)counts_out);
   BOP_LAUNCH_CHECK();
   return 0;
 }

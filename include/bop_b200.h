@@ -179,6 +179,26 @@ int bop_vsd_from_depth_dev(const void* depth_test, const float* depth_scale,
                            int64_t* counts_out, void* workspace,
                            size_t workspace_bytes, void* stream);
 
+/* bop_vsd_from_depth_dev without a workspace argument and without any allocation.  It has no
+ * counterpart in the reference; it was added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and results as bop_vsd_from_depth_dev; the scratch (counters,
+ * per-pair counts, tlinear sums: 272 B per pair) lives in a static __device__ array inside the
+ * library, sized for BOP_STATIC_MAX_PAIRS pairs (1.06 MiB, held by every GPU that loads the
+ * library until the process exits).  n_pairs > BOP_STATIC_MAX_PAIRS is rejected with an error
+ * (split the batch, or use the workspace variant).  The function calls no cudaMalloc / cudaFree /
+ * allocating routine; its only set-up is one cudaGetSymbolAddress per device on the first call
+ * made with that device current (make that call once outside a graph capture).  All calls on a
+ * device share the one array: each call clears the part it uses on `stream` first, and calls
+ * that OVERLAP on the GPU (different streams without an ordering between them) race on it. */
+#define BOP_STATIC_MAX_PAIRS 4096
+int bop_vsd_from_depth_static_dev(const void* depth_test, const float* depth_scale,
+                                  const int32_t* im_idx, const double* K,
+                                  const float* depth_est, const float* depth_gt,
+                                  const double* diameters, int n_pairs,
+                                  const bop_vsd_params* prm, double* errors_out,
+                                  int64_t* counts_out, void* stream);
+
 /* ---- K1+K2 fused: pose_error.vsd for a batch of pose pairs -----------------
  * pose_error.vsd (pose_error.py:17-93) with the library's own rasteriser: both
  * poses are rendered into shared-memory z-tiles over the union ROI and consumed
