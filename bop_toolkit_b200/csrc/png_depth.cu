@@ -6,8 +6,8 @@
 //   1. bop_png_stage_files_host  host threads read the files straight into one pinned staging
 //      buffer and compact each file's IDAT payloads in place (no decompression on the host);
 //   2. png_inflate_kernel        one warp per image inflates the zlib stream (png_inflate.cuh):
-//      lane 0 decodes symbols with its tables in shared memory, matches of >= 16 bytes are copied
-//      by all 32 lanes;
+//      the 32 lanes decode in lockstep on identical state with the tables in shared memory, lane 0
+//      stores literals and every match is copied by all lanes;
 //   3. png_unfilter_kernel       one warp per image undoes the PNG row filters (None / Sub / Up /
 //      Average / Paeth, PNG spec 9.2) row by row in shared memory and writes little-endian uint16
 //      samples, coalesced.
@@ -68,45 +68,23 @@ png_inflate_kernel(const uint8_t* __restrict__ comp, const int64_t* __restrict__
   ring_load(ring, src, nwords, 0u, kRingWords, lane);
   uint32_t ring_hi = kRingWords;           // words [ring_hi - kRingWords, ring_hi) are in the ring
   __syncwarp();
+  // Warp-replicated decode (png_inflate.cuh): every lane holds the same State and takes the same
+  // branches; lane 0 stores literals, all lanes copy matches.
   State s;
-  int ev = 0;
-  if (lane == 0) {
-    if (nb < 6) ev = EV_TRUNCATED;
-    else ev = inflate_begin(s, ring, nwords, kRingWords - 1u,
-                            ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin, out, expect);
-  }
-  ev = __shfl_sync(BOP_FULL_MASK, ev, 0);
+  int ev = nb < 6 ? (int)EV_TRUNCATED
+                  : inflate_begin(s, ring, nwords, kRingWords - 1u,
+                                  ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin, out, expect);
   if (ev == 0) {
     for (;;) {
-      uint32_t o = 0, len = 0, dist = 0;
-      if (lane == 0) {
-        ev = inflate_run(s, tabs[warp]);
-        o = s.o; len = s.m_len; dist = s.m_dist;
-      }
-      ev = __shfl_sync(BOP_FULL_MASK, ev, 0);
-      if (ev == EV_INPUT) {
-        // the reader is within kRingMargin words of the ring's end: everything more than that
-        // behind it is consumed, so the oldest kRingRefill words can be replaced
-        ring_load(ring, src, nwords, ring_hi, kRingRefill, lane);
-        ring_hi += kRingRefill;
-        __syncwarp();
-        if (lane == 0) s.br.limit = ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin;
-        continue;
-      }
-      if (ev != EV_COPY) break;
-      o = __shfl_sync(BOP_FULL_MASK, o, 0);
-      len = __shfl_sync(BOP_FULL_MASK, len, 0);
-      dist = __shfl_sync(BOP_FULL_MASK, dist, 0);
-      __syncwarp();   // lane 0's stores are ordered before the other lanes' loads
-      // every source byte lies in the already written window [o - dist, o)
-      const uint8_t* srcb = out + o - dist;
-      if (dist >= len) {
-        for (uint32_t i = lane; i < len; i += 32) out[o + i] = srcb[i];
-      } else {
-        for (uint32_t i = lane; i < len; i += 32) out[o + i] = srcb[i % dist];
-      }
+      ev = inflate_run(s, tabs[warp], lane, 32);
+      if (ev != EV_INPUT) break;
+      // the reader is within kRingMargin words of the ring's end: everything more than that
+      // behind it is consumed, so the oldest kRingRefill words can be replaced
       __syncwarp();
-      if (lane == 0) s.o = o + len;
+      ring_load(ring, src, nwords, ring_hi, kRingRefill, lane);
+      ring_hi += kRingRefill;
+      __syncwarp();
+      s.br.limit = ring_hi >= nwords + 8u ? 0xffffffffu : ring_hi - kRingMargin;
     }
   }
   if (lane == 0) {

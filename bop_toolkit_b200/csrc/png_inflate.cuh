@@ -4,10 +4,15 @@
 // bop_toolkit_lib/inout.py:39-46, `imageio.imread` of the 16-bit depth PNGs read by
 // scripts/eval_calc_errors.py:236-243).  One DEFLATE stream is serial by construction (symbol
 // boundaries are only known after decoding), so the parallelism is ACROSS images: on the device
-// one warp owns one image, lane 0 runs `inflate_run` below with its Huffman tables in shared
-// memory and hands long LZ77 matches to the whole warp (EV_COPY).  The same source compiles for
-// the host (`bop_png_decode_selftest_host`), which is how the CPU test-suite checks the decoder
-// bit for bit against zlib without a GPU.
+// one warp owns one image.  The decode loop is WARP-REPLICATED: all 32 lanes run `inflate_run`
+// below on identical state (the Huffman tables and the input ring are in shared memory, so a
+// table look-up is one broadcast load for the warp and costs the issue slot it cost when a single
+// lane decoded), lane 0 stores the literals, and every LZ77 match -- whatever its length -- is
+// copied by all lanes at once: no hand-off between a decoding lane and a copying warp, and no
+// byte-by-byte copies of the short matches that make up most of a depth PNG.  Tables are built by
+// lane 0 and the bit reader is broadcast afterwards (the builders are read-modify-write code).
+// The same source compiles for the host (`bop_png_decode_selftest_host`, lane 0 of 1), which is
+// how the CPU test-suite checks the decoder bit for bit against zlib without a GPU.
 #pragma once
 #include <stdint.h>
 
@@ -19,11 +24,16 @@
 #define BOP_HD_NOINLINE
 #endif
 
+#ifdef __CUDA_ARCH__
+#define BOP_PNG_WARP_SYNC() __syncwarp()
+#else
+#define BOP_PNG_WARP_SYNC() ((void)0)
+#endif
+
 namespace bop_png {
 
 constexpr int kLitBits = 10;    // primary lookup width of the literal/length code
 constexpr int kDistBits = 8;    // primary lookup width of the distance code
-constexpr uint32_t kCoopMin = 16;  // matches at least this long are copied by the whole warp
 constexpr uint32_t kRingWords = 1024;   // device input ring per stream (4 KB of shared memory)
 constexpr uint32_t kRingRefill = 512;   // words loaded per EV_INPUT
 constexpr uint32_t kRingMargin = 256;   // the reader asks for input this far before the ring's end:
@@ -31,7 +41,7 @@ constexpr uint32_t kRingMargin = 256;   // the reader asks for input this far be
 
 enum {
   EV_DONE = 0,           // final block finished
-  EV_COPY = 1,           // caller copies m_len bytes from distance m_dist, then adds m_len to o
+  EV_COPY = 1,           // (unused since the decode loop is warp-replicated: matches are copied inside inflate_run)
   EV_INPUT = 2,          // caller loads more of the stream into the ring and raises br.limit
   EV_BAD_HEADER = -1,    // not a zlib stream (CM != 8, preset dictionary, bad check bits)
   EV_BAD_BLOCK = -2,     // reserved block type / stored LEN != ~NLEN
@@ -232,9 +242,10 @@ BOP_HD int inflate_begin(State& s, const uint32_t* in, uint32_t nwords, uint32_t
   return 0;
 }
 
-// Decodes until the stream ends (EV_DONE), a long match needs the caller (EV_COPY) or an error.
-// Matches shorter than kCoopMin are copied here.
-BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
+// Decodes until the stream ends (EV_DONE), more input is needed (EV_INPUT) or an error.
+// Device: called by ALL lanes of the warp that owns the stream with identical `s` (lane = 0..31,
+// nlanes = 32); every lane follows the same control flow.  Host: lane 0 of 1.
+BOP_HD_NOINLINE int inflate_run(State& s, Tables& t, int lane = 0, int nlanes = 1) {
   BitReader br = s.br;
   uint8_t* const out = s.out;
 #ifdef __CUDA_ARCH__
@@ -252,7 +263,9 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
       uint32_t left = s.stored_left;
       while (left && !br.starved()) {
         br.refill();
-        out[o++] = (uint8_t)br.bits(8);
+        const uint8_t v = (uint8_t)br.bits(8);
+        if (lane == 0) out[o] = v;
+        ++o;
         --left;
       }
       s.stored_left = left;
@@ -289,10 +302,22 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
         if (o + len > cap) { ev = EV_OVERFLOW; break; }
         s.stored_left = len;
         continue;
-      } else if (type == 1) {
-        build_fixed(t);
-      } else if (type == 2) {
-        const int rc = build_dynamic(br, t);
+      } else if (type == 1 || type == 2) {
+        // lane 0 builds the tables (every lane is done with the previous block's), then hands
+        // the bit reader -- advanced past a dynamic block's header -- to the other lanes
+        int rc = 0;
+        BOP_PNG_WARP_SYNC();
+        if (lane == 0) rc = type == 1 ? build_fixed(t) : build_dynamic(br, t);
+#ifdef __CUDA_ARCH__
+        if (nlanes > 1) {
+          rc = __shfl_sync(0xffffffffu, rc, 0);
+          br.buf = __shfl_sync(0xffffffffu, (unsigned long long)br.buf, 0);
+          br.cnt = __shfl_sync(0xffffffffu, br.cnt, 0);
+          br.ipos = __shfl_sync(0xffffffffu, br.ipos, 0);
+          br.nextw = __shfl_sync(0xffffffffu, br.nextw, 0);
+        }
+#endif
+        BOP_PNG_WARP_SYNC();
         if (rc) { ev = rc; break; }
       } else {
         ev = EV_BAD_BLOCK;
@@ -305,18 +330,32 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
     // and taken branches per symbol, so the checks that only guard against corrupt input are
     // folded (one range test per match, input exhaustion looked at only when a word is loaded).
     for (;;) {
-      // Runs of literals: one table look-up, one combined test (a literal whose code fits the
-      // primary table has an entry in [1, 4095]; 0 = long code, >= 4096 = end of block / length),
-      // everything else drops to the general step below.
+      // Runs of literals: one table look-up and one combined test per literal (a literal whose code
+      // fits the primary table has an entry in [1, 4095]; 0 = long code, >= 4096 = end of block /
+      // length); everything else drops to the general step below.  After a refill at least 33 bits
+      // are valid and such a literal takes at most kLitBits = 10 of them, so THREE are decoded per
+      // refill check, and the output bound is checked once for the three.
       for (;;) {
         if (br.cnt <= 32) {
           if (br.starved()) break;
           br.refill();
         }
-        const uint32_t e = t.lit_fast[br.peek(kLitBits)];
-        if (e - 1u >= 4095u || o >= cap) break;
+        if (o + 3u > cap) break;
+        uint32_t e = t.lit_fast[br.peek(kLitBits)];
+        if (e - 1u >= 4095u) break;
         br.drop((int)(e & 15u));
-        out[o++] = (uint8_t)(e >> 4);
+        if (lane == 0) out[o] = (uint8_t)(e >> 4);
+        ++o;
+        e = t.lit_fast[br.peek(kLitBits)];
+        if (e - 1u >= 4095u) break;
+        br.drop((int)(e & 15u));
+        if (lane == 0) out[o] = (uint8_t)(e >> 4);
+        ++o;
+        e = t.lit_fast[br.peek(kLitBits)];
+        if (e - 1u >= 4095u) break;
+        br.drop((int)(e & 15u));
+        if (lane == 0) out[o] = (uint8_t)(e >> 4);
+        ++o;
       }
       if (br.cnt <= 32) {
         if (br.starved()) { ev = EV_INPUT; goto done; }
@@ -333,7 +372,8 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
       }
       if (sym < 256) {
         if (o >= cap) { ev = EV_OVERFLOW; goto done; }
-        out[o++] = (uint8_t)sym;
+        if (lane == 0) out[o] = (uint8_t)sym;
+        ++o;
         continue;
       }
       if (sym == 256) {
@@ -362,56 +402,23 @@ BOP_HD_NOINLINE int inflate_run(State& s, Tables& t) {
         dist = ((2u + (ds & 1u)) << eb) + 1u + br.bits(eb);
       }
       if (dist > o || o + len > cap) { ev = dist > o ? EV_BAD_DISTANCE : EV_OVERFLOW; goto done; }
-      if (len >= kCoopMin) {
-        s.m_len = len;
-        s.m_dist = dist;
-        ev = EV_COPY;
-        goto done;
-      }
-      // 3 <= len < kCoopMin.  Without overlap every load is issued before the first store (one
-      // memory round trip, not one per byte) and the two switches execute exactly len loads and
-      // len stores.
-      const uint8_t* src = out + o - dist;
-      uint8_t* dst = out + o;
-      o += len;
-      if (dist >= len) {
-        uint8_t b0, b1, b2, b3 = 0, b4 = 0, b5 = 0, b6 = 0, b7 = 0, b8 = 0, b9 = 0, b10 = 0, b11 = 0,
-                b12 = 0, b13 = 0, b14 = 0;
-        switch (len) {
-          case 15: b14 = src[14];  // fallthrough
-          case 14: b13 = src[13];  // fallthrough
-          case 13: b12 = src[12];  // fallthrough
-          case 12: b11 = src[11];  // fallthrough
-          case 11: b10 = src[10];  // fallthrough
-          case 10: b9 = src[9];    // fallthrough
-          case 9: b8 = src[8];     // fallthrough
-          case 8: b7 = src[7];     // fallthrough
-          case 7: b6 = src[6];     // fallthrough
-          case 6: b5 = src[5];     // fallthrough
-          case 5: b4 = src[4];     // fallthrough
-          case 4: b3 = src[3];     // fallthrough
-          default: b2 = src[2]; b1 = src[1]; b0 = src[0];
+      // The match, copied by all lanes: every source byte lies in the window [o - dist, o) that was
+      // complete before this match began (i % dist wraps an overlapping match onto it), so one
+      // pass needs no ordering inside the match; the barrier orders it behind the stores that
+      // filled the window (lane 0's literals, earlier matches).
+      {
+        BOP_PNG_WARP_SYNC();
+        const uint8_t* src = out + o - dist;
+        uint8_t* dst = out + o;
+        o += len;
+        if (dist >= len) {
+          for (uint32_t i = (uint32_t)lane; i < len; i += (uint32_t)nlanes) dst[i] = src[i];
+        } else if (dist == 1) {
+          const uint8_t v = src[0];
+          for (uint32_t i = (uint32_t)lane; i < len; i += (uint32_t)nlanes) dst[i] = v;
+        } else {
+          for (uint32_t i = (uint32_t)lane; i < len; i += (uint32_t)nlanes) dst[i] = src[i % dist];
         }
-        switch (len) {
-          case 15: dst[14] = b14;  // fallthrough
-          case 14: dst[13] = b13;  // fallthrough
-          case 13: dst[12] = b12;  // fallthrough
-          case 12: dst[11] = b11;  // fallthrough
-          case 11: dst[10] = b10;  // fallthrough
-          case 10: dst[9] = b9;    // fallthrough
-          case 9: dst[8] = b8;     // fallthrough
-          case 8: dst[7] = b7;     // fallthrough
-          case 7: dst[6] = b6;     // fallthrough
-          case 6: dst[5] = b5;     // fallthrough
-          case 5: dst[4] = b4;     // fallthrough
-          case 4: dst[3] = b3;     // fallthrough
-          default: dst[2] = b2; dst[1] = b1; dst[0] = b0;
-        }
-      } else if (dist == 1) {
-        const uint8_t v = src[0];
-        for (uint32_t k = 0; k < len; ++k) dst[k] = v;
-      } else {
-        for (uint32_t k = 0; k < len; ++k) dst[k] = src[k];
       }
     }
   }

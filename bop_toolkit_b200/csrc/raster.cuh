@@ -151,10 +151,16 @@ __device__ __forceinline__ float plane_iz(float pa, float rowbase, float fdx) {
 // The store is a predicated shared-memory reduction (cover >= 0 <=> the three biased edge
 // functions are all non-negative): no branch in the per-candidate loop.
 #ifndef BOP_ZMERGE_SELECT
-#define BOP_ZMERGE_SELECT 1
+#define BOP_ZMERGE_SELECT 2
 #endif
 __device__ __forceinline__ void z_merge_if(unsigned saddr, float iz, int cover) {
-#if BOP_ZMERGE_SELECT
+#if BOP_ZMERGE_SELECT == 2
+  // branch-free: an uncovered candidate (cover < 0) gets the sign bit and, merged as a signed
+  // integer, never wins against a tile entry (>= 0); one LOP3 (a | (b & imm)) per candidate
+  const int v = __float_as_int(iz) | (cover & (int)0x80000000);
+  asm volatile("red.shared.max.s32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
+  return;
+#elif BOP_ZMERGE_SELECT
   // branch-free variant: an uncovered candidate merges 0, which never wins
   const int v = __float_as_int(iz) & ~(cover >> 31);
   asm volatile("red.shared.max.s32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
