@@ -87,6 +87,23 @@ def make_cases(d, seed=0):
   return cases
 
 
+def make_periodic_cases(d):
+  """Images whose rows repeat with a period of p pixels: zlib codes them as overlapping matches
+  (distance 2p < length 258), the `src[i % dist]` path of the decoder's all-lane match copy --
+  below, at and above the 32 lanes of a warp -- plus a period beyond the longest match."""
+  rng = np.random.default_rng(9)
+  cases = []
+  for period in (1, 3, 5, 16, 17, 200):
+    base = rng.integers(1, 60000, size=period).astype(np.uint16)
+    im = np.tile(base, (H, W // period + 1))[:, :W].copy()
+    im[H // 2:] = np.roll(im[H // 2:], 1, axis=1)          # a second phase, so rows are not all equal
+    for lvl, filt in ((6, [0]), (9, [1])):
+      p = os.path.join(d, 'periodic_%d_l%d_f%d.png' % (period, lvl, filt[0]))
+      write_png16(p, im, filt, lvl)
+      cases.append((p, im))
+  return cases
+
+
 def _scan(path):
   buf = bytearray(open(path, 'rb').read())
   cb = (ctypes.c_uint8 * len(buf)).from_buffer(buf)
@@ -117,6 +134,10 @@ def test_decoder_source_on_host_matches_opencv(tmp_path):
   cv2.imwrite(p, odd)
   rc, out = _host_twin(p, 37, 53)
   assert rc == 0 and np.array_equal(out, odd)
+  for path, im in make_periodic_cases(str(tmp_path)):
+    assert np.array_equal(cv2.imread(path, cv2.IMREAD_UNCHANGED), im), path
+    rc, out = _host_twin(path, H, W)
+    assert rc == 0 and np.array_equal(out, im), path
 
 
 def test_staging_compacts_idat_and_reports_per_file_status(tmp_path):
@@ -217,6 +238,11 @@ def test_gpu_decode_matches_opencv(tmp_path):
   assert out.shape == (len(cases), H, W) and out.dtype == torch.int16 and out.is_cuda
   got = out.cpu().numpy().view(np.uint16)
   for i, (path, im) in enumerate(cases):
+    assert np.array_equal(got[i], im), path
+  # overlapping matches (distance < length), copied by all lanes with src[i % dist]
+  per = make_periodic_cases(str(tmp_path))
+  got = batch.decode_depth_pngs([c[0] for c in per], H, W, 'cuda:0', threads=4).cpu().numpy().view(np.uint16)
+  for i, (path, im) in enumerate(per):
     assert np.array_equal(got[i], im), path
   # many images: more than one wave of warps
   many = paths * 12
