@@ -194,6 +194,19 @@ geometry_kernel(const __grid_constant__ GeomArgs g) {
     fx = c[0]; fy = c[1]; cx = c[2]; cy = c[3];
   }
   if (M.n_pts > g.pv_stride || M.n_faces > g.tri_cap) __trap();   // max_geom below the model's size: fail loudly
+  if (n_poses == 2 && tid > 0 && tid < cnt) {
+    // the pairs of a group must share object, image, GT pose and diameter (bop_vsd_grouped_dev's
+    // contract; batch.group_pairs_by_gt builds such groups): anything else would silently score
+    // the estimates of pair first + tid against the wrong GT render -- fail loudly instead
+    bool same = g.obj_idx[first + tid] == g.obj_idx[first];
+    if (g.cam_mode == 0) same = same && g.im_idx[first + tid] == g.im_idx[first];
+    if (g.diameters) same = same && g.diameters[first + tid] == g.diameters[first];
+    const long long* a = (const long long*)(g.pose_b + 12 * (size_t)first);
+    const long long* b = (const long long*)(g.pose_b + 12 * (size_t)(first + tid));
+#pragma unroll
+    for (int k = 0; k < 12; ++k) same = same && a[k] == b[k];
+    if (!same) __trap();
+  }
   if (tid < cnt)
     s_act[tid] = (g.gate && n_poses == 2) ? (sphere_projections_overlap(0.5 * diam, pose_of(tid) + 9, pose_of(cnt) + 9) ? 1 : 0) : 1;
   if (tid < 4) s_box[tid] = (tid & 2) ? INT_MIN : INT_MAX;

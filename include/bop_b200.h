@@ -218,7 +218,8 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * estimate of an object with every GT pose of it, so a GT pose is typically evaluated against
  * several estimates.  group_off_host (HOST array, [n_groups + 1], group_off_host[0] = 0,
  * group_off_host[n_groups] = n_pairs) cuts the batch into groups of 1 .. 32 consecutive pairs
- * with the same obj_idx, im_idx, pose_gt and diameter (the caller sorts; the library trusts it).
+ * with the same obj_idx, im_idx, pose_gt and diameter (the caller sorts, batch.group_pairs_by_gt
+ * does; a group that mixes them is a contract violation and traps the kernel).
  * The GT pose of a group is projected, sorted and rasterised once; its z-tile stays in shared
  * memory while the estimates of the group take turns.  Results are bit-identical to bop_vsd_dev
  * on the same pairs (tests/test_gpu_parity.py::test_vsd_grouped_equals_ungrouped). */
