@@ -87,13 +87,13 @@ struct SymMaxSmem {
   double xf[BOP_MAX_SYMS_PER_CTA][12];
   double Pe[12];
   unsigned long long symmax[BOP_MAX_SYMS_PER_CTA];
-  // Running maximum of every lane per symmetry (32 KB): the cross-lane reduction happens once
-  // per CTA and symmetry instead of once per 128 points and symmetry.  (The float32 paths keep
-  // their maxima in the same storage, widened to double when written.)
+  // float64 paths: running maximum of every lane per symmetry (32 KB): the cross-lane reduction
+  // happens once per CTA and symmetry instead of once per 128 points and symmetry.  (The float32
+  // paths keep theirs in registers, four symmetries at a time.)
   double run[kWarps][BOP_MAX_SYMS_PER_CTA][32];
   // float32 copies for the float32 per-vertex paths: xg = dR|dt (MSSD) or P_gs (MSPD); xd = P_e - P_gs (MSPD)
-  float xg[BOP_MAX_SYMS_PER_CTA][12];
-  float xd[BOP_MAX_SYMS_PER_CTA][12];
+  alignas(16) float xg[BOP_MAX_SYMS_PER_CTA][12];   // rows read as three float4
+  alignas(16) float xd[BOP_MAX_SYMS_PER_CTA][12];
 };
 
 // 1/x for the projections: the hardware's 20-bit float64 seed (MUFU.RCP64H) + one Newton step,
@@ -177,9 +177,11 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
   }
-  for (int i = tid; i < kWarps * ns * 32; i += kThreads) {   // only the symmetries this CTA owns
-    const int wi = i / (ns * 32);
-    (&sm.run[wi][0][0])[i - wi * ns * 32] = 0.0;
+  if (!F32) {
+    for (int i = tid; i < kWarps * ns * 32; i += kThreads) {   // only the symmetries this CTA owns
+      const int wi = i / (ns * 32);
+      (&sm.run[wi][0][0])[i - wi * ns * 32] = 0.0;
+    }
   }
   if (MODE == 1 && tid == 32) {
     const double* Kp = Kmat + 9 * (size_t)pair;
@@ -197,49 +199,75 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
   const PT* __restrict__ pts = (const PT*)M.pts;
   const int N = M.n_pts;
   const int warp = tid >> 5, lane = tid & 31;
-  if (MODE == 1 && F32) {
-    // MSPD, float32: per (point, symmetry) n = P_gs [p; 1] and D = (P_e - P_gs) [p; 1] (18 FFMA),
-    // then du = (D.x n.w - n.x D.w) / (n.w (n.w + D.w)) (likewise dv): the projections themselves
+  if (F32) {
+    // float32 sweeps.  A warp takes 128 points (4 per lane; the last pass repeats point N-1, which
+    // cannot change a maximum) and visits the CTA's symmetries four at a time with their running
+    // maxima in registers: one warp reduction per (warp, symmetry) at the end, nothing per pass.
+    // MSSD: |dR p + dt|^2 with dR, dt folded in float64 and rounded once (9 FFMA + 3 for the norm).
+    // MSPD: per (point, symmetry) n = P_gs [p; 1] and D = (P_e - P_gs) [p; 1] (18 FFMA), then
+    // du = (D.x n.w - n.x D.w) / (n.w (n.w + D.w)) (likewise dv): the projections themselves
     // (hundreds of pixels) never meet, only their difference is formed, from factors that are
     // each good to ~1e-7 relative.  One MUFU reciprocal per (point, symmetry).
-    constexpr int kPerLane = 4;
+    constexpr int kPerLane = 4, kSymChunk = 4;
     const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
-    for (int pass = warp; pass < npass; pass += kWarps) {
-      float px[kPerLane], py[kPerLane], pz[kPerLane];
-      bool ok[kPerLane];
+    for (int c0 = 0; c0 < ns; c0 += kSymChunk) {
+      const int nc = min(kSymChunk, ns - c0);
+      float runmax[kSymChunk];
 #pragma unroll
-      for (int k = 0; k < kPerLane; ++k) {
-        const int i = (pass * kPerLane + k) * 32 + lane;
-        ok[k] = i < N;
-        px[k] = py[k] = pz[k] = 0.f;
-        if (ok[k]) {
+      for (int j = 0; j < kSymChunk; ++j) runmax[j] = 0.f;
+      for (int pass = warp; pass < npass; pass += kWarps) {
+        float px[kPerLane], py[kPerLane], pz[kPerLane];
+#pragma unroll
+        for (int k = 0; k < kPerLane; ++k) {
+          const int i = min((pass * kPerLane + k) * 32 + lane, N - 1);
           px[k] = (float)__ldg(pts + 3 * (size_t)i + 0);
           py[k] = (float)__ldg(pts + 3 * (size_t)i + 1);
           pz[k] = (float)__ldg(pts + 3 * (size_t)i + 2);
         }
-      }
-      for (int sy = 0; sy < ns; ++sy) {
-        float G[12], D[12];
 #pragma unroll
-        for (int k = 0; k < 12; ++k) { G[k] = sm.xg[sy][k]; D[k] = sm.xd[sy][k]; }
-        float m2 = 0.f;
+        for (int j = 0; j < kSymChunk; ++j) {
+          if (j < nc) {
+            const float4* g4 = reinterpret_cast<const float4*>(sm.xg[c0 + j]);
+            const float4 g0 = g4[0], g1 = g4[1], g2 = g4[2];
+            float m2 = runmax[j];
+            if (MODE == 0) {
+              // T = dR row-major (g0.x .. g2.x), dt = (g2.y, g2.z, g2.w)
 #pragma unroll
-        for (int k = 0; k < kPerLane; ++k) {
-          if (ok[k]) {
-            const float nx = fmaf(G[0], px[k], fmaf(G[1], py[k], fmaf(G[2], pz[k], G[3])));
-            const float ny = fmaf(G[4], px[k], fmaf(G[5], py[k], fmaf(G[6], pz[k], G[7])));
-            const float nw = fmaf(G[8], px[k], fmaf(G[9], py[k], fmaf(G[10], pz[k], G[11])));
-            const float dx = fmaf(D[0], px[k], fmaf(D[1], py[k], fmaf(D[2], pz[k], D[3])));
-            const float dy = fmaf(D[4], px[k], fmaf(D[5], py[k], fmaf(D[6], pz[k], D[7])));
-            const float dw = fmaf(D[8], px[k], fmaf(D[9], py[k], fmaf(D[10], pz[k], D[11])));
-            float inv;
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(nw * (nw + dw)));
-            const float du = fmaf(dx, nw, -(nx * dw)) * inv, dv = fmaf(dy, nw, -(ny * dw)) * inv;
-            const float d2 = fmaf(du, du, dv * dv);
-            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
+              for (int k = 0; k < kPerLane; ++k) {
+                const float dx = fmaf(g0.x, px[k], fmaf(g0.y, py[k], fmaf(g0.z, pz[k], g2.y)));
+                const float dy = fmaf(g0.w, px[k], fmaf(g1.x, py[k], fmaf(g1.y, pz[k], g2.z)));
+                const float dz = fmaf(g1.z, px[k], fmaf(g1.w, py[k], fmaf(g2.x, pz[k], g2.w)));
+                m2 = fmaxf(m2, fmaf(dx, dx, fmaf(dy, dy, dz * dz)));   // a NaN never wins, like fmax
+              }
+            } else {
+              const float4* d4 = reinterpret_cast<const float4*>(sm.xd[c0 + j]);
+              const float4 d0 = d4[0], d1 = d4[1], d2r = d4[2];
+#pragma unroll
+              for (int k = 0; k < kPerLane; ++k) {
+                const float nx = fmaf(g0.x, px[k], fmaf(g0.y, py[k], fmaf(g0.z, pz[k], g0.w)));
+                const float ny = fmaf(g1.x, px[k], fmaf(g1.y, py[k], fmaf(g1.z, pz[k], g1.w)));
+                const float nw = fmaf(g2.x, px[k], fmaf(g2.y, py[k], fmaf(g2.z, pz[k], g2.w)));
+                const float dx = fmaf(d0.x, px[k], fmaf(d0.y, py[k], fmaf(d0.z, pz[k], d0.w)));
+                const float dy = fmaf(d1.x, px[k], fmaf(d1.y, py[k], fmaf(d1.z, pz[k], d1.w)));
+                const float dw = fmaf(d2r.x, px[k], fmaf(d2r.y, py[k], fmaf(d2r.z, pz[k], d2r.w)));
+                float inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(nw * (nw + dw)));
+                const float du = fmaf(dx, nw, -(nx * dw)) * inv, dv = fmaf(dy, nw, -(ny * dw)) * inv;
+                m2 = fmaxf(m2, fmaf(du, du, dv * dv));
+              }
+            }
+            runmax[j] = m2;
           }
         }
-        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], (double)m2);
+      }
+#pragma unroll
+      for (int j = 0; j < kSymChunk; ++j) {
+        if (j < nc) {
+          float m = runmax[j];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(BOP_FULL_MASK, m, o));
+          if (lane == 0) atomicMax(&symmax[c0 + j], (unsigned long long)__double_as_longlong((double)m));
+        }
       }
     }
   }
@@ -288,43 +316,6 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
       }
     }
   }
-  if (MODE == 0 && F32) {
-    // MSSD, float32: |dR p + dt|^2 with dR, dt folded in float64 and rounded once.
-    constexpr int kPerLane = 4;
-    const int npass = (N + 32 * kPerLane - 1) / (32 * kPerLane);
-    for (int pass = warp; pass < npass; pass += kWarps) {
-      float px[kPerLane], py[kPerLane], pz[kPerLane];
-      bool ok[kPerLane];
-#pragma unroll
-      for (int k = 0; k < kPerLane; ++k) {
-        const int i = (pass * kPerLane + k) * 32 + lane;
-        ok[k] = i < N;
-        px[k] = py[k] = pz[k] = 0.f;
-        if (ok[k]) {
-          px[k] = (float)__ldg(pts + 3 * (size_t)i + 0);
-          py[k] = (float)__ldg(pts + 3 * (size_t)i + 1);
-          pz[k] = (float)__ldg(pts + 3 * (size_t)i + 2);
-        }
-      }
-      for (int sy = 0; sy < ns; ++sy) {
-        float T[12];
-#pragma unroll
-        for (int k = 0; k < 12; ++k) T[k] = sm.xg[sy][k];
-        float m2 = 0.f;
-#pragma unroll
-        for (int k = 0; k < kPerLane; ++k) {
-          if (ok[k]) {
-            const float dx = fmaf(T[0], px[k], fmaf(T[1], py[k], fmaf(T[2], pz[k], T[9])));
-            const float dy = fmaf(T[3], px[k], fmaf(T[4], py[k], fmaf(T[5], pz[k], T[10])));
-            const float dz = fmaf(T[6], px[k], fmaf(T[7], py[k], fmaf(T[8], pz[k], T[11])));
-            const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            m2 = d2 > m2 ? d2 : m2;   // NaN never wins, like fmax
-          }
-        }
-        sm.run[warp][sy][lane] = fmax(sm.run[warp][sy][lane], (double)m2);
-      }
-    }
-  }
   if (MODE == 0 && !F32) {
     // MSSD: same sweep -- a warp keeps 128 points in registers and visits every symmetry, so the
     // points are loaded (and converted to float64) once instead of once per symmetry.
@@ -360,11 +351,13 @@ sym_max_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_e
     }
   }
   __syncthreads();
-  for (int sy = 0; sy < ns; ++sy) {   // 256 running maxima per symmetry -> one value
-    const double m = warp_max(sm.run[warp][sy][lane]);
-    if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m));
+  if (!F32) {
+    for (int sy = 0; sy < ns; ++sy) {   // 256 running maxima per symmetry -> one value
+      const double m = warp_max(sm.run[warp][sy][lane]);
+      if (lane == 0) atomicMax(&symmax[sy], (unsigned long long)__double_as_longlong(m));
+    }
+    __syncthreads();
   }
-  __syncthreads();
   if (tid == 0) {
     unsigned long long best = symmax[0];
     for (int s = 1; s < ns; ++s) best = min(best, symmax[s]);
