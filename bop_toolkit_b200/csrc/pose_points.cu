@@ -15,8 +15,10 @@
 // model) MSSD evaluates |dR p + dt|^2 in float32 and MSPD evaluates the difference of the two
 // projections as (D.x n.w - n.x D.w) / (n.w (n.w + D.w)) with n = K [R_gs | t_gs] [p; 1] and
 // D = (K [R_e | t_e] - K [R_gs | t_gs]) [p; 1] in float32: every factor is good to ~1e-7 relative
-// and the error of the result stays below 1e-6 relative (bar: 1e-5).  Models whose points are not
-// float32-representable, ADD / PROJ sums and the final square roots stay in float64.  ADI runs in
+// and the error of the result stays below 1e-6 relative (bar: 1e-5).  ADD / PROJ use the same two
+// per-vertex forms and add the norms up in float64.  Models whose points are not float32-
+// representable, ill-conditioned projections (a vertex within 10 % of the camera plane) and the
+// final square roots / means stay in float64.  ADI runs in
 // the estimated model frame (distances are invariant under the rigid map R_e^T(. - t_e)), so the
 // search set is the static model.
 #include "common.cuh"
@@ -408,7 +410,7 @@ sym_max_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restri
 // K3: mean errors (ADD / PROJ).  grid = (n_pairs, splits); partial sums are combined with
 // one double atomicAdd per CTA into sum[]; a finalize kernel divides by N / applies the gate.
 // ---------------------------------------------------------------------------------
-template <typename PT, int MODE>  // MODE 0 = ADD, 1 = PROJ
+template <typename PT, int MODE, bool F32>  // MODE 0 = ADD, 1 = PROJ; F32: float32 per-vertex arithmetic
 __device__ __forceinline__ void
 mean_err_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_est,
               const double* __restrict__ pose_gt, const double* __restrict__ Kmat, int gate,
@@ -440,7 +442,35 @@ mean_err_body(const bop_model_dev& M, int pair, const double* __restrict__ pose_
   }
   const PT* __restrict__ pts = (const PT*)M.pts;
   double acc = 0.0;
-  for (int i = i0 + threadIdx.x; i < i1; i += kThreads) {
+  if (F32) {
+    // float32 per vertex as in the MSSD / MSPD sweeps (dR, dt and P_e - P_g are folded in float64
+    // above and rounded once); the norms are summed in float64.
+    float G[12], D[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) { G[k] = (float)T[k]; D[k] = MODE == 1 ? (float)(Pe[k] - T[k]) : 0.f; }
+    for (int i = i0 + threadIdx.x; i < i1; i += kThreads) {
+      const float x = (float)__ldg(pts + 3 * (size_t)i + 0), y = (float)__ldg(pts + 3 * (size_t)i + 1),
+                  z = (float)__ldg(pts + 3 * (size_t)i + 2);
+      if (MODE == 0) {
+        const float dx = fmaf(G[0], x, fmaf(G[1], y, fmaf(G[2], z, G[9])));
+        const float dy = fmaf(G[3], x, fmaf(G[4], y, fmaf(G[5], z, G[10])));
+        const float dz = fmaf(G[6], x, fmaf(G[7], y, fmaf(G[8], z, G[11])));
+        acc += (double)sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+      } else {
+        const float nx = fmaf(G[0], x, fmaf(G[1], y, fmaf(G[2], z, G[3])));
+        const float ny = fmaf(G[4], x, fmaf(G[5], y, fmaf(G[6], z, G[7])));
+        const float nw = fmaf(G[8], x, fmaf(G[9], y, fmaf(G[10], z, G[11])));
+        const float dx = fmaf(D[0], x, fmaf(D[1], y, fmaf(D[2], z, D[3])));
+        const float dy = fmaf(D[4], x, fmaf(D[5], y, fmaf(D[6], z, D[7])));
+        const float dw = fmaf(D[8], x, fmaf(D[9], y, fmaf(D[10], z, D[11])));
+        float inv;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(nw * (nw + dw)));
+        const float du = fmaf(dx, nw, -(nx * dw)) * inv, dv = fmaf(dy, nw, -(ny * dw)) * inv;
+        acc += (double)sqrtf(fmaf(du, du, dv * dv));
+      }
+    }
+  }
+  for (int i = i0 + threadIdx.x; !F32 && i < i1; i += kThreads) {
     double x, y, z;
     load_pt(pts, i, x, y, z);
     if (MODE == 0) {
@@ -474,14 +504,27 @@ template <int MODE>
 __global__ void __launch_bounds__(kThreads)
 mean_err_kernel(const bop_model_dev* __restrict__ models, const int32_t* __restrict__ obj_idx,
                 const double* __restrict__ pose_est, const double* __restrict__ pose_gt,
-                const double* __restrict__ Kmat, int gate, double* __restrict__ sum) {
+                const double* __restrict__ Kmat, int gate, int exact64, double* __restrict__ sum) {
   __shared__ double wsum[kWarps];
   const int pair = blockIdx.x;
   const bop_model_dev M = models[obj_idx[pair]];
+  bool f32 = !M.pts_f64 && !exact64;
+  if (MODE == 1 && f32) {
+    // same conditioning test as MSPD: every vertex of both poses at >= 10 % of the centre's depth
+    const double* Kp = Kmat + 9 * (size_t)pair;
+    const double kr = sqrt(Kp[6] * Kp[6] + Kp[7] * Kp[7] + Kp[8] * Kp[8]) * (double)M.cull_min_dist;
+    const double* te = pose_est + 12 * (size_t)pair + 9;
+    const double* tg = pose_gt + 12 * (size_t)pair + 9;
+    const double we = Kp[6] * te[0] + Kp[7] * te[1] + Kp[8] * te[2];
+    const double wg = Kp[6] * tg[0] + Kp[7] * tg[1] + Kp[8] * tg[2];
+    f32 = we - kr >= 0.1 * we && wg - kr >= 0.1 * wg;
+  }
   if (M.pts_f64)
-    mean_err_body<double, MODE>(M, pair, pose_est, pose_gt, Kmat, gate, sum, wsum);
+    mean_err_body<double, MODE, false>(M, pair, pose_est, pose_gt, Kmat, gate, sum, wsum);
+  else if (!f32)
+    mean_err_body<float, MODE, false>(M, pair, pose_est, pose_gt, Kmat, gate, sum, wsum);
   else
-    mean_err_body<float, MODE>(M, pair, pose_est, pose_gt, Kmat, gate, sum, wsum);
+    mean_err_body<float, MODE, true>(M, pair, pose_est, pose_gt, Kmat, gate, sum, wsum);
 }
 
 // out[i] = gated ? +inf : out[i] / n_pts   (in place on the sum buffer)
@@ -625,7 +668,7 @@ extern "C" int bop_re_te_dev(const double* pose_est, const double* pose_gt, int 
   return 0;
 }
 
-static int g_points_exact = 0;   // bop_points_set_exact: float64 per-vertex arithmetic for MSSD / MSPD (tests)
+static int g_points_exact = 0;   // bop_points_set_exact: float64 per-vertex arithmetic for MSSD / MSPD / ADD / PROJ (tests)
 
 // Test hook: exact != 0 makes MSSD / MSPD evaluate every vertex in float64 (the reference's dtype)
 // instead of the float32 forms described at the top of this file; tests compare the two.
@@ -688,9 +731,9 @@ static int launch_mean(int mode, const bop_model_dev* models, const int32_t* obj
   while (n_pairs * splits < want_ctas && max_pts / (splits + 1) >= 4 * kThreads) ++splits;
   dim3 grid(n_pairs, splits);
   if (mode == 0)
-    mean_err_kernel<0><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, gate, out);
+    mean_err_kernel<0><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, gate, g_points_exact, out);
   else
-    mean_err_kernel<1><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, 0, out);
+    mean_err_kernel<1><<<grid, kThreads, 0, s>>>(models, obj_idx, pose_est, pose_gt, K, 0, g_points_exact, out);
   BOP_LAUNCH_CHECK();
   mean_finalize_kernel<<<(n_pairs + 255) / 256, 256, 0, s>>>(models, obj_idx, pose_est, pose_gt,
                                                             n_pairs, mode == 0 ? gate : 0, out);

@@ -427,8 +427,8 @@ def test_wide_image(B, oracle_built):
 
 
 def test_point_errors_float32_fold_vs_float64(B):
-  """MSSD / MSPD evaluate float32-exact model points in float32 AFTER folding the rigid parts in
-  float64 (pose_points.cu); bop_points_set_exact(1) forces the reference's float64 per vertex.
+  """MSSD / MSPD / ADD / PROJ evaluate float32-exact model points in float32 AFTER folding the rigid
+  parts in float64 (pose_points.cu); bop_points_set_exact(1) forces the reference's float64 per vertex.
   The two must agree to 1e-6 relative (bar: 1e-5) on close estimates, gross outliers, a skewed K,
   estimates that ARE a symmetry of the GT (errors ~ 0) and poses partly behind the camera."""
   from bop_toolkit_b200 import _lib, synth, misc
@@ -457,10 +457,12 @@ def test_point_errors_float32_fold_vs_float64(B):
   try:
     for exact in (1, 0):
       _lib.check(lib.bop_points_set_exact(exact))
-      out[exact] = (B.mssd_batch(ms, 0, pe, pg).cpu().numpy(), B.mspd_batch(ms, 0, pe, pg, Ks).cpu().numpy())
+      out[exact] = (B.mssd_batch(ms, 0, pe, pg).cpu().numpy(), B.mspd_batch(ms, 0, pe, pg, Ks).cpu().numpy(),
+                    B.add_batch(ms, 0, pe, pg).cpu().numpy(), B.proj_batch(ms, 0, pe, pg, Ks).cpu().numpy())
   finally:
     _lib.check(lib.bop_points_set_exact(0))
-  for name, a, b in (('mssd', out[1][0], out[0][0]), ('mspd', out[1][1], out[0][1])):
+  for k, name in enumerate(('mssd', 'mspd', 'add', 'proj')):
+    a, b = out[1][k], out[0][k]
     fin = np.isfinite(a)
     assert np.array_equal(fin, np.isfinite(b)), name
     rel = np.abs(a[fin] - b[fin]) / np.maximum(np.abs(a[fin]), 1e-6)   # 1e-6 mm / px floor for the ~0 cases
