@@ -221,13 +221,22 @@ class ModelSet(object):
 
 
 class Workspace(object):
-  """Grow-only device scratch buffer (256-byte aligned by the caching allocator)."""
+  """Grow-only device scratch buffer (256-byte aligned by the caching allocator), ONE per device:
+  every batched call on the device uses it, so calls are ordered behind each other -- a call
+  issued on another stream than the previous one first waits for that stream (the library keeps
+  its work counters in the buffer; overlapping calls would race)."""
 
   def __init__(self, device):
     self.device = device
     self.buf = None
+    self.stream = None
 
   def get(self, nbytes):
+    cur = torch.cuda.current_stream(self.device)
+    if self.stream is not None and self.stream != cur and not torch.cuda.is_current_stream_capturing():
+      cur.wait_stream(self.stream)
+    if not torch.cuda.is_current_stream_capturing():
+      self.stream = cur
     if self.buf is None or self.buf.numel() < nbytes:
       self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
     return self.buf

@@ -507,3 +507,39 @@ def test_triangle_lists_are_sorted_by_band_and_class(B):
         cost += int(np.where(H_ > r, W_, 0).max(1).sum())
       assert (W_ * H_).sum() >= 0.8 * 32 * cost           # >= 80 % of the lane-slots of the pixel loops are used
   assert n_multi > 0                                       # some ROI needed more than one band
+
+
+def test_calls_on_two_streams_share_the_workspace_in_order(B):
+  """Every batched call on a device uses ONE scratch buffer (batch.Workspace; the library keeps
+  its work lists and counters there).  A call issued on another stream than the previous one
+  must therefore wait for it: two different batches launched back to back on two streams give
+  the results each gives alone."""
+  import torch
+  from bop_toolkit_b200 import synth
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(40, 80, 200.0, seed=51)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  n = 1500
+  cases = []
+  for seed in (52, 53):
+    R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=seed, z_range=(400.0, 1200.0), outlier_frac=0.05)
+    cases.append((B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)))
+  depth = torch.full((1, 480, 640), 900.0, dtype=torch.float32, device=ms.device)
+  im = np.zeros(n, np.int32)
+  Ks = K.reshape(1, 9)
+  taus = [0.05 * (k + 1) for k in range(10)]
+  run = lambda pe, pg: B.vsd_batch(ms, 0, pe, pg, depth, im, Ks, 15, taus, True, 'step', return_counts=True)
+  want = [tuple(x.cpu().numpy() for x in run(*c)) for c in cases]
+  torch.cuda.synchronize()
+  streams = [torch.cuda.Stream(ms.device), torch.cuda.Stream(ms.device)]
+  for rep in range(3):
+    got = []
+    for s_, c in zip(streams, cases):
+      s_.wait_stream(torch.cuda.current_stream())
+      with torch.cuda.stream(s_):
+        got.append(run(*c))
+    torch.cuda.synchronize()
+    for (e1, c1), (e0, c0) in zip(got, want):
+      assert np.array_equal(c1.cpu().numpy(), c0) and np.array_equal(e1.cpu().numpy(), e0, equal_nan=True)
+  assert not np.array_equal(want[0][1], want[1][1])
