@@ -152,7 +152,10 @@ int bop_adi_dev(const bop_model_dev* models, const int32_t* obj_idx,
  * (the assembled-triangle list: 2 * max_geom records of 36 bytes per pose).  A smaller value
  * is a contract violation and traps the kernel.
  * workspace: bop_render_workspace_bytes(n, H, W, max_geom) bytes of device memory, 256-byte
- * aligned.  Batches whose scratch would exceed 8 GiB are processed in several passes.   */
+ * aligned.  Batches whose scratch would exceed 8 GiB are processed in several passes.  A
+ * workspace holds the call's triangle lists and work counters until the call has finished on
+ * the GPU: calls that share one must be stream-ordered (this holds for every workspace argument
+ * in this header).   */
 size_t bop_render_workspace_bytes(int n, int height, int width, int max_geom);
 int bop_render_depth_dev(const bop_model_dev* models, const int32_t* obj_idx,
                          const double* pose, const double* cam, int n, int max_geom,
