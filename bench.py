@@ -398,6 +398,109 @@ def gpu_arm(args):
     h_out.copy_(errs, non_blocking=True)
     return errs
 
+  # The same end-to-end step on an SM partition (sm_partition.py): the pairs are split in two
+  # sub-batches in proportion to the SMs of the two green contexts and issued on their streams;
+  # nothing orders the two streams against each other from step to step, so one partition's
+  # PCIe-bound pixel pass runs while the other one's geometry / MSSD / MSPD kernels compute.
+  part_state = {}
+
+  def part_setup(sms_a):
+    from bop_toolkit_b200 import sm_partition
+    part = sm_partition.SmPartition(local_rank, sms_a)
+    n_a = int(round(P * part.sm_counts[0] / float(sum(part.sm_counts))))
+    # a partition may take its share in several pieces per step: pieces of different length on the
+    # two streams keep them from falling into lockstep (both in their PCIe-bound phase at once)
+    pieces = [max(1, int(x)) for x in args.e2e_pieces.split(',')]
+    cuts = []
+    for (lo, hi), n_p in zip(((0, n_a), (n_a, P)), pieces):
+      edges = [lo + (hi - lo) * j // n_p for j in range(n_p + 1)]
+      cuts.append([slice(edges[j], edges[j + 1]) for j in range(n_p) if edges[j + 1] > edges[j]])
+    part_state.update(part=part, cuts=cuts, ws=[batch.Workspace(device) for _ in range(max(2, args.e2e_depth))])
+    return part
+
+  def step_e2e_part_default(only=(0, 1)):
+    part, outs = part_state['part'], []
+    for k in only:
+      with torch.cuda.stream(part.streams[k]), batch.private_workspace(part_state['ws'][k]):
+        for sl in part_state['cuts'][k]:
+          vsd = batch.vsd_batch(ms, h_obj[sl], h_pe[sl], h_pg[sl], h_d16, h_im[sl], h_K, DELTA, TAUS, True, 'step',
+                                'bop19', gate=True, depth_scale=h_scale, zero_copy=True)
+          o, a, b = (x[sl].to(device, non_blocking=True) for x in (h_obj, h_pe, h_pg))
+          mssd = batch.mssd_batch(ms, o, a, b, gate=True)
+          mspd = batch.mspd_batch(ms, o, a, b, h_Kp[sl])
+          errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
+          h_out[sl].copy_(errs, non_blocking=True)
+          outs.append(errs)
+    if world > 1:   # the exchange runs on the main stream behind both partitions; they do not wait for it
+      cur = torch.cuda.current_stream()
+      for k in (0, 1):
+        cur.wait_stream(part.streams[k])
+      for o_ in outs:
+        o_.record_stream(cur)
+      sharding.gather_records(ids, torch.cat(outs, dim=0), counts=[P] * world)
+    return outs
+
+  # The same step as a two-stage pipeline over the two partitions: geometry + MSSD + MSPD of every
+  # step on the compute partition, the PCIe-bound raster + pixel pass (bop_vsd_split_dev), the
+  # assembly of the records and the D2H copy on the raster partition; two workspaces alternate.
+  def step_e2e_pipe():
+    part = part_state['part']
+    s_r, s_c = part.streams
+    k = part_state['k'] = (part_state.get('k', 0) + 1) % len(part_state['ws'])
+    with torch.cuda.stream(s_c), batch.private_workspace(part_state['ws'][k]):
+      if part_state.get('done%d' % k) is not None:   # this workspace's previous raster pass
+        s_c.wait_event(part_state['done%d' % k])
+      vsd = batch.vsd_batch(ms, h_obj, h_pe, h_pg, h_d16, h_im, h_K, DELTA, TAUS, True, 'step', 'bop19',
+                            gate=True, depth_scale=h_scale, zero_copy=True, raster_stream=s_r)
+      o, a, b = (x.to(device, non_blocking=True) for x in (h_obj, h_pe, h_pg))
+      mssd = batch.mssd_batch(ms, o, a, b, gate=True)
+      mspd = batch.mspd_batch(ms, o, a, b, h_Kp)
+      mssd.record_stream(s_r)
+      mspd.record_stream(s_r)
+      ev_c = torch.cuda.Event()
+      ev_c.record(s_c)
+    with torch.cuda.stream(s_r):
+      s_r.wait_event(ev_c)
+      errs = torch.cat([vsd, mssd.unsqueeze(1), mspd.unsqueeze(1)], dim=1)
+      h_out.copy_(errs, non_blocking=True)
+      ev_r = torch.cuda.Event()
+      ev_r.record(s_r)
+      part_state['done%d' % k] = ev_r
+    if world > 1:
+      cur = torch.cuda.current_stream()
+      cur.wait_stream(s_r)
+      errs.record_stream(cur)
+      sharding.gather_records(ids, errs, counts=[P] * world)
+    return [errs]
+
+  def timed_part(steps, warmup, step_e2e_part=None):
+    step_e2e_part = step_e2e_part or step_e2e_part_default
+    part = part_state['part']
+    cur = torch.cuda.current_stream()
+    for _ in range(warmup):
+      step_e2e_part()
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+    l0 = batch.kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for st in part.streams:
+      st.wait_stream(cur)
+    for _ in range(steps):
+      outs = step_e2e_part()
+    for st in part.streams:
+      cur.wait_stream(st)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), batch.kernel_launch_count() - l0, torch.cat(outs, dim=0)
+
   def timed(fn, steps, warmup):
     for _ in range(warmup):
       fn()
@@ -473,6 +576,41 @@ def gpu_arm(args):
   e2e_parts = kernel_parts(args.steps)
   depth_pulled = batch.depth_bytes_fetched(device, _lib.DEPTH_U16)
   ms_e2e_copy, _, _, out_e2e_copy = timed(lambda: step_e2e(False), max(1, args.steps // 2), 1)
+  # (3b) the same step on two SM partitions (skipped with --e2e-sms 0 or when green contexts are unavailable)
+  e2e_part = None
+  if args.e2e_sms > 0:
+    lib.bop_profile_enable(0)
+    try:
+      part = part_setup(args.e2e_sms)
+      if args.e2e_mode == 'pipe':   # every kernel has a partition to itself: the per-kernel events are meaningful
+        lib.bop_profile_enable(1)
+        lib.bop_profile_reset()
+      ms_part, _, out_part = timed_part(args.steps, args.warmup, step_e2e_pipe if args.e2e_mode == 'pipe' else None)
+      diag = None
+      if args.e2e_mode == 'pipe':
+        diag = {'kernels_ms': kernel_parts(args.steps)}
+        lib.bop_profile_enable(0)
+      if args.e2e_diag and args.e2e_mode != 'pipe':   # each sub-batch alone on its partition, with the library's per-kernel events
+        diag = {}
+        lib.bop_profile_enable(1)
+        for k in (0, 1):
+          for _ in range(2):
+            step_e2e_part_default((k,))
+          torch.cuda.synchronize()
+          lib.bop_profile_reset()
+          t0 = time.time()
+          for _ in range(4):
+            step_e2e_part_default((k,))
+          torch.cuda.synchronize()
+          diag['alone_%d' % k] = {'ms_per_step': (time.time() - t0) * 250.0, 'kernels_ms': kernel_parts(4)}
+        lib.bop_profile_enable(0)
+      e2e_part = {'ms': ms_part, 'sms': list(part.sm_counts), 'diag': diag, 'mode': args.e2e_mode,
+                  'pairs': [[c.stop - c.start for c in cs] for cs in part_state['cuts']],
+                  'same': bool(world > 1 or torch.equal(out_part, out_e2e))}
+      # the partition lives until the process ends: torch's allocator keeps blocks tied to its streams
+    except Exception as e:
+      e2e_part = {'error': str(e).splitlines()[0][:200]}
+    lib.bop_profile_enable(1)
   # (4) the opt-in back-face culling on the same step (closed synthetic meshes)
   ms_cull_t, _, _, out_cull = timed(lambda: step_resident(ms_cull), max(2, args.steps // 2), 2)
   cull_parts = kernel_parts(max(2, args.steps // 2))
@@ -529,6 +667,22 @@ def gpu_arm(args):
   h2d = small + depth_pulled
   h2d_copy = small + h_d16.numel() * h_d16.element_size()
   e2e_copy_v = P * world * max(1, args.steps // 2) / (ms_e2e_copy * 1e-3)
+  e2e_serial = {'value': e2e_v, 'ms_per_step': ms_e2e / args.steps, 'kernels_ms': e2e_parts,
+                'mode': 'one stream: geometry, fused (PCIe-bound), MSSD, MSPD one after the other'}
+  e2e_mode = 'pinned host buffers; depth pulled on demand over PCIe by the fused kernel'
+  e2e_ms_step = ms_e2e / args.steps
+  if e2e_part and 'ms' in e2e_part and e2e_part['same'] and e2e_part['ms'] < ms_e2e:
+    e2e_v = P * world * args.steps / (e2e_part['ms'] * 1e-3)
+    e2e_ms_step = e2e_part['ms'] / args.steps
+    if e2e_part['mode'] == 'pipe':
+      e2e_mode += ('; two-stage pipeline over two SM partitions (CUDA green contexts): the raster + pixel pass, the '
+                   'record assembly and the D2H copy on %d SMs, geometry + MSSD + MSPD of the next step on %d SMs '
+                   '(bop_vsd_split_dev; two workspaces alternate)' % (e2e_part['sms'][0], e2e_part['sms'][1]))
+    else:
+      e2e_mode += ('; the step is issued as sub-batches (%s + %s pairs) on the streams of two SM partitions '
+                   '(CUDA green contexts, %d + %d SMs) that run independently, so one partition\'s PCIe-bound pixel '
+                   'pass overlaps the other one\'s geometry / MSSD / MSPD kernels' %
+                   (e2e_part['pairs'][0], e2e_part['pairs'][1], e2e_part['sms'][0], e2e_part['sms'][1]))
   line = {
     'metric': 'pose-error pairs/sec (VSD+MSSD+MSPD)', 'value': value, 'unit': 'pairs/s',
     'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
@@ -544,10 +698,10 @@ def gpu_arm(args):
                'resident_depth': 'float32 mm in HBM', 'e2e_depth': 'uint16 samples + depth_scale (pinned host)',
                'exchange': 'all-gather of error records per step' if world > 1 else 'none',
                'cpu_affinity': bound},
-    'e2e': {'value': e2e_v, 'unit': 'pairs/s', 'ms_per_step': ms_e2e / args.steps,
+    'e2e': {'value': e2e_v, 'unit': 'pairs/s', 'ms_per_step': e2e_ms_step,
             'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(h_out.numel() * 8),
             'matches_resident': same, 'kernels_ms': e2e_parts,
-            'mode': 'pinned host buffers; depth pulled on demand over PCIe by the fused kernel',
+            'mode': e2e_mode, 'serial': e2e_serial, 'sm_partition': e2e_part,
             'full_copy': {'value': e2e_copy_v, 'h2d_bytes_per_step': int(h2d_copy),
                           'note': 'same call with whole-image H2D copies of the uint16 depth'}},
     'cull_auto': {'value': P * world * max(2, args.steps // 2) / (ms_cull_t * 1e-3), 'unit': 'pairs/s',
@@ -652,6 +806,13 @@ def main():
                   help='0: one image per pair (cfg2 as quoted); N: N shared images x pairs/N estimates each')
   ap.add_argument('--cpu-per-core', type=int, default=32, help='sample pairs per host worker of the CPU arm')
   ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--e2e-mode', default='pipe', choices=['pipe', 'part'],
+                  help='pipe: raster pass on one SM partition, geometry + point kernels on the other; part: two independent sub-batch streams')
+  ap.add_argument('--e2e-depth', type=int, default=2, help='workspaces the pipelined end-to-end leg alternates')
+  ap.add_argument('--e2e-pieces', default='1,1', help='sub-batches per step on the two partitions')
+  ap.add_argument('--e2e-diag', action='store_true', help='time each sub-batch alone on its SM partition')
+  ap.add_argument('--e2e-sms', type=int, default=96,
+                  help='SMs of the first of the two partitions of the end-to-end leg (0 = one stream only)')
   ap.add_argument('--cfg5-images', type=int, default=20000,
                   help='images of the cfg5 strong-scaling leg (BASELINE configs[4]); 0 skips it')
   args = ap.parse_args()

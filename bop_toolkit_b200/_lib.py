@@ -108,6 +108,8 @@ _SIGNATURES = {
   'bop_vsd_from_depth_static_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P]),
   'bop_vsd_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
                        _P]),
+  'bop_vsd_split_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, ctypes.c_size_t,
+                             _P, _P]),
   'bop_vsd_grouped_dev': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P,
                                ctypes.c_size_t, _P]),
   'bop_mask_overlap_dev': (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P,

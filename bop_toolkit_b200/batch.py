@@ -4,8 +4,10 @@ This is the fast path the drop-in facade (pose_error.py) and the driver (eval_ca
 sit on.  torch is used for device memory, streams and pinned staging only; all arithmetic runs
 in the hand-written sm_100a kernels behind the C ABI (include/bop_b200.h).
 """
+import contextlib
 import ctypes
 import os
+import threading
 
 import numpy as np
 import torch
@@ -243,9 +245,28 @@ class Workspace(object):
 
 
 _workspaces = {}
+_private = threading.local()
+
+
+@contextlib.contextmanager
+def private_workspace(ws):
+  """Batched calls inside the block (this thread) use `ws`, a Workspace the caller owns, instead
+  of the device's shared one: what calls that are meant to run concurrently on several streams
+  need -- one Workspace per stream."""
+  prev = getattr(_private, 'ws', None)
+  _private.ws = ws
+  try:
+    yield ws
+  finally:
+    _private.ws = prev
 
 
 def _workspace(device, nbytes):
+  ws = getattr(_private, 'ws', None)
+  if ws is not None:
+    if ws.device != device:
+      raise ValueError('private workspace lives on %s, the call runs on %s' % (ws.device, device))
+    return ws.get(nbytes)
   key = (device.type, device.index)
   ws = _workspaces.get(key)
   if ws is None:
@@ -432,8 +453,14 @@ def group_pairs_by_gt(obj, pose_gt, im_idx, diameter=None):
 def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus,
               normalized_by_diameter=True, cost_type='step', visib_mode='bop19', gate=False,
               depth_scale=None, return_counts=False, diameter_override=None, zero_copy=False,
-              group_off=None):
+              group_off=None, raster_stream=None):
   """pose_error.vsd for P pairs with the fused raster + pixel-pass kernel.
+
+  raster_stream (a torch stream): the geometry pass stays on the current stream, the raster +
+  pixel pass and the results go to raster_stream (bop_vsd_split_dev): for callers that give the
+  two passes an SM partition each (sm_partition.py) so that the PCIe-bound pixel pass of
+  host-resident depth overlaps the next batch's geometry pass.  The returned tensors are ready
+  on raster_stream; reuse the workspace (private_workspace) only behind it.
 
   group_off (host int32 [G + 1], from group_pairs_by_gt): consecutive pairs of a group share
   object, image, GT pose and diameter; the GT pose's geometry and raster work is then done once
@@ -486,7 +513,21 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
                             gate, code)
       err = torch.empty((n, len(chunk)), dtype=torch.float64, device=dev)
       cnt = torch.empty((n, 2 + len(chunk)), dtype=torch.int64, device=dev) if return_counts else None
-      if group_off is not None:
+      if raster_stream is not None:
+        if group_off is not None:
+          raise ValueError('raster_stream and group_off cannot be combined')
+        if outs:   # the previous tau chunk's raster pass still reads the workspace
+          torch.cuda.current_stream().wait_stream(raster_stream)
+        for t_ in (err, cnt, dd, sc):
+          if t_ is not None and t_.is_cuda:
+            t_.record_stream(raster_stream)
+        rc = _lib.lib().bop_vsd_split_dev(
+          models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
+          sc.data_ptr() if sc is not None else None, ii.data_ptr(), Kd.data_ptr(),
+          diam.data_ptr() if diam is not None else None, n, models.max_geom,
+          ctypes.byref(prm), err.data_ptr(), cnt.data_ptr() if cnt is not None else None,
+          ws.data_ptr(), wsb, _stream_ptr(), ctypes.c_void_p(raster_stream.cuda_stream))
+      elif group_off is not None:
         goff = np.ascontiguousarray(group_off, dtype=np.int32)
         rc = _lib.lib().bop_vsd_grouped_dev(
           models.table.data_ptr(), oi.data_ptr(), pe.data_ptr(), pg.data_ptr(), dd.data_ptr(),
@@ -504,10 +545,12 @@ def vsd_batch(models, obj, pose_est, pose_gt, depth_test, im_idx, K, delta, taus
       _lib.check(rc)
       outs.append(err)
       cnts.append(cnt)
-  err = outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
-  if return_counts:
-    cnt = cnts[0] if len(cnts) == 1 else torch.cat([cnts[0]] + [c[:, 2:] for c in cnts[1:]], dim=1)
-    return err, cnt
+  # several tau chunks are joined on the stream their values are ready on
+  with torch.cuda.stream(raster_stream) if raster_stream is not None and len(outs) > 1 else contextlib.nullcontext():
+    err = outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
+    if return_counts:
+      cnt = cnts[0] if len(cnts) == 1 else torch.cat([cnts[0]] + [c[:, 2:] for c in cnts[1:]], dim=1)
+      return err, cnt
   return err
 
 

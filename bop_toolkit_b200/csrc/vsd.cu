@@ -1603,7 +1603,7 @@ static int vsd_impl(const bop_model_dev* models, const int32_t* obj_idx, const d
                     const int32_t* im_idx, const double* K, const double* diameters, int n_pairs,
                     const int32_t* group_off_host, int n_groups, int max_geom,
                     const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
-                    void* workspace, size_t workspace_bytes, void* stream) {
+                    void* workspace, size_t workspace_bytes, void* stream, void* geometry_stream = nullptr) {
   if (n_pairs <= 0) return 0;
   BOP_REQUIRE(models && obj_idx && pose_est && pose_gt && depth_test && im_idx && K && errors_out,
               "bop_vsd_dev: null pointer");
@@ -1622,10 +1622,27 @@ static int vsd_impl(const bop_model_dev* models, const int32_t* obj_idx, const d
     }
   }
   cudaStream_t s = (cudaStream_t)stream;
+  // Two-stream form (bop_vsd_split_dev): the geometry pass runs on `sg`, the raster + pixel pass on
+  // `s`; an event orders each chunk's raster pass behind its geometry pass and the next chunk's
+  // geometry pass behind the raster pass that still reads the workspace.
+  cudaStream_t sg = geometry_stream ? (cudaStream_t)geometry_stream : s;
+  const bool split = sg != s;
+  auto order = [](cudaStream_t first, cudaStream_t then) -> int {
+    cudaEvent_t ev;
+    BOP_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t e = cudaEventRecord(ev, first);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(then, ev, 0);
+    cudaEventDestroy(ev);   // released once the recorded work has completed
+    BOP_CUDA(e);
+    return 0;
+  };
   unsigned char* ws = (unsigned char*)workspace;
   std::vector<int32_t> rebased;
   int g0 = 0;   // first group of the chunk
   for (int c0 = 0; c0 < n_pairs;) {
+    if (split && c0 > 0) {
+      if (int rc = order(s, sg)) return rc;
+    }
     int nc, ng = 0;
     if (group_off_host) {   // whole groups, at most L.chunk pairs (a group never exceeds a chunk: chunk >= kMaxGroup or n_pairs)
       int g1 = g0;
@@ -1635,17 +1652,20 @@ static int vsd_impl(const bop_model_dev* models, const int32_t* obj_idx, const d
       ng = g1 - g0;
       rebased.resize((size_t)ng + 1);
       for (int k = 0; k <= ng; ++k) rebased[k] = group_off_host[g0 + k] - c0;
-      BOP_CUDA(cudaMemcpyAsync(ws + L.goff, rebased.data(), sizeof(int32_t) * ((size_t)ng + 1), cudaMemcpyHostToDevice, s));
-      BOP_CUDA(cudaStreamSynchronize(s));   // `rebased` is reused by the next chunk
+      BOP_CUDA(cudaMemcpyAsync(ws + L.goff, rebased.data(), sizeof(int32_t) * ((size_t)ng + 1), cudaMemcpyHostToDevice, sg));
+      BOP_CUDA(cudaStreamSynchronize(sg));   // `rebased` is reused by the next chunk
       g0 = g1;
     } else {
       nc = n_pairs - c0 < L.chunk ? n_pairs - c0 : L.chunk;
     }
     if (int rc = launch_plan(models, obj_idx + c0, pose_est + 12 * (size_t)c0, pose_gt + 12 * (size_t)c0,
                              im_idx + c0, K, diameters ? diameters + c0 : nullptr, 0, nc, 2, pp.H,
-                             pp.W, prm->gate, ws, L, s, 0, 0,
+                             pp.W, prm->gate, ws, L, sg, 0, 0,
                              group_off_host ? (const int32_t*)(ws + L.goff) : nullptr, ng))
       return rc;
+    if (split) {
+      if (int rc = order(sg, s)) return rc;
+    }
     FusedArgs a;
     a.models = models;
     a.desc = (const PairDesc*)(ws + L.desc);
@@ -1685,6 +1705,18 @@ extern "C" int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                            void* workspace, size_t workspace_bytes, void* stream) {
   return vsd_impl(models, obj_idx, pose_est, pose_gt, depth_test, depth_scale, im_idx, K, diameters, n_pairs,
                   nullptr, 0, max_geom, prm, errors_out, counts_out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int bop_vsd_split_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                                 const double* pose_est, const double* pose_gt, const void* depth_test,
+                                 const float* depth_scale, const int32_t* im_idx, const double* K,
+                                 const double* diameters, int n_pairs, int max_geom,
+                                 const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
+                                 void* workspace, size_t workspace_bytes, void* geometry_stream,
+                                 void* raster_stream) {
+  return vsd_impl(models, obj_idx, pose_est, pose_gt, depth_test, depth_scale, im_idx, K, diameters, n_pairs,
+                  nullptr, 0, max_geom, prm, errors_out, counts_out, workspace, workspace_bytes, raster_stream,
+                  geometry_stream);
 }
 
 extern "C" int bop_vsd_grouped_dev(const bop_model_dev* models, const int32_t* obj_idx,

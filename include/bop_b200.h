@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BOP_B200_ABI_VERSION 5
+#define BOP_B200_ABI_VERSION 6
 #define BOP_MAX_TAUS 16      /* taus per launch; the host layer chunks longer lists */
 #define BOP_MAX_SYMS_PER_CTA 16
 
@@ -217,6 +217,26 @@ int bop_vsd_dev(const bop_model_dev* models, const int32_t* obj_idx,
                 const bop_vsd_params* prm, double* errors_out,
                 int64_t* counts_out, void* workspace, size_t workspace_bytes,
                 void* stream);
+/* bop_vsd_dev with its two passes on two streams: the geometry pass (projection, planning, sorted
+ * triangle lists) is launched on `geometry_stream`, the raster + pixel pass and the final
+ * reduction on `raster_stream`; events order each raster pass behind its geometry pass (and, for
+ * batches that take several workspace chunks, the next geometry pass behind the raster pass that
+ * still reads the workspace).  For callers that partition the SMs (CUDA green contexts,
+ * bop_toolkit_b200/sm_partition.py): with HOST-resident depth the pixel pass is bound by the PCIe
+ * link, and on a partition of its own it overlaps the geometry pass of the next batch.  The
+ * inputs the geometry pass reads must be ready on geometry_stream, depth_test / depth_scale on
+ * raster_stream (or earlier on geometry_stream); the results are ready on raster_stream.  A
+ * workspace may be reused by a later call once that call's geometry_stream is ordered behind this
+ * call's raster_stream.  Same results as bop_vsd_dev, bit for bit.  (Reference: the same
+ * pose_error.vsd, :17-93; the reference has no streams.)                                      */
+int bop_vsd_split_dev(const bop_model_dev* models, const int32_t* obj_idx,
+                      const double* pose_est, const double* pose_gt, const void* depth_test,
+                      const float* depth_scale, const int32_t* im_idx, const double* K,
+                      const double* diameters, int n_pairs, int max_geom,
+                      const bop_vsd_params* prm, double* errors_out, int64_t* counts_out,
+                      void* workspace, size_t workspace_bytes, void* geometry_stream,
+                      void* raster_stream);
+
 /* bop_vsd_dev for pairs that share their GT pose: scripts/eval_calc_errors.py:281-289 pairs every
  * estimate of an object with every GT pose of it, so a GT pose is typically evaluated against
  * several estimates.  group_off_host (HOST array, [n_groups + 1], group_off_host[0] = 0,

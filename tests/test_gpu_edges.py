@@ -543,3 +543,74 @@ def test_calls_on_two_streams_share_the_workspace_in_order(B):
     for (e1, c1), (e0, c0) in zip(got, want):
       assert np.array_equal(c1.cpu().numpy(), c0) and np.array_equal(e1.cpu().numpy(), e0, equal_nan=True)
   assert not np.array_equal(want[0][1], want[1][1])
+
+
+def test_split_streams_on_an_sm_partition_are_bit_identical(B):
+  """bop_vsd_split_dev (vsd_batch(raster_stream=...)): geometry pass on one stream, raster + pixel
+  pass on another, ordered by events inside the call -- on two plain streams and on the two
+  streams of an SM partition (sm_partition.SmPartition, CUDA green contexts), pipelined over
+  several batches with alternating private workspaces the way bench.py's end-to-end leg does,
+  resident float32 depth and host-mapped uint16 depth: results equal bop_vsd_dev's bit for bit."""
+  import torch
+  from bop_toolkit_b200 import synth, sm_partition
+  K = synth.LM_K
+  pts, faces = synth.make_mesh(40, 80, 200.0, seed=61)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  dev = ms.device
+  n = 1200
+  cases = []
+  for seed in (62, 63, 64):
+    R_e, t_e, R_g, t_g = synth.make_pose_pairs(n, seed=seed, z_range=(400.0, 1200.0), outlier_frac=0.05)
+    cases.append((B.pack_poses(R_e, t_e), B.pack_poses(R_g, t_g)))
+  rng = np.random.default_rng(65)
+  d16 = (rng.uniform(7000, 11000, size=(4, 480, 640))).astype(np.uint16)        # 0.1 mm units
+  d16[:, ::7, ::5] = 0
+  h_d16 = torch.from_numpy(d16.view(np.int16)).pin_memory()
+  scale = np.full(4, 0.1, np.float32)
+  d_f32 = torch.from_numpy(d16.astype(np.float32) * np.float32(0.1)).to(dev)
+  im = (np.arange(n) % 4).astype(np.int32)
+  Ks = np.tile(K.reshape(1, 9), (4, 1))
+  taus = [0.05 * (k + 1) for k in range(10)]
+
+  def run(c, host, **kw):
+    if host:
+      return B.vsd_batch(ms, 0, c[0], c[1], h_d16, im, Ks, 15, taus, True, 'step', return_counts=True,
+                         depth_scale=scale, zero_copy=True, **kw)
+    return B.vsd_batch(ms, 0, c[0], c[1], d_f32, im, Ks, 15, taus, True, 'step', return_counts=True, **kw)
+
+  want = {(i, host): tuple(x.cpu().numpy() for x in run(c, host)) for i, c in enumerate(cases) for host in (False, True)}
+  assert np.array_equal(want[(0, False)][1], want[(0, True)][1])     # u16 * 0.1f == the float32 image
+  torch.cuda.synchronize()
+  part = sm_partition.SmPartition(dev.index if dev.index is not None else 0, 96)
+  assert sum(part.sm_counts) == torch.cuda.get_device_properties(dev).multi_processor_count
+  assert min(part.sm_counts) >= 8
+  plain = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
+  for s_r, s_c in (plain, part.streams):
+    wss = [B.Workspace(dev), B.Workspace(dev)]
+    done = [None, None]
+    got = []
+    order = [(i % 3, bool(i & 1)) for i in range(7)]
+    for s_ in (s_r, s_c):
+      s_.wait_stream(torch.cuda.current_stream())
+    for j, (i, host) in enumerate(order):
+      k = j % 2
+      with torch.cuda.stream(s_c), B.private_workspace(wss[k]):
+        if done[k] is not None:
+          s_c.wait_event(done[k])
+        e, c = run(cases[i], host, raster_stream=s_r)
+      with torch.cuda.stream(s_r):
+        done[k] = torch.cuda.Event()
+        done[k].record(s_r)
+      got.append((e, c))
+    torch.cuda.synchronize()
+    for (i, host), (e, c) in zip(order, got):
+      assert np.array_equal(c.cpu().numpy(), want[(i, host)][1]), (i, host)
+      assert np.array_equal(e.cpu().numpy(), want[(i, host)][0], equal_nan=True), (i, host)
+  # more taus than one launch takes: the tau chunks reuse the workspace, ordered inside vsd_batch
+  many = [0.01 * (k + 1) for k in range(45)]
+  e0 = B.vsd_batch(ms, 0, cases[0][0], cases[0][1], d_f32, im, Ks, 15, many, True, 'step').cpu().numpy()
+  with torch.cuda.stream(part.streams[1]), B.private_workspace(B.Workspace(dev)):
+    e1 = B.vsd_batch(ms, 0, cases[0][0], cases[0][1], d_f32, im, Ks, 15, many, True, 'step', raster_stream=part.streams[0])
+  torch.cuda.synchronize()
+  assert np.array_equal(e1.cpu().numpy(), e0, equal_nan=True)
