@@ -446,6 +446,10 @@ def gpu_arm(args):
   def step_e2e_pipe():
     part = part_state['part']
     s_r, s_c = part.streams
+    if part_state.pop('pipeline_empty', False):
+      # nothing is in flight (first step after a synchronisation): this step's geometry + MSSD + MSPD
+      # may use the whole GPU instead of filling the pipeline from the small partition
+      s_c = torch.cuda.current_stream()
     k = part_state['k'] = (part_state.get('k', 0) + 1) % len(part_state['ws'])
     with torch.cuda.stream(s_c), batch.private_workspace(part_state['ws'][k]):
       if part_state.get('done%d' % k) is not None:   # this workspace's previous raster pass
@@ -488,6 +492,7 @@ def gpu_arm(args):
     e0.record()
     for st in part.streams:
       st.wait_stream(cur)
+    part_state['pipeline_empty'] = True
     for _ in range(steps):
       outs = step_e2e_part()
     for st in part.streams:
