@@ -471,8 +471,6 @@ struct PixParams {
   int H, W;
   int depth_dtype;
   int vec_ok;        // rows of depth_test are 16-byte (f32) / 8-byte (u16) aligned
-  int host_depth;    // depth_test is host memory mapped into the device (zero-copy): the pixel pass
-                     // issues L2 prefetches for all of a thread's groups before it consumes the first
   // float32 decision path (step cost): thresholds and their undecidable bands (see vsd_pixel_fast)
   float tau_f[BOP_MAX_TAUS], tau_eps[BOP_MAX_TAUS];
   int fast;          // 1: try the float32 decision path first
@@ -1044,21 +1042,6 @@ fused_kernel(const __grid_constant__ FusedArgs a) {
     const float inv_diam = a.pp.normalized ? (float)(1.0 / diameter) : 1.f;
     const bool fast = MODE == MODE_STEP && a.pp.fast != 0;
     const float scale = (a.pp.depth_dtype == BOP_DEPTH_U16 && a.depth_scale) ? a.depth_scale[sD.im] : 1.f;
-    if (a.pp.host_depth) {
-      // Host-mapped depth: a load is a PCIe round trip (~2 us), and the loop below would pay one
-      // per group, one after the other.  Ask for all of this thread's groups first.
-      const int esz = a.pp.depth_dtype == BOP_DEPTH_F32 ? 4 : 2;
-      const char* im0 = (const char*)a.depth_test + (size_t)sD.im * a.pp.H * a.pp.W * esz;
-      for (int g = tid; g < ngroups; g += nthr) {
-        const int r = g / w4, c4 = g - r * w4;
-        const uint4 ze = *(const uint4*)(zt + r * w + 4 * c4);
-        const uint4 zg = *(const uint4*)(zt + a.tile_px + r * w + 4 * c4);
-        if (((ze.x | ze.y | ze.z | ze.w) | (zg.x | zg.y | zg.z | zg.w)) != 0u) {
-          const char* p = im0 + ((size_t)(cy0 + r) * a.pp.W + cx0 + 4 * c4) * esz;
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-        }
-      }
-    }
     for (int g = tid; g < ngroups; g += nthr) {
       const int r = g / w4, c4 = g - r * w4;
       const uint4 ze = *(const uint4*)(zt + r * w + 4 * c4);
@@ -1428,12 +1411,6 @@ int fill_pix_params(const bop_vsd_params* prm, const void* depth_test, PixParams
   pp.depth_dtype = prm->depth_dtype;
   const size_t al = prm->depth_dtype == BOP_DEPTH_F32 ? 16 : 8;
   pp.vec_ok = (prm->width % 4 == 0) && (((uintptr_t)depth_test) % al == 0);
-  pp.host_depth = 0;
-  if (depth_test && !getenv("BOP_NO_DEPTH_PREFETCH")) {
-    cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, depth_test) == cudaSuccess) pp.host_depth = at.type == cudaMemoryTypeHost;
-    else cudaGetLastError();
-  }
   return 0;
 }
 

@@ -5,7 +5,7 @@ TAG=${1:-evidence}
 OUT=gpurun_out/$TAG; mkdir -p $OUT
 timeout 900 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref rc=$?"
-CMD="python bench.py --pairs 2000 --steps 2 --warmup 3 --no-cpu-baseline --cfg5-images 0"
+CMD="python bench.py --pairs 2000 --steps 2 --warmup 3 --no-cpu-baseline --cfg5-images 0 --e2e-sms 0"
 timeout 900 $CMD > $OUT/bench_small.json 2> /dev/null
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/launches.csv $CMD > $OUT/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 # launches before the bench steps: cull probes of the second ModelSet (3 per model) + depth synthesis (5 chunks)
