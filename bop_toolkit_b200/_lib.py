@@ -14,6 +14,7 @@ SOURCES = ['api.cu', 'pose_points.cu', 'vsd.cu', 'png_depth.cu', 'error_json.cpp
 HEADERS = ['common.cuh', 'raster.cuh', 'png_inflate.cuh', os.path.join('..', '..', 'include', 'bop_b200.h')]
 
 BOP_MAX_TAUS = 16
+ABI_VERSION = 6            # BOP_B200_ABI_VERSION of include/bop_b200.h
 STATIC_MAX_PAIRS = 4096   # BOP_STATIC_MAX_PAIRS (bop_vsd_from_depth_static_dev)
 COST_TYPES = {'step': 0, 'tlinear': 1}
 VISIB_MODES = {'bop19': 0, 'bop18': 1}
@@ -159,10 +160,17 @@ def lib():
         'bop_toolkit_b200: %s is missing. Build it with `python -c "import __graft_entry__ as g; '
         'g.build()"` (needs nvcc). There is no CPU fallback.' % SO_PATH)
     l = ctypes.CDLL(SO_PATH)
+    stale = 'bop_toolkit_b200: %s is older than these sources (%%s); rebuild it with `python -c "import ' \
+      '__graft_entry__ as g; g.build()"`' % SO_PATH
     for name, (res, args) in _SIGNATURES.items():
-      fn = getattr(l, name)
+      try:
+        fn = getattr(l, name)
+      except AttributeError:
+        raise ImportError(stale % ('no symbol %s' % name))
       fn.restype = res
       fn.argtypes = args
+    if l.bop_abi_version() != ABI_VERSION:
+      raise ImportError(stale % ('ABI %d, expected %d' % (l.bop_abi_version(), ABI_VERSION)))
     _lib = l
   return _lib
 

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
   for name in declared:
     assert hasattr(lib, name), 'missing export: ' + name
   assert sorted(_lib.EXPORTED_SYMBOLS) == declared     # the ctypes table covers the header
-  assert _lib.lib().bop_abi_version() == 6
+  assert _lib.lib().bop_abi_version() == _lib.ABI_VERSION == 6
 
 
 def test_struct_layouts_match_header():
