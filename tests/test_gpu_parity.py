@@ -709,3 +709,32 @@ def test_vsd_grouped_equals_ungrouped(B, oracle_built):
     else:
       assert np.abs(e0[order] - e1).max() <= 1e-12      # float64 sums of the tlinear cost: order of the adds
     assert (c1[:, 0] > 0).sum() > P // 2 and (e1 == 1.0).all(axis=1).sum() >= 12
+
+
+@pytest.mark.parametrize('H,W,scale,cost', [(97, 150, 0.22, 'step'), (120, 161, 0.25, 'tlinear'), (61, 64, 0.1, 'step'),
+                                            (240, 322, 0.5, 'tlinear')])
+def test_vsd_fused_vs_oracle_odd_sizes(B, oracle_built, H, W, scale, cost):
+  """Image sizes that are not multiples of 4 (scalar depth loads, padded regions of interest at the
+  right border), scaled intrinsics and both costs, 8 pairs each against the oracle: 1e-3 per tau."""
+  from oracle import pose_error_oracle as po
+  n = 8
+  K, pts, faces, R_e, t_e, R_g, t_g, depth, ren = _vsd_case(B, n, seed=70 + W, H=H, W=W, scale=scale, n_lat=20, n_lon=40)
+  ms = B.ModelSet()
+  ms.add(1, pts, faces, None, 200.0)
+  taus = list(np.arange(0.05, 0.51, 0.05))
+  Ks = np.tile(K.reshape(1, 9), (n, 1))
+  err, cnt = B.vsd_batch(ms, 0, _poses(B, R_e, t_e), _poses(B, R_g, t_g), depth, np.arange(n, dtype=np.int32), Ks, 15,
+                         taus, True, cost, return_counts=True)
+  err, cnt = err.cpu().numpy(), cnt.cpu().numpy()
+  seen = 0
+  for i in range(n):
+    ref, rc = po.vsd_from_depth(
+      ren.render_object(1, R_e[i], t_e[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2])['depth'],
+      ren.render_object(1, R_g[i], t_g[i], K[0, 0], K[1, 1], K[0, 2], K[1, 2])['depth'],
+      depth[i], K, 15, taus, True, 200.0, cost, return_counts=True)
+    assert abs(int(cnt[i, 0]) - rc[0]) <= 0.01 * rc[0] + 3, (i, cnt[i, 0], rc[0])
+    # a silhouette pixel more or less moves the error of a small mask by 1 / union
+    tol = 1e-3 if rc[0] >= 3000 else 1e-3 + 3.0 / max(rc[0], 1)
+    assert np.abs(err[i] - np.array(ref)).max() <= tol, (i, err[i], ref, rc)
+    seen += rc[0] > 0
+  assert seen >= n // 2
