@@ -139,6 +139,21 @@ def test_k2_bit_exact_vs_reference_golden(B, golden):
                                None, np.tile(g['vsd_K'].reshape(1, 9), (n, 1)), 180.0, 15,
                                [5.0, 20.0], False, 'step').cpu().numpy()
   assert np.array_equal(err, g['vsd_unnorm'])
+  # 'bop18' visibility (visibility.py:29-32; pose_error.vsd itself always asks for 'bop19'): against the
+  # oracle, whose masks are pinned to the reference's visibility module in tests/test_oracle_golden.py
+  from oracle import pose_error_oracle as po
+  err, cnt = B.vsd_from_depth_batch(g['vsd_render_est'], g['vsd_render_gt'], g['vsd_depth_test'],
+                                    np.arange(n, dtype=np.int32), np.tile(g['vsd_K'].reshape(1, 9), (n, 1)),
+                                    180.0, 15, taus, True, 'step', visib_mode='bop18', return_counts=True)
+  err, cnt = err.cpu().numpy(), cnt.cpu().numpy()
+  differs = False
+  for i in range(n):
+    ref, rc = po.vsd_from_depth(g['vsd_render_est'][i], g['vsd_render_gt'][i], g['vsd_depth_test'][i], g['vsd_K'],
+                                15, taus, True, 180.0, 'step', visib_mode='bop18', return_counts=True)
+    assert int(cnt[i, 0]) == rc[0] and int(cnt[i, 1]) == rc[1]
+    assert np.array_equal(err[i], np.array(ref))
+    differs = differs or not np.array_equal(err[i], g['vsd_step'][i])
+  assert differs            # the mode matters on this data (missing depth pixels)
 
 
 # ------------------------------------------------------------------ oracle, seeded
